@@ -1,0 +1,99 @@
+"""Thin, allocation-free wrappers over the collective kernels (csrc/collectives.cu).
+
+Everything here works on *heap offsets*: the caller has already placed its operands in the
+symmetric heap (see runtime/symm.py). ``comms`` is a list of device communicators -- one in
+production, several when emulating ranks on a single GPU -- and is turned into the contiguous
+C array the native entry points expect.
+
+Reference call sites these replace: comm.py:16 (Barrier), :22 (Allreduce), :29 (Allgather),
+:36 (Reduce_scatter_block), :61 (Alltoall), :63-107 (myAllreduce), :110-199 (myAlltoall/2).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Sequence
+
+import torch
+
+from .. import _native as N
+
+_TORCH2CC = None
+
+
+def cc_dtype(dtype) -> int:
+    """torch / numpy dtype -> ccmpi_dtype."""
+    global _TORCH2CC
+    if _TORCH2CC is None:
+        import numpy as np
+        _TORCH2CC = {
+            torch.float32: N.F32, torch.bfloat16: N.BF16, torch.float16: N.F16, torch.float64: N.F64,
+            torch.int32: N.I32, torch.int64: N.I64, torch.uint8: N.U8,
+            np.dtype("float32"): N.F32, np.dtype("float16"): N.F16, np.dtype("float64"): N.F64,
+            np.dtype("int32"): N.I32, np.dtype("int64"): N.I64, np.dtype("uint8"): N.U8,
+        }
+    try:
+        return _TORCH2CC[dtype]
+    except (KeyError, TypeError):
+        import numpy as np
+        try:
+            return _TORCH2CC[np.dtype(dtype)]
+        except Exception:
+            raise TypeError(f"dtype {dtype!r} is not supported by the device collectives") from None
+
+
+def _arr(comms: Sequence[N.DevComm]):
+    n = len(comms)
+    if not 1 <= n <= N.MAX_VRANKS:
+        raise ValueError(f"{n} emulated ranks requested; supported: 1..{N.MAX_VRANKS}")
+    a = (N.DevComm * n)(*comms)
+    return a, n
+
+
+def _sp(stream) -> C.c_void_p:
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return C.c_void_p(s.cuda_stream)
+
+
+def barrier(comms, stream=None):
+    a, n = _arr(comms)
+    N.check(N.device_lib().ccmpi_barrier(a, n, _sp(stream)), "ccmpi_barrier")
+
+
+def allreduce(comms, dtype: int, op: int, src_off: int, dst_off: int, count: int, *, tmp_off: int = 0,
+              algo: int = N.AR_AUTO, scale: float = 1.0, out_dtype: int = -1, max_blocks: int = 0, stream=None):
+    a, n = _arr(comms)
+    N.check(N.device_lib().ccmpi_allreduce(a, n, algo, dtype, op, src_off, dst_off, tmp_off, count,
+                                           C.c_float(scale), out_dtype, max_blocks, _sp(stream)), "ccmpi_allreduce")
+
+
+def allgather(comms, src_off: int, dst_off: int, rows: int, row_bytes: int, src_row_stride: int,
+              dst_row_stride: int, *, use_mc: bool = True, max_blocks: int = 0, stream=None):
+    a, n = _arr(comms)
+    N.check(N.device_lib().ccmpi_allgather(a, n, src_off, dst_off, rows, row_bytes, src_row_stride,
+                                           dst_row_stride, int(use_mc), max_blocks, _sp(stream)), "ccmpi_allgather")
+
+
+def reduce_scatter(comms, dtype: int, op: int, src_off: int, dst_off: int, rows: int, row_elems: int,
+                   src_row_stride: int, dst_row_stride: int, *, use_mc: bool = True, max_blocks: int = 0,
+                   stream=None):
+    a, n = _arr(comms)
+    N.check(N.device_lib().ccmpi_reduce_scatter(a, n, dtype, op, src_off, dst_off, rows, row_elems,
+                                                src_row_stride, dst_row_stride, int(use_mc), max_blocks,
+                                                _sp(stream)), "ccmpi_reduce_scatter")
+
+
+def alltoall(comms, src_off: int, dst_off: int, seg_bytes: int, *, staggered: bool = False, max_blocks: int = 0,
+             stream=None):
+    a, n = _arr(comms)
+    N.check(N.device_lib().ccmpi_alltoall(a, n, src_off, dst_off, seg_bytes, int(staggered), max_blocks,
+                                          _sp(stream)), "ccmpi_alltoall")
+
+
+def put_signal(comm: N.DevComm, peer: int, src_off: int, dst_off: int, nbytes: int, flag: int, stream=None):
+    a, n = _arr([comm])
+    N.check(N.device_lib().ccmpi_put_signal(a, n, peer, src_off, dst_off, nbytes, flag, _sp(stream)), "ccmpi_put_signal")
+
+
+def wait_signal(comm: N.DevComm, peer: int, flag: int, stream=None):
+    a, n = _arr([comm])
+    N.check(N.device_lib().ccmpi_wait_signal(a, n, peer, flag, _sp(stream)), "ccmpi_wait_signal")

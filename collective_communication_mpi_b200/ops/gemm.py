@@ -1,0 +1,90 @@
+"""bf16 GEMMs on the hand-written tcgen05 kernel (csrc/gemm_tcgen05.cu).
+
+The reference contains no matrix multiply: README.md:173-175 says forward/backward compute is
+"taken care of", and func_impl.py only moves activations around it. These three products are
+what a tensor-parallel FC layer needs between those communication steps, each in the storage
+layout it naturally has (no transposes are ever materialised):
+
+================  ==========================  =============================
+``matmul_nn``     ``y  = x @ w``              forward,  w stored ``[in, out]``
+``matmul_nt``     ``dx = dy @ w.T``           backward, w stored ``[in, out]``
+``matmul_tn``     ``dw = x.T @ dy``           weight gradient
+================  ==========================  =============================
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from .. import _native as N
+
+
+def _stream_ptr(stream=None) -> int:
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return s.cuda_stream
+
+
+def _check_operand(t: torch.Tensor, name: str):
+    if not t.is_cuda or t.dtype != torch.bfloat16 or t.dim() != 2:
+        raise TypeError(f"{name} must be a 2-D CUDA bfloat16 tensor (got {t.dtype}, {tuple(t.shape)}, {t.device})")
+    if t.stride(1) != 1:
+        raise ValueError(f"{name} must have unit stride on its last axis (strides {t.stride()})")
+    if t.stride(0) % 8 or t.data_ptr() % 16:
+        raise ValueError(f"{name} needs 16-byte aligned rows (row stride {t.stride(0)} elements)")
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, *, a_km: bool = False, b_kn: bool = False,
+         out: torch.Tensor | None = None, out_dtype: torch.dtype = torch.bfloat16,
+         accumulate: bool = False, num_sms: int = 0, stream=None) -> torch.Tensor:
+    """``C[M,N] = A[M,K] @ B[K,N]`` with fp32 accumulation in tensor memory.
+
+    ``a`` is stored ``[M,K]`` (or ``[K,M]`` when ``a_km``); ``b`` is stored ``[N,K]`` (the
+    ``nn.Linear`` weight layout) or ``[K,N]`` when ``b_kn``. ``num_sms`` caps the persistent grid
+    (leave SMs free for a communication kernel running alongside).
+    """
+    _check_operand(a, "a")
+    _check_operand(b, "b")
+    if a_km:
+        K, M = a.shape
+    else:
+        M, K = a.shape
+    if b_kn:
+        Kb, Nn = b.shape
+    else:
+        Nn, Kb = b.shape
+    if K != Kb:
+        raise ValueError(f"inner dimensions differ: {K} vs {Kb}")
+    if out is None:
+        out = torch.empty((M, Nn), dtype=out_dtype, device=a.device)
+    else:
+        if out.shape != (M, Nn) or out.stride(1) != 1 or not out.is_cuda:
+            raise ValueError("out has the wrong shape / layout")
+        out_dtype = out.dtype
+    if out_dtype not in (torch.bfloat16, torch.float32):
+        raise TypeError("GEMM output must be bfloat16 or float32")
+    if accumulate and out_dtype != torch.float32:
+        raise TypeError("accumulate=True needs a float32 output")
+    lib = N.device_lib()
+    rc = lib.ccmpi_gemm_bf16(
+        C.c_void_p(a.data_ptr()), C.c_void_p(b.data_ptr()), C.c_void_p(out.data_ptr()),
+        M, Nn, K, a.stride(0), b.stride(0), out.stride(0), int(a_km), int(b_kn),
+        N.BF16 if out_dtype == torch.bfloat16 else N.F32, int(accumulate), int(num_sms),
+        C.c_void_p(_stream_ptr(stream)))
+    N.check(rc, "ccmpi_gemm_bf16")
+    return out
+
+
+def matmul_nn(x: torch.Tensor, w: torch.Tensor, **kw) -> torch.Tensor:
+    """``x[M,K] @ w[K,N]``."""
+    return gemm(x, w, b_kn=True, **kw)
+
+
+def matmul_nt(x: torch.Tensor, w: torch.Tensor, **kw) -> torch.Tensor:
+    """``x[M,K] @ w[N,K].T``."""
+    return gemm(x, w, **kw)
+
+
+def matmul_tn(x: torch.Tensor, dy: torch.Tensor, **kw) -> torch.Tensor:
+    """``x[T,M].T @ dy[T,N]`` (contraction over the token axis)."""
+    return gemm(x, dy, a_km=True, b_kn=True, **kw)

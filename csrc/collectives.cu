@@ -1,0 +1,743 @@
+// Stand-alone collective kernels over peer-mapped symmetric memory (NVLink 5 / NVSwitch).
+//
+// What MPI does for the reference -- MPI_Barrier (comm.py:16), MPI_Allreduce (:22),
+// MPI_Allgather (:29), MPI_Reduce_scatter_block (:36), MPI_Alltoall (:61) -- and what the
+// reference hand-rolls over Send/Recv (myAllreduce :63-107, myAlltoall :110-159, myAlltoall2
+// :162-199) are single kernels here: every rank launches the same grid, block b of every rank
+// forms a little group that synchronises through epoch-numbered flags in the ranks' signal
+// pads (st.release.sys / ld.acquire.sys), and the payload moves with 16-byte loads/stores on
+// peer pointers or with multimem instructions that the NVSwitch executes.
+//
+// "Virtual ranks": the launch carries up to CCMPI_MAX_VRANKS communicators. In production
+// there is one. In single-GPU tests several emulated ranks run inside ONE cooperative launch
+// (blockIdx.x % nvr selects the rank), which exercises the same protocol code without ever
+// having two kernels wait on each other on one GPU.
+#include "host_common.h"
+#include "ptx.cuh"
+
+namespace coll {
+
+constexpr int THREADS = 512;
+
+struct Launch {
+    int nvr;
+    int pad_[3];
+    ccmpi_dev_comm c[CCMPI_MAX_VRANKS];
+};
+
+struct Ctx {
+    const ccmpi_dev_comm* c;
+    int blk;      // block index within the rank
+    int nblk;     // blocks per rank
+};
+
+__device__ __forceinline__ Ctx make_ctx(const Launch& lp) {
+    Ctx x;
+    x.c = &lp.c[blockIdx.x % lp.nvr];
+    x.blk = blockIdx.x / lp.nvr;
+    x.nblk = gridDim.x / lp.nvr;
+    return x;
+}
+
+// Block-granular barrier across ranks. Block b of rank r publishes epoch e to every member's
+// pad word [b][r] and waits until its own pad holds >= e from everyone. Epochs only grow, so
+// the flags never need resetting and a kernel can be replayed from a CUDA graph.
+__device__ __forceinline__ void block_barrier(const Ctx& x) {
+    const ccmpi_dev_comm& c = *x.c;
+    __syncthreads();
+    uint32_t* self = c.pad[c.rank];
+    const uint32_t epoch = *reinterpret_cast<volatile uint32_t*>(self + CCMPI_PAD_EPOCH + x.blk) + 1;
+    if (threadIdx.x < c.size) {
+        const int peer = threadIdx.x;
+        ptx::st_release_sys(c.pad[peer] + CCMPI_PAD_BARRIER + x.blk * CCMPI_MAX_RANKS + c.rank, epoch);
+        ptx::wait_flag_ge_sys(self + CCMPI_PAD_BARRIER + x.blk * CCMPI_MAX_RANKS + peer, epoch, peer);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) *reinterpret_cast<volatile uint32_t*>(self + CCMPI_PAD_EPOCH + x.blk) = epoch;
+}
+
+// ------------------------------------------------------------------------------------------------
+// element-wise reduce machinery on 16-byte vectors
+// ------------------------------------------------------------------------------------------------
+template <int OP, typename A>
+__device__ __forceinline__ A apply(A a, A b) {
+    if constexpr (OP == CCMPI_SUM) return a + b;
+    else if constexpr (OP == CCMPI_MIN) return b < a ? b : a;
+    else return b > a ? b : a;
+}
+
+// Accumulator type: 16-bit floats accumulate in fp32 and round once.
+template <typename T> struct AccOf { using type = T; };
+template <> struct AccOf<__nv_bfloat16> { using type = float; };
+template <> struct AccOf<__half> { using type = float; };
+
+template <typename T> __device__ __forceinline__ typename AccOf<T>::type to_acc(T v) { return v; }
+template <> __device__ __forceinline__ float to_acc<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <> __device__ __forceinline__ float to_acc<__half>(__half v) { return __half2float(v); }
+
+template <typename T, typename A> __device__ __forceinline__ T from_acc(A v) { return static_cast<T>(v); }
+template <> __device__ __forceinline__ __nv_bfloat16 from_acc<__nv_bfloat16, float>(float v) { return __float2bfloat16_rn(v); }
+template <> __device__ __forceinline__ __half from_acc<__half, float>(float v) { return __float2half_rn(v); }
+
+template <typename T>
+struct Vec {
+    static constexpr int N = 16 / sizeof(T);
+    union {
+        uint4 raw;
+        T e[N];
+    };
+    __device__ Vec() {}
+};
+
+template <typename T>
+struct AccVec {
+    using A = typename AccOf<T>::type;
+    static constexpr int N = 16 / sizeof(T);
+    A e[N];
+    __device__ __forceinline__ void init(const uint4& r) {
+        Vec<T> v;
+        v.raw = r;
+#pragma unroll
+        for (int i = 0; i < N; ++i) e[i] = to_acc<T>(v.e[i]);
+    }
+    template <int OP>
+    __device__ __forceinline__ void fold(const uint4& r) {
+        Vec<T> v;
+        v.raw = r;
+#pragma unroll
+        for (int i = 0; i < N; ++i) e[i] = apply<OP, A>(e[i], to_acc<T>(v.e[i]));
+    }
+    __device__ __forceinline__ uint4 pack() const {
+        Vec<T> v;
+#pragma unroll
+        for (int i = 0; i < N; ++i) v.e[i] = from_acc<T, A>(e[i]);
+        return v.raw;
+    }
+};
+
+// scale + (optional) cast of a reduced fp32 accumulator vector of N elements, stored to dst
+// element offset i0. Only floating outputs take a scale; integer types pass through.
+template <typename OutT, typename A, int N>
+__device__ __forceinline__ void store_scaled(OutT* dst, size_t i0, const A (&e)[N], float scale) {
+    constexpr int OB = N * sizeof(OutT);
+    union {
+        OutT o[N];
+        uint4 q[(OB + 15) / 16];
+        uint2 d;
+        uint32_t w;
+    } u;
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        if constexpr (std::is_same<A, float>::value) u.o[i] = from_acc<OutT, float>(e[i] * scale);
+        else u.o[i] = static_cast<OutT>(e[i]);
+    }
+    if constexpr (OB >= 16) {
+#pragma unroll
+        for (int k = 0; k < OB / 16; ++k) ptx::st_v4(reinterpret_cast<uint8_t*>(dst + i0) + 16 * k, u.q[k]);
+    } else if constexpr (OB == 8) {
+        *reinterpret_cast<uint2*>(dst + i0) = u.d;
+    } else {
+        *reinterpret_cast<uint32_t*>(dst + i0) = u.w;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// barrier
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(THREADS) barrier_kernel(const __grid_constant__ Launch lp) {
+    Ctx x = make_ctx(lp);
+    block_barrier(x);
+}
+
+// ------------------------------------------------------------------------------------------------
+// all-reduce, one-shot: every rank pulls all n copies and folds them in rank order 0..n-1,
+// the same order as the root loop of myAllreduce (comm.py:85-93), so results are bit-identical
+// on every rank and run to run.
+// ------------------------------------------------------------------------------------------------
+template <typename T, int OP, typename OutT, bool VECTOR>
+__global__ void __launch_bounds__(THREADS)
+allreduce_oneshot_kernel(const __grid_constant__ Launch lp, size_t src_off, size_t dst_off, size_t count, float scale) {
+    Ctx x = make_ctx(lp);
+    const ccmpi_dev_comm& c = *x.c;
+    using A = typename AccOf<T>::type;
+    block_barrier(x);
+    OutT* dst = reinterpret_cast<OutT*>(c.heap[c.rank] + dst_off);
+    if constexpr (VECTOR) {
+        constexpr int N = 16 / sizeof(T);
+        const size_t nvec = count / N;
+        for (size_t i = (size_t)x.blk * THREADS + threadIdx.x; i < nvec; i += (size_t)x.nblk * THREADS) {
+            uint4 r[CCMPI_MAX_RANKS];
+#pragma unroll
+            for (int p = 0; p < CCMPI_MAX_RANKS; ++p)
+                if (p < c.size) r[p] = ptx::ld_v4(c.heap[p] + src_off + i * 16);
+            AccVec<T> acc;
+            acc.init(r[0]);
+#pragma unroll
+            for (int p = 1; p < CCMPI_MAX_RANKS; ++p)
+                if (p < c.size) acc.template fold<OP>(r[p]);
+            store_scaled<OutT, A, N>(dst, i * N, acc.e, scale);
+        }
+    } else {
+        for (size_t i = (size_t)x.blk * THREADS + threadIdx.x; i < count; i += (size_t)x.nblk * THREADS) {
+            A acc = to_acc<T>(reinterpret_cast<const T*>(c.heap[0] + src_off)[i]);
+            for (int p = 1; p < c.size; ++p)
+                acc = apply<OP, A>(acc, to_acc<T>(reinterpret_cast<const T*>(c.heap[p] + src_off)[i]));
+            if constexpr (std::is_same<A, float>::value) dst[i] = from_acc<OutT, float>(acc * scale);
+            else dst[i] = static_cast<OutT>(acc);
+        }
+    }
+    block_barrier(x);
+}
+
+// ------------------------------------------------------------------------------------------------
+// all-reduce, two-shot: rank r reduces slice r (pull, rank order), parks it in symmetric
+// scratch, then everyone gathers the n reduced slices. 2(n-1)/n of the payload crosses each
+// link instead of (n-1).
+// ------------------------------------------------------------------------------------------------
+template <typename T, int OP, typename OutT>
+__global__ void __launch_bounds__(THREADS)
+allreduce_twoshot_kernel(const __grid_constant__ Launch lp, size_t src_off, size_t dst_off, size_t tmp_off,
+                         size_t count, float scale) {
+    Ctx x = make_ctx(lp);
+    const ccmpi_dev_comm& c = *x.c;
+    using A = typename AccOf<T>::type;
+    constexpr int N = 16 / sizeof(T);
+    const size_t nvec = count / N;                       // host guarantees divisibility
+    const size_t per = (nvec + c.size - 1) / c.size;     // vectors per slice
+    block_barrier(x);
+    {
+        const size_t lo = per * c.rank, hi = min(nvec, lo + per);
+        OutT* tmp = reinterpret_cast<OutT*>(c.heap[c.rank] + tmp_off);
+        for (size_t i = lo + (size_t)x.blk * THREADS + threadIdx.x; i < hi; i += (size_t)x.nblk * THREADS) {
+            uint4 r[CCMPI_MAX_RANKS];
+#pragma unroll
+            for (int p = 0; p < CCMPI_MAX_RANKS; ++p)
+                if (p < c.size) r[p] = ptx::ld_v4(c.heap[p] + src_off + i * 16);
+            AccVec<T> acc;
+            acc.init(r[0]);
+#pragma unroll
+            for (int p = 1; p < CCMPI_MAX_RANKS; ++p)
+                if (p < c.size) acc.template fold<OP>(r[p]);
+            store_scaled<OutT, A, N>(tmp, i * N, acc.e, scale);
+        }
+    }
+    block_barrier(x);
+    {
+        constexpr size_t OV = N * sizeof(OutT);  // bytes of one output vector
+        uint8_t* dst = c.heap[c.rank] + dst_off;
+        for (int s = 0; s < c.size; ++s) {
+            const int p = (c.rank + s) % c.size;  // own slice first, then spread over peers
+            const size_t lo = per * p, hi = min(nvec, lo + per);
+            const uint8_t* from = c.heap[p] + tmp_off;
+            for (size_t i = lo + (size_t)x.blk * THREADS + threadIdx.x; i < hi; i += (size_t)x.nblk * THREADS) {
+                if constexpr (OV == 16) {
+                    ptx::st_v4(dst + i * 16, ptx::ld_v4(from + i * 16));
+                } else if constexpr (OV == 8) {
+                    *reinterpret_cast<uint2*>(dst + i * 8) = ptx::ld_v2(from + i * 8);
+                } else {
+#pragma unroll
+                    for (int k = 0; k < (int)(OV / 16); ++k)
+                        ptx::st_v4(dst + i * OV + 16 * k, ptx::ld_v4(from + i * OV + 16 * k));
+                }
+            }
+        }
+    }
+    block_barrier(x);
+}
+
+// ------------------------------------------------------------------------------------------------
+// all-reduce, NVLS: the switch reduces (multimem.ld_reduce) and broadcasts (multimem.st).
+// Each rank owns slice r; one load + one store per 16 bytes, no per-peer loops at all.
+// ------------------------------------------------------------------------------------------------
+template <typename T> __device__ __forceinline__ uint4 mc_ld_reduce(const void* p);
+template <> __device__ __forceinline__ uint4 mc_ld_reduce<float>(const void* p) { return ptx::multimem_ld_reduce_add_f32x4(p); }
+template <> __device__ __forceinline__ uint4 mc_ld_reduce<__nv_bfloat16>(const void* p) { return ptx::multimem_ld_reduce_add_bf16x8(p); }
+template <> __device__ __forceinline__ uint4 mc_ld_reduce<__half>(const void* p) { return ptx::multimem_ld_reduce_add_f16x8(p); }
+
+template <typename T, typename OutT>
+__global__ void __launch_bounds__(THREADS)
+allreduce_nvls_kernel(const __grid_constant__ Launch lp, size_t src_off, size_t dst_off, size_t count, float scale) {
+    Ctx x = make_ctx(lp);
+    const ccmpi_dev_comm& c = *x.c;
+    constexpr int N = 16 / sizeof(T);
+    constexpr int G = (sizeof(OutT) < sizeof(T)) ? (int)(sizeof(T) / sizeof(OutT)) : 1;  // input vectors per 16-byte output
+    const size_t ngrp = count / (N * G);
+    const size_t per = (ngrp + c.size - 1) / c.size;
+    const size_t lo = per * c.rank, hi = min(ngrp, lo + per);
+    const uint8_t* msrc = c.mc_heap + src_off;
+    uint8_t* mdst = c.mc_heap + dst_off;
+    const bool identity = (scale == 1.0f) && std::is_same<T, OutT>::value;
+    block_barrier(x);
+    for (size_t g = lo + (size_t)x.blk * THREADS + threadIdx.x; g < hi; g += (size_t)x.nblk * THREADS) {
+        if constexpr (std::is_same<T, OutT>::value) {
+            uint4 r = mc_ld_reduce<T>(msrc + g * 16);
+            if (!identity) {
+                AccVec<T> a;
+                a.init(r);
+#pragma unroll
+                for (int i = 0; i < N; ++i) a.e[i] = a.e[i] * scale;
+                r = a.pack();
+            }
+            ptx::multimem_st_v4(mdst + g * 16, r);
+        } else if constexpr (sizeof(OutT) < sizeof(T)) {
+            // fp32 in -> 16-bit out: two input vectors make one output vector
+            Vec<OutT> o;
+#pragma unroll
+            for (int k = 0; k < G; ++k) {
+                Vec<T> v;
+                v.raw = mc_ld_reduce<T>(msrc + (g * G + k) * 16);
+#pragma unroll
+                for (int i = 0; i < N; ++i) o.e[k * N + i] = from_acc<OutT, float>(to_acc<T>(v.e[i]) * scale);
+            }
+            ptx::multimem_st_v4(mdst + g * 16, o.raw);
+        } else {
+            // 16-bit in -> fp32 out: one input vector makes two output vectors
+            Vec<T> v;
+            v.raw = mc_ld_reduce<T>(msrc + g * 16);
+            constexpr int R = sizeof(OutT) / sizeof(T);
+#pragma unroll
+            for (int k = 0; k < R; ++k) {
+                Vec<OutT> o;
+#pragma unroll
+                for (int i = 0; i < N / R; ++i) o.e[i] = static_cast<OutT>(to_acc<T>(v.e[k * (N / R) + i]) * scale);
+                ptx::multimem_st_v4(mdst + (g * R + k) * 16, o.raw);
+            }
+        }
+    }
+    block_barrier(x);
+}
+
+// ------------------------------------------------------------------------------------------------
+// all-gather (push): row i of this rank goes to every member's dst at
+//     dst + i*dst_row_stride + rank*row_bytes.
+// rows = 1 is MPI_Allgather; rows > 1 is the last-axis gather of func_impl.py:89-90 without the
+// np.concatenate copy. W = access width in bytes (16 when everything is 16-byte aligned).
+// ------------------------------------------------------------------------------------------------
+template <int W> struct Word;
+template <> struct Word<16> { using type = uint4; };
+template <> struct Word<8> { using type = uint2; };
+template <> struct Word<4> { using type = uint32_t; };
+template <> struct Word<2> { using type = uint16_t; };
+template <> struct Word<1> { using type = uint8_t; };
+
+template <int W, bool MC>
+__global__ void __launch_bounds__(THREADS)
+allgather_kernel(const __grid_constant__ Launch lp, size_t src_off, size_t dst_off, size_t rows, size_t row_bytes,
+                 size_t src_row_stride, size_t dst_row_stride) {
+    using WT = typename Word<W>::type;
+    Ctx x = make_ctx(lp);
+    const ccmpi_dev_comm& c = *x.c;
+    const size_t wpr = row_bytes / W;  // words per row
+    const size_t total = rows * wpr;
+    block_barrier(x);  // every member's dst is free to be overwritten
+    const uint8_t* src = c.heap[c.rank] + src_off;
+    const size_t col0 = (size_t)c.rank * row_bytes;
+    for (size_t i = (size_t)x.blk * THREADS + threadIdx.x; i < total; i += (size_t)x.nblk * THREADS) {
+        const size_t row = i / wpr, w = i - row * wpr;
+        const WT v = *reinterpret_cast<const WT*>(src + row * src_row_stride + w * W);
+        const size_t d = dst_off + row * dst_row_stride + col0 + w * W;
+        if constexpr (MC && W == 16) {
+            ptx::multimem_st_v4(c.mc_heap + d, v);
+        } else {
+#pragma unroll
+            for (int s = 0; s < CCMPI_MAX_RANKS; ++s) {
+                if (s < c.size) {
+                    const int p = (c.rank + s) % c.size;
+                    *reinterpret_cast<WT*>(c.heap[p] + d) = v;
+                }
+            }
+        }
+    }
+    block_barrier(x);  // all pushes have landed everywhere
+}
+
+// ------------------------------------------------------------------------------------------------
+// reduce-scatter (pull): rank r reduces column block r of every row over all members.
+// rows = 1 is MPI_Reduce_scatter_block; rows > 1 is func_impl.py:182-186 (split on the last
+// axis, all-to-all, sum) in one pass and in the same rank order as np.sum(axis=0).
+// ------------------------------------------------------------------------------------------------
+template <typename T, int OP, bool VECTOR, bool MC>
+__global__ void __launch_bounds__(THREADS)
+reduce_scatter_kernel(const __grid_constant__ Launch lp, size_t src_off, size_t dst_off, size_t rows, size_t row_elems,
+                      size_t src_row_stride, size_t dst_row_stride) {
+    Ctx x = make_ctx(lp);
+    const ccmpi_dev_comm& c = *x.c;
+    using A = typename AccOf<T>::type;
+    block_barrier(x);
+    uint8_t* dst = c.heap[c.rank] + dst_off;
+    const size_t col0 = (size_t)c.rank * row_elems * sizeof(T);
+    if constexpr (VECTOR) {
+        constexpr int N = 16 / sizeof(T);
+        const size_t vpr = row_elems / N;
+        const size_t total = rows * vpr;
+        for (size_t i = (size_t)x.blk * THREADS + threadIdx.x; i < total; i += (size_t)x.nblk * THREADS) {
+            const size_t row = i / vpr, w = i - row * vpr;
+            const size_t s = src_off + row * src_row_stride + col0 + w * 16;
+            uint4 out;
+            if constexpr (MC) {
+                out = mc_ld_reduce<T>(c.mc_heap + s);
+            } else {
+                uint4 r[CCMPI_MAX_RANKS];
+#pragma unroll
+                for (int p = 0; p < CCMPI_MAX_RANKS; ++p)
+                    if (p < c.size) r[p] = ptx::ld_v4(c.heap[p] + s);
+                AccVec<T> acc;
+                acc.init(r[0]);
+#pragma unroll
+                for (int p = 1; p < CCMPI_MAX_RANKS; ++p)
+                    if (p < c.size) acc.template fold<OP>(r[p]);
+                out = acc.pack();
+            }
+            ptx::st_v4(dst + row * dst_row_stride + w * 16, out);
+        }
+    } else {
+        const size_t total = rows * row_elems;
+        for (size_t i = (size_t)x.blk * THREADS + threadIdx.x; i < total; i += (size_t)x.nblk * THREADS) {
+            const size_t row = i / row_elems, w = i - row * row_elems;
+            const size_t s = src_off + row * src_row_stride + col0 + w * sizeof(T);
+            A acc = to_acc<T>(*reinterpret_cast<const T*>(c.heap[0] + s));
+            for (int p = 1; p < c.size; ++p) acc = apply<OP, A>(acc, to_acc<T>(*reinterpret_cast<const T*>(c.heap[p] + s)));
+            *reinterpret_cast<T*>(dst + row * dst_row_stride + w * sizeof(T)) = from_acc<T, A>(acc);
+        }
+    }
+    block_barrier(x);  // nobody may overwrite src before every member has read it
+}
+
+// ------------------------------------------------------------------------------------------------
+// all-to-all (push): segment j of src lands in member j's dst at segment index `rank`. All
+// n-1 peer transfers are in flight from one kernel (what Isend/Irecv + Waitall buy myAlltoall,
+// comm.py:136-150) and land directly in dst (no receive buffers, comm.py:152-155). In
+// `staggered` mode a block walks peers in (rank+i)%n order like the Sendrecv loop of
+// myAlltoall2; otherwise work is interleaved over all peers at vector granularity.
+// ------------------------------------------------------------------------------------------------
+template <int W>
+__global__ void __launch_bounds__(THREADS)
+alltoall_kernel(const __grid_constant__ Launch lp, size_t src_off, size_t dst_off, size_t seg_bytes, int staggered) {
+    using WT = typename Word<W>::type;
+    Ctx x = make_ctx(lp);
+    const ccmpi_dev_comm& c = *x.c;
+    const size_t wps = seg_bytes / W;
+    block_barrier(x);
+    const uint8_t* src = c.heap[c.rank] + src_off;
+    if (staggered) {
+        for (int s = 0; s < c.size; ++s) {
+            const int p = (c.rank + s) % c.size;
+            const WT* from = reinterpret_cast<const WT*>(src + (size_t)p * seg_bytes);
+            WT* to = reinterpret_cast<WT*>(c.heap[p] + dst_off + (size_t)c.rank * seg_bytes);
+            for (size_t i = (size_t)x.blk * THREADS + threadIdx.x; i < wps; i += (size_t)x.nblk * THREADS) to[i] = from[i];
+        }
+    } else {
+        const size_t total = wps * c.size;
+        for (size_t i = (size_t)x.blk * THREADS + threadIdx.x; i < total; i += (size_t)x.nblk * THREADS) {
+            const size_t w = i / c.size;
+            const int p = (int)((i - w * c.size + c.rank) % c.size);
+            reinterpret_cast<WT*>(c.heap[p] + dst_off + (size_t)c.rank * seg_bytes)[w] =
+                reinterpret_cast<const WT*>(src + (size_t)p * seg_bytes)[w];
+        }
+    }
+    block_barrier(x);
+}
+
+// ------------------------------------------------------------------------------------------------
+// point-to-point: put-with-signal into the peer's segment, and the matching wait. Backs the
+// Send/Recv/Isend/Irecv/Sendrecv surface of the mpi4py front end (comm.py:86,99,104-105,140,147,
+// 192). Flags are counters in the user area of the signal pad: the sender adds 1, the receiver
+// waits for its private expected count (kept in the word after the flag).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(THREADS)
+put_signal_kernel(const __grid_constant__ Launch lp, int peer, size_t src_off, size_t dst_off, size_t bytes, int flag) {
+    const ccmpi_dev_comm& c = lp.c[0];
+    const uint8_t* src = c.heap[c.rank] + src_off;
+    uint8_t* dst = c.heap[peer] + dst_off;
+    if (((src_off | dst_off | bytes) & 15) == 0) {
+        for (size_t i = threadIdx.x; i < bytes / 16; i += THREADS) ptx::st_v4(dst + i * 16, ptx::ld_v4(src + i * 16));
+    } else {
+        for (size_t i = threadIdx.x; i < bytes; i += THREADS) dst[i] = src[i];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) ptx::red_release_sys_add(c.pad[peer] + CCMPI_PAD_USER + flag, 1u);
+}
+
+__global__ void wait_signal_kernel(const __grid_constant__ Launch lp, int flag) {
+    const ccmpi_dev_comm& c = lp.c[0];
+    uint32_t* f = c.pad[c.rank] + CCMPI_PAD_USER + flag;
+    const uint32_t want = *reinterpret_cast<volatile uint32_t*>(f + 1) + 1;
+    ptx::wait_flag_ge_sys(f, want, flag);
+    *reinterpret_cast<volatile uint32_t*>(f + 1) = want;
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+static int fill_launch(Launch& lp, const ccmpi_dev_comm* comms, int nvr) {
+    CCMPI_REQUIRE(comms != nullptr && nvr >= 1 && nvr <= CCMPI_MAX_VRANKS, "nvr=%d out of range", nvr);
+    memset(&lp, 0, sizeof(lp));
+    lp.nvr = nvr;
+    for (int i = 0; i < nvr; ++i) {
+        lp.c[i] = comms[i];
+        CCMPI_REQUIRE(comms[i].size >= 1 && comms[i].size <= CCMPI_MAX_RANKS, "communicator size %d out of range",
+                      comms[i].size);
+        CCMPI_REQUIRE(comms[i].size == comms[0].size, "emulated ranks disagree on communicator size");
+    }
+    return CCMPI_OK;
+}
+
+static int clamp_blocks(size_t work_items, int max_blocks) {
+    int cap = max_blocks > 0 ? max_blocks : 64;
+    if (cap > CCMPI_MAX_BLOCKS) cap = CCMPI_MAX_BLOCKS;
+    size_t want = (work_items + THREADS - 1) / THREADS;
+    // a few vectors per thread before adding blocks: these kernels are latency-, then link-bound
+    want = (want + 3) / 4;
+    if (want < 1) want = 1;
+    return (int)(want < (size_t)cap ? want : (size_t)cap);
+}
+
+template <typename... Args>
+static int launch(void (*kern)(Args...), int nvr, int blocks, cudaStream_t stream, Args... args) {
+    void* ptrs[] = {(void*)&args...};
+    if (nvr > 1) {
+        // emulated ranks spin on one another: co-residency must be guaranteed
+        CCMPI_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)kern, dim3(blocks * nvr), dim3(THREADS), ptrs, 0, stream));
+    } else {
+        CCMPI_CUDA_CHECK(cudaLaunchKernel((const void*)kern, dim3(blocks), dim3(THREADS), ptrs, 0, stream));
+    }
+    return CCMPI_OK;
+}
+
+static int max_align(size_t v) {
+    for (int a = 16; a > 1; a >>= 1)
+        if ((v & (size_t)(a - 1)) == 0) return a;
+    return 1;
+}
+
+}  // namespace coll
+
+using namespace coll;
+
+extern "C" int ccmpi_barrier(const ccmpi_dev_comm* comms, int nvr, void* stream) {
+    Launch lp;
+    int rc = fill_launch(lp, comms, nvr);
+    if (rc) return rc;
+    return launch(barrier_kernel, nvr, 1, (cudaStream_t)stream, lp);
+}
+
+namespace coll {
+
+template <typename T, int OP>
+static int allreduce_typed(const Launch& lp, int nvr, int algo, size_t src_off, size_t dst_off, size_t tmp_off,
+                           size_t count, float scale, int out_dtype, int dtype, int max_blocks, cudaStream_t st) {
+    constexpr int N = 16 / sizeof(T);
+    const bool aligned = ((src_off | dst_off | tmp_off) & 15) == 0;
+    const int n = lp.c[0].size;
+    constexpr bool is_float = std::is_same<T, float>::value || std::is_same<T, __nv_bfloat16>::value || std::is_same<T, __half>::value;
+    const bool cast = out_dtype != dtype;
+    CCMPI_REQUIRE(!cast || is_float, "all-reduce output cast is only defined for fp32/bf16/fp16");
+    if (algo == CCMPI_AR_NVLS) {
+        if constexpr (is_float && OP == CCMPI_SUM) {
+            CCMPI_REQUIRE(lp.c[0].mc_heap != nullptr, "NVLS all-reduce needs a multicast mapping");
+            CCMPI_REQUIRE(aligned && count % (N * 2) == 0, "NVLS all-reduce needs 16-byte aligned offsets and count %% %d == 0", N * 2);
+            const int blocks = clamp_blocks(count / N / n, max_blocks);
+            if (!cast) return launch(allreduce_nvls_kernel<T, T>, nvr, blocks, st, lp, src_off, dst_off, count, scale);
+            if constexpr (std::is_same<T, float>::value) {
+                if (out_dtype == CCMPI_BF16) return launch(allreduce_nvls_kernel<float, __nv_bfloat16>, nvr, blocks, st, lp, src_off, dst_off, count, scale);
+            }
+            if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+                if (out_dtype == CCMPI_F32) return launch(allreduce_nvls_kernel<__nv_bfloat16, float>, nvr, blocks, st, lp, src_off, dst_off, count, scale);
+            }
+            ccmpi::set_error("NVLS all-reduce: unsupported cast %d -> %d", dtype, out_dtype);
+            return CCMPI_ERR_UNSUPPORTED;
+        } else {
+            ccmpi::set_error("NVLS all-reduce supports SUM over fp32/bf16/fp16 only");
+            return CCMPI_ERR_UNSUPPORTED;
+        }
+    }
+    if (algo == CCMPI_AR_TWOSHOT) {
+        CCMPI_REQUIRE(aligned && count % N == 0, "two-shot all-reduce needs 16-byte aligned offsets and whole vectors");
+        const int blocks = clamp_blocks(count / N / n, max_blocks);
+        if (!cast) return launch(allreduce_twoshot_kernel<T, OP, T>, nvr, blocks, st, lp, src_off, dst_off, tmp_off, count, scale);
+        if constexpr (std::is_same<T, float>::value) {
+            if (out_dtype == CCMPI_BF16) return launch(allreduce_twoshot_kernel<float, OP, __nv_bfloat16>, nvr, blocks, st, lp, src_off, dst_off, tmp_off, count, scale);
+        }
+        if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+            if (out_dtype == CCMPI_F32) return launch(allreduce_twoshot_kernel<__nv_bfloat16, OP, float>, nvr, blocks, st, lp, src_off, dst_off, tmp_off, count, scale);
+        }
+        ccmpi::set_error("two-shot all-reduce: unsupported cast %d -> %d", dtype, out_dtype);
+        return CCMPI_ERR_UNSUPPORTED;
+    }
+    // one-shot
+    const bool vec = aligned && count % N == 0;
+    const int blocks = clamp_blocks(vec ? count / N : count, max_blocks);
+    if (!cast) {
+        if (vec) return launch(allreduce_oneshot_kernel<T, OP, T, true>, nvr, blocks, st, lp, src_off, dst_off, count, scale);
+        return launch(allreduce_oneshot_kernel<T, OP, T, false>, nvr, blocks, st, lp, src_off, dst_off, count, scale);
+    }
+    if constexpr (std::is_same<T, float>::value) {
+        if (out_dtype == CCMPI_BF16) {
+            if (vec) return launch(allreduce_oneshot_kernel<float, OP, __nv_bfloat16, true>, nvr, blocks, st, lp, src_off, dst_off, count, scale);
+            return launch(allreduce_oneshot_kernel<float, OP, __nv_bfloat16, false>, nvr, blocks, st, lp, src_off, dst_off, count, scale);
+        }
+    }
+    if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+        if (out_dtype == CCMPI_F32) {
+            if (vec) return launch(allreduce_oneshot_kernel<__nv_bfloat16, OP, float, true>, nvr, blocks, st, lp, src_off, dst_off, count, scale);
+            return launch(allreduce_oneshot_kernel<__nv_bfloat16, OP, float, false>, nvr, blocks, st, lp, src_off, dst_off, count, scale);
+        }
+    }
+    ccmpi::set_error("one-shot all-reduce: unsupported cast %d -> %d", dtype, out_dtype);
+    return CCMPI_ERR_UNSUPPORTED;
+}
+
+template <typename T>
+static int allreduce_op(const Launch& lp, int nvr, int algo, int op, size_t src_off, size_t dst_off, size_t tmp_off,
+                        size_t count, float scale, int out_dtype, int dtype, int max_blocks, cudaStream_t st) {
+    switch (op) {
+        case CCMPI_SUM: return allreduce_typed<T, CCMPI_SUM>(lp, nvr, algo, src_off, dst_off, tmp_off, count, scale, out_dtype, dtype, max_blocks, st);
+        case CCMPI_MIN: return allreduce_typed<T, CCMPI_MIN>(lp, nvr, algo, src_off, dst_off, tmp_off, count, scale, out_dtype, dtype, max_blocks, st);
+        case CCMPI_MAX: return allreduce_typed<T, CCMPI_MAX>(lp, nvr, algo, src_off, dst_off, tmp_off, count, scale, out_dtype, dtype, max_blocks, st);
+    }
+    // mirrors the NotImplementedError of comm.py:94-95, but raised on every rank before any
+    // communication so nobody is left waiting
+    ccmpi::set_error("reduce op %d is not supported (SUM, MIN, MAX only)", op);
+    return CCMPI_ERR_UNSUPPORTED;
+}
+
+}  // namespace coll
+
+extern "C" int ccmpi_allreduce(const ccmpi_dev_comm* comms, int nvr, int algo, int dtype, int op, size_t src_off,
+                               size_t dst_off, size_t tmp_off, size_t count, float scale, int out_dtype, int max_blocks,
+                               void* stream) {
+    Launch lp;
+    int rc = fill_launch(lp, comms, nvr);
+    if (rc) return rc;
+    if (count == 0) return CCMPI_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (out_dtype < 0) out_dtype = dtype;
+    if (algo == CCMPI_AR_AUTO) {
+        static const size_t esz[] = {4, 2, 2, 8, 4, 8, 1};
+        const size_t bytes = count * esz[dtype];
+        const bool nvls_ok = lp.c[0].mc_heap && op == CCMPI_SUM && (dtype == CCMPI_F32 || dtype == CCMPI_BF16 || dtype == CCMPI_F16) &&
+                             ((src_off | dst_off) & 15) == 0 && (bytes % 32) == 0;
+        const bool vec_ok = ((src_off | dst_off | tmp_off) & 15) == 0 && bytes % 16 == 0;
+        if (bytes <= 256 * 1024 || !vec_ok) algo = CCMPI_AR_ONESHOT;
+        else algo = nvls_ok ? CCMPI_AR_NVLS : CCMPI_AR_TWOSHOT;
+    }
+    switch (dtype) {
+        case CCMPI_F32: return allreduce_op<float>(lp, nvr, algo, op, src_off, dst_off, tmp_off, count, scale, out_dtype, dtype, max_blocks, st);
+        case CCMPI_BF16: return allreduce_op<__nv_bfloat16>(lp, nvr, algo, op, src_off, dst_off, tmp_off, count, scale, out_dtype, dtype, max_blocks, st);
+        case CCMPI_F16: return allreduce_op<__half>(lp, nvr, algo, op, src_off, dst_off, tmp_off, count, scale, out_dtype, dtype, max_blocks, st);
+        case CCMPI_F64: return allreduce_op<double>(lp, nvr, algo, op, src_off, dst_off, tmp_off, count, scale, out_dtype, dtype, max_blocks, st);
+        case CCMPI_I32: return allreduce_op<int32_t>(lp, nvr, algo, op, src_off, dst_off, tmp_off, count, scale, out_dtype, dtype, max_blocks, st);
+        case CCMPI_I64: return allreduce_op<long long>(lp, nvr, algo, op, src_off, dst_off, tmp_off, count, scale, out_dtype, dtype, max_blocks, st);
+    }
+    ccmpi::set_error("all-reduce: unsupported dtype %d", dtype);
+    return CCMPI_ERR_UNSUPPORTED;
+}
+
+extern "C" int ccmpi_allgather(const ccmpi_dev_comm* comms, int nvr, size_t src_off, size_t dst_off, size_t rows,
+                               size_t row_bytes, size_t src_row_stride, size_t dst_row_stride, int use_mc,
+                               int max_blocks, void* stream) {
+    Launch lp;
+    int rc = fill_launch(lp, comms, nvr);
+    if (rc) return rc;
+    if (rows == 0 || row_bytes == 0) return CCMPI_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int W = max_align(src_off | dst_off | row_bytes | (rows > 1 ? (src_row_stride | dst_row_stride) : 0));
+    const int blocks = clamp_blocks(rows * (row_bytes / W), max_blocks);
+    const bool mc = use_mc && lp.c[0].mc_heap != nullptr && W == 16;
+    switch (W) {
+        case 16:
+            if (mc) return launch(allgather_kernel<16, true>, nvr, blocks, st, lp, src_off, dst_off, rows, row_bytes, src_row_stride, dst_row_stride);
+            return launch(allgather_kernel<16, false>, nvr, blocks, st, lp, src_off, dst_off, rows, row_bytes, src_row_stride, dst_row_stride);
+        case 8: return launch(allgather_kernel<8, false>, nvr, blocks, st, lp, src_off, dst_off, rows, row_bytes, src_row_stride, dst_row_stride);
+        case 4: return launch(allgather_kernel<4, false>, nvr, blocks, st, lp, src_off, dst_off, rows, row_bytes, src_row_stride, dst_row_stride);
+        case 2: return launch(allgather_kernel<2, false>, nvr, blocks, st, lp, src_off, dst_off, rows, row_bytes, src_row_stride, dst_row_stride);
+        default: return launch(allgather_kernel<1, false>, nvr, blocks, st, lp, src_off, dst_off, rows, row_bytes, src_row_stride, dst_row_stride);
+    }
+}
+
+namespace coll {
+template <typename T, int OP>
+static int rs_typed(const Launch& lp, int nvr, size_t src_off, size_t dst_off, size_t rows, size_t row_elems,
+                    size_t sstride, size_t dstride, int use_mc, int max_blocks, cudaStream_t st) {
+    constexpr int N = 16 / sizeof(T);
+    const size_t row_bytes = row_elems * sizeof(T);
+    const bool vec = ((src_off | dst_off | row_bytes | (rows > 1 ? (sstride | dstride) : 0)) & 15) == 0;
+    const int blocks = clamp_blocks(vec ? rows * (row_elems / N) : rows * row_elems, max_blocks);
+    constexpr bool mc_type = (std::is_same<T, float>::value || std::is_same<T, __nv_bfloat16>::value || std::is_same<T, __half>::value) && OP == CCMPI_SUM;
+    if constexpr (mc_type) {
+        if (vec && use_mc && lp.c[0].mc_heap)
+            return launch(reduce_scatter_kernel<T, OP, true, true>, nvr, blocks, st, lp, src_off, dst_off, rows, row_elems, sstride, dstride);
+    }
+    if (vec) return launch(reduce_scatter_kernel<T, OP, true, false>, nvr, blocks, st, lp, src_off, dst_off, rows, row_elems, sstride, dstride);
+    return launch(reduce_scatter_kernel<T, OP, false, false>, nvr, blocks, st, lp, src_off, dst_off, rows, row_elems, sstride, dstride);
+}
+template <typename T>
+static int rs_op(const Launch& lp, int nvr, int op, size_t src_off, size_t dst_off, size_t rows, size_t row_elems,
+                 size_t sstride, size_t dstride, int use_mc, int max_blocks, cudaStream_t st) {
+    switch (op) {
+        case CCMPI_SUM: return rs_typed<T, CCMPI_SUM>(lp, nvr, src_off, dst_off, rows, row_elems, sstride, dstride, use_mc, max_blocks, st);
+        case CCMPI_MIN: return rs_typed<T, CCMPI_MIN>(lp, nvr, src_off, dst_off, rows, row_elems, sstride, dstride, use_mc, max_blocks, st);
+        case CCMPI_MAX: return rs_typed<T, CCMPI_MAX>(lp, nvr, src_off, dst_off, rows, row_elems, sstride, dstride, use_mc, max_blocks, st);
+    }
+    ccmpi::set_error("reduce op %d is not supported (SUM, MIN, MAX only)", op);
+    return CCMPI_ERR_UNSUPPORTED;
+}
+}  // namespace coll
+
+extern "C" int ccmpi_reduce_scatter(const ccmpi_dev_comm* comms, int nvr, int dtype, int op, size_t src_off,
+                                    size_t dst_off, size_t rows, size_t row_elems, size_t src_row_stride,
+                                    size_t dst_row_stride, int use_mc, int max_blocks, void* stream) {
+    Launch lp;
+    int rc = fill_launch(lp, comms, nvr);
+    if (rc) return rc;
+    if (rows == 0 || row_elems == 0) return CCMPI_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (dtype) {
+        case CCMPI_F32: return rs_op<float>(lp, nvr, op, src_off, dst_off, rows, row_elems, src_row_stride, dst_row_stride, use_mc, max_blocks, st);
+        case CCMPI_BF16: return rs_op<__nv_bfloat16>(lp, nvr, op, src_off, dst_off, rows, row_elems, src_row_stride, dst_row_stride, use_mc, max_blocks, st);
+        case CCMPI_F16: return rs_op<__half>(lp, nvr, op, src_off, dst_off, rows, row_elems, src_row_stride, dst_row_stride, use_mc, max_blocks, st);
+        case CCMPI_F64: return rs_op<double>(lp, nvr, op, src_off, dst_off, rows, row_elems, src_row_stride, dst_row_stride, use_mc, max_blocks, st);
+        case CCMPI_I32: return rs_op<int32_t>(lp, nvr, op, src_off, dst_off, rows, row_elems, src_row_stride, dst_row_stride, use_mc, max_blocks, st);
+        case CCMPI_I64: return rs_op<long long>(lp, nvr, op, src_off, dst_off, rows, row_elems, src_row_stride, dst_row_stride, use_mc, max_blocks, st);
+    }
+    ccmpi::set_error("reduce-scatter: unsupported dtype %d", dtype);
+    return CCMPI_ERR_UNSUPPORTED;
+}
+
+extern "C" int ccmpi_alltoall(const ccmpi_dev_comm* comms, int nvr, size_t src_off, size_t dst_off, size_t seg_bytes,
+                              int staggered, int max_blocks, void* stream) {
+    Launch lp;
+    int rc = fill_launch(lp, comms, nvr);
+    if (rc) return rc;
+    if (seg_bytes == 0) return CCMPI_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int W = max_align(src_off | dst_off | seg_bytes);
+    const int blocks = clamp_blocks((seg_bytes / W) * lp.c[0].size, max_blocks);
+    switch (W) {
+        case 16: return launch(alltoall_kernel<16>, nvr, blocks, st, lp, src_off, dst_off, seg_bytes, staggered);
+        case 8: return launch(alltoall_kernel<8>, nvr, blocks, st, lp, src_off, dst_off, seg_bytes, staggered);
+        case 4: return launch(alltoall_kernel<4>, nvr, blocks, st, lp, src_off, dst_off, seg_bytes, staggered);
+        case 2: return launch(alltoall_kernel<2>, nvr, blocks, st, lp, src_off, dst_off, seg_bytes, staggered);
+        default: return launch(alltoall_kernel<1>, nvr, blocks, st, lp, src_off, dst_off, seg_bytes, staggered);
+    }
+}
+
+extern "C" int ccmpi_put_signal(const ccmpi_dev_comm* comms, int nvr, int peer, size_t src_off, size_t dst_off,
+                                size_t bytes, int flag_index, void* stream) {
+    Launch lp;
+    int rc = fill_launch(lp, comms, 1);
+    if (rc) return rc;
+    CCMPI_REQUIRE(peer >= 0 && peer < lp.c[0].size, "put: peer %d out of range", peer);
+    CCMPI_REQUIRE(flag_index >= 0 && flag_index + 1 < CCMPI_PAD_USER_WORDS, "put: flag %d out of range", flag_index);
+    return launch(put_signal_kernel, 1, 1, (cudaStream_t)stream, lp, peer, src_off, dst_off, bytes, flag_index);
+}
+
+extern "C" int ccmpi_wait_signal(const ccmpi_dev_comm* comms, int nvr, int peer, int flag_index, void* stream) {
+    Launch lp;
+    int rc = fill_launch(lp, comms, 1);
+    if (rc) return rc;
+    CCMPI_REQUIRE(flag_index >= 0 && flag_index + 1 < CCMPI_PAD_USER_WORDS, "wait: flag %d out of range", flag_index);
+    void* ptrs[] = {(void*)&lp, (void*)&flag_index};
+    CCMPI_CUDA_CHECK(cudaLaunchKernel((const void*)wait_signal_kernel, dim3(1), dim3(1), ptrs, 0, (cudaStream_t)stream));
+    return CCMPI_OK;
+}

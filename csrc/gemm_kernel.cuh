@@ -1,0 +1,232 @@
+// The persistent tcgen05 GEMM kernel body, parameterised by a Policy (see gemm_tcgen05.cuh).
+#pragma once
+#include "gemm_tcgen05.cuh"
+
+namespace gemm {
+
+// ------------------------------------------------------------------------------------------------
+// Output conversion helpers: 32 fp32 accumulator values of one row -> global memory
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t pack_bf16(uint32_t lo_bits, uint32_t hi_bits) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(lo_bits), __uint_as_float(hi_bits));
+    return *reinterpret_cast<uint32_t*>(&h);
+}
+
+// Store up to 32 columns of one row. `ncols` (multiple of 8 for bf16, 4 for fp32) handles the
+// right edge. dst points at (row, col0).
+template <typename OutT>
+__device__ __forceinline__ void store_row32(OutT* dst, const uint32_t (&v)[32], int ncols, bool accumulate) {
+    if constexpr (sizeof(OutT) == 2) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            if (j * 8 < ncols) {
+                uint4 q;
+                q.x = pack_bf16(v[8 * j + 0], v[8 * j + 1]);
+                q.y = pack_bf16(v[8 * j + 2], v[8 * j + 3]);
+                q.z = pack_bf16(v[8 * j + 4], v[8 * j + 5]);
+                q.w = pack_bf16(v[8 * j + 6], v[8 * j + 7]);
+                ptx::st_v4(dst + 8 * j, q);
+            }
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            if (j * 4 < ncols) {
+                uint4 q = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                if (accumulate) {
+                    const uint4 o = ptx::ld_v4(dst + 4 * j);
+                    q.x = __float_as_uint(__uint_as_float(q.x) + __uint_as_float(o.x));
+                    q.y = __float_as_uint(__uint_as_float(q.y) + __uint_as_float(o.y));
+                    q.z = __float_as_uint(__uint_as_float(q.z) + __uint_as_float(o.z));
+                    q.w = __float_as_uint(__uint_as_float(q.w) + __uint_as_float(o.w));
+                }
+                ptx::st_v4(dst + 4 * j, q);
+            }
+        }
+    }
+}
+
+// 128 epilogue threads only (named barrier 1); never stalls the producer / MMA warps.
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+// ------------------------------------------------------------------------------------------------
+// Plain policy: C = A*B, row-major C, grouped raster, no communication.
+// ------------------------------------------------------------------------------------------------
+struct PlainPolicy {
+    static constexpr bool kCommCtas = false;
+
+    struct State {};
+
+    __device__ static int num_tiles(const RankParams& p, int mb, int nb) { return mb * nb; }
+    __device__ static TileCoord tile(const RankParams& p, int t, int mb, int nb) { return raster(t, mb, nb); }
+    // producer: K-block `it` of tile `tc` -> coordinates + operand source
+    __device__ static void kblock(const RankParams& p, const TileCoord& tc, int it, int& k0, const CUtensorMap*& ta,
+                                  int& a_k0, int& a_m0) {
+        k0 = it * BK;
+        ta = &p.tmap_a;
+        a_k0 = k0;
+        a_m0 = tc.m_blk * BM;
+    }
+    template <typename OutT>
+    __device__ static void store(const RankParams& p, const TileCoord& tc, int row, int col0, const uint32_t (&v)[32]) {
+        if (row < p.M) {
+            const int ncols = min(32, p.N - col0);
+            if (ncols > 0)
+                store_row32<OutT>(reinterpret_cast<OutT*>(p.C) + (long long)row * p.ldc + col0, v, ncols,
+                                  p.accumulate != 0);
+        }
+    }
+    // called by all 128 epilogue threads after every tile
+    __device__ static void tile_done(const RankParams& p, const TileCoord& tc, int epi_tid) {}
+    // called by all epilogue threads once the CTA has no more tiles
+    template <typename OutT>
+    __device__ static void tail(const RankParams& p, int cta, int nctas, int epi_tid) {}
+    // body of a communication CTA (only if kCommCtas)
+    __device__ static void comm_cta(const RankParams& p, int comm_cta, int ncomm) {}
+};
+
+// ------------------------------------------------------------------------------------------------
+// The kernel
+// ------------------------------------------------------------------------------------------------
+template <int BN, bool A_MN, bool B_MN, typename OutT, typename Policy>
+__global__ void __launch_bounds__(NUM_THREADS, 1) gemm_kernel(const __grid_constant__ Launch lp) {
+    using C = Cfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    Smem<BN> sm(smem_raw);
+
+    // virtual-rank decomposition (nvr == 1 in production)
+    const int nvr = lp.nvr;
+    const int vr = blockIdx.x % nvr;
+    const int cta = blockIdx.x / nvr;
+    const int nctas_all = gridDim.x / nvr;
+    const RankParams& p = lp.r[vr];
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if constexpr (Policy::kCommCtas) {
+        // trailing CTAs of each rank move data; they never touch TMEM / mbarriers
+        const int ncomm = p.num_comm_ctas;
+        if (cta >= nctas_all - ncomm) {
+            Policy::comm_cta(p, cta - (nctas_all - ncomm), ncomm);
+            return;
+        }
+    }
+    const int nctas = nctas_all - (Policy::kCommCtas ? p.num_comm_ctas : 0);
+
+    const int m_blocks = (p.M + BM - 1) / BM;
+    const int n_blocks = (p.N + BN - 1) / BN;
+    const int k_blocks = (p.K + BK - 1) / BK;
+    const int ntiles = Policy::num_tiles(p, m_blocks, n_blocks);
+
+    // ---- one-time setup ----
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tmap(&p.tmap_a);
+        ptx::prefetch_tmap(&p.tmap_a2);
+        ptx::prefetch_tmap(&p.tmap_b);
+#pragma unroll
+        for (int s = 0; s < C::STAGES; ++s) {
+            ptx::mbar_init(&sm.full[s], 1);
+            ptx::mbar_init(&sm.empty[s], 1);
+        }
+        ptx::mbar_init(&sm.tmem_full[0], 1);
+        ptx::mbar_init(&sm.tmem_full[1], 1);
+        ptx::mbar_init(&sm.tmem_empty[0], 4);  // one arrival per epilogue warp
+        ptx::mbar_init(&sm.tmem_empty[1], 4);
+        ptx::fence_mbar_init();
+    }
+    if (warp == 1) ptx::tmem_alloc<C::TMEM_COLS>(sm.tmem_base);
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *sm.tmem_base;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int t = cta; t < ntiles; t += nctas) {
+                const TileCoord tc = Policy::tile(p, t, m_blocks, n_blocks);
+                for (int it = 0; it < k_blocks; ++it) {
+                    int k0, a_k0, a_m0;
+                    const CUtensorMap* ta;
+                    Policy::kblock(p, tc, it, k0, ta, a_k0, a_m0);  // may wait on gather flags
+                    ptx::mbar_wait(&sm.empty[stage], phase ^ 1, 100 + stage);
+                    ptx::mbar_arrive_expect_tx(&sm.full[stage], C::STAGE_BYTES);
+                    load_operand<A_MN, BM>(sm.a(stage), ta, &sm.full[stage], a_k0, a_m0);
+                    load_operand<B_MN, BN>(sm.b(stage), &p.tmap_b, &sm.full[stage], k0, tc.n_blk * BN);
+                    if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            constexpr uint32_t idesc = ptx::umma_idesc(1, 1, A_MN, B_MN, BM, BN);
+            int stage = 0;
+            uint32_t phase = 0;
+            int local = 0;
+            for (int t = cta; t < ntiles; t += nctas, ++local) {
+                const int acc = local & 1;
+                const uint32_t acc_phase = (local >> 1) & 1;
+                ptx::mbar_wait(&sm.tmem_empty[acc], acc_phase ^ 1, 200 + acc);
+                ptx::tc_fence_after();
+                const uint32_t tmem_d = tmem_base + acc * BN;
+                for (int it = 0; it < k_blocks; ++it) {
+                    ptx::mbar_wait(&sm.full[stage], phase, 300 + stage);
+                    ptx::tc_fence_after();
+                    const uint32_t a_addr = ptx::smem_u32(sm.a(stage));
+                    const uint32_t b_addr = ptx::smem_u32(sm.b(stage));
+#pragma unroll
+                    for (int ks = 0; ks < BK / UMMA_K; ++ks) {
+                        ptx::umma_f16_ss(tmem_d, operand_desc<A_MN>(a_addr, ks), operand_desc<B_MN>(b_addr, ks), idesc,
+                                         (it | ks) != 0 ? 1u : 0u);
+                    }
+                    ptx::umma_commit(&sm.empty[stage]);  // smem slot reusable once these MMAs retire
+                    if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                }
+                ptx::umma_commit(&sm.tmem_full[acc]);    // accumulator complete -> epilogue
+            }
+        }
+    } else {
+        // ===================== epilogue warps =====================
+        const int q = warp & 3;                  // TMEM lane quarter this warp may access
+        const int epi_tid = (warp - EPI_WARP0) * 32 + lane;
+        int local = 0;
+        for (int t = cta; t < ntiles; t += nctas, ++local) {
+            const TileCoord tc = Policy::tile(p, t, m_blocks, n_blocks);
+            const int acc = local & 1;
+            const uint32_t acc_phase = (local >> 1) & 1;
+            ptx::mbar_wait(&sm.tmem_full[acc], acc_phase, 400 + acc);
+            ptx::tc_fence_after();
+            const int row = tc.m_blk * BM + q * 32 + lane;
+            const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + acc * BN;
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                uint32_t v[32];
+                ptx::tmem_ld_32x32b_x32(taddr + c, v);
+                ptx::tmem_ld_wait();
+                if (c + 32 >= BN) {
+                    // all TMEM reads of this accumulator stage are done: hand it back early
+                    ptx::tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) ptx::mbar_arrive(&sm.tmem_empty[acc]);
+                }
+                Policy::template store<OutT>(p, tc, row, tc.n_blk * BN + c, v);
+            }
+            Policy::tile_done(p, tc, epi_tid);
+        }
+        Policy::template tail<OutT>(p, cta, nctas, epi_tid);
+    }
+
+    // ---- teardown ----
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc<C::TMEM_COLS>(tmem_base);
+    }
+}
+
+}  // namespace gemm

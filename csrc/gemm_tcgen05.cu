@@ -1,0 +1,121 @@
+// Plain bf16 GEMM entry point on the tcgen05 mainloop. The reference ships no GEMM at all
+// (README.md:173-175 says the FC compute is "taken care of" elsewhere); these are the three
+// products a tensor-parallel FC layer needs around func_impl.py:76-187:
+//     y = x W        (A K-major,  B stored [K][N] -> b_mn_major)
+//     dx = dy W^T    (A K-major,  B stored [N][K] -> K-major)
+//     dW = x^T dy    (A stored [K][M] -> a_mn_major, B stored [K][N] -> b_mn_major)
+#include "gemm_kernel.cuh"
+#include "host_common.h"
+
+namespace gemm {
+
+// Fill the three TMA descriptors of a rank. A2 (alternate A source) defaults to A.
+int fill_tmaps(RankParams& rp, const void* A, const void* A2, const void* B, int M, int N, int K, long long lda,
+               long long lda2, long long ldb, bool a_mn, bool b_mn, int BN, int a2_rows, int a2_cols) {
+    int rc;
+    if (!a_mn) {
+        rc = ccmpi::make_tmap_2d(&rp.tmap_a, A, 2, M, K, lda, BM, BK);
+        if (rc) return rc;
+        rc = ccmpi::make_tmap_2d(&rp.tmap_a2, A2, 2, a2_rows, a2_cols, lda2, BM, BK);
+    } else {
+        rc = ccmpi::make_tmap_2d(&rp.tmap_a, A, 2, K, M, lda, BK, 64);
+        if (rc) return rc;
+        rc = ccmpi::make_tmap_2d(&rp.tmap_a2, A2, 2, a2_rows, a2_cols, lda2, BK, 64);
+    }
+    if (rc) return rc;
+    if (!b_mn)
+        rc = ccmpi::make_tmap_2d(&rp.tmap_b, B, 2, N, K, ldb, BN, BK);
+    else
+        rc = ccmpi::make_tmap_2d(&rp.tmap_b, B, 2, K, N, ldb, BK, 64);
+    return rc;
+}
+
+template <int BN, bool A_MN, bool B_MN, typename OutT, typename Policy>
+int launch(const Launch& lp, int grid, cudaStream_t stream, bool cooperative) {
+    auto kern = gemm_kernel<BN, A_MN, B_MN, OutT, Policy>;
+    static bool configured = false;  // per instantiation
+    if (!configured) {
+        CCMPI_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM_BYTES));
+        configured = true;
+    }
+    if (!cooperative) {
+        kern<<<grid, NUM_THREADS, Cfg<BN>::SMEM_BYTES, stream>>>(lp);
+    } else {
+        // CTAs of different (virtual) ranks wait on one another: co-residency must be guaranteed
+        void* args[] = {const_cast<Launch*>(&lp)};
+        CCMPI_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)kern, dim3(grid), dim3(NUM_THREADS), args,
+                                                     Cfg<BN>::SMEM_BYTES, stream));
+    }
+    CCMPI_CUDA_CHECK(cudaGetLastError());
+    return CCMPI_OK;
+}
+
+template <typename Policy>
+int dispatch(const Launch& lp, int BN, bool a_mn, bool b_mn, int out_dtype, int grid, cudaStream_t stream,
+             bool cooperative) {
+#define CCMPI_GEMM_CASE(bn, amn, bmn)                                                                   \
+    if (BN == bn && a_mn == amn && b_mn == bmn) {                                                       \
+        if (out_dtype == CCMPI_BF16) return launch<bn, amn, bmn, __nv_bfloat16, Policy>(lp, grid, stream, cooperative); \
+        return launch<bn, amn, bmn, float, Policy>(lp, grid, stream, cooperative);                     \
+    }
+    CCMPI_GEMM_CASE(256, false, false)
+    CCMPI_GEMM_CASE(256, false, true)
+    CCMPI_GEMM_CASE(256, true, false)
+    CCMPI_GEMM_CASE(256, true, true)
+    CCMPI_GEMM_CASE(128, false, false)
+    CCMPI_GEMM_CASE(128, false, true)
+    CCMPI_GEMM_CASE(128, true, false)
+    CCMPI_GEMM_CASE(128, true, true)
+#undef CCMPI_GEMM_CASE
+    ccmpi::set_error("no GEMM instantiation for BN=%d", BN);
+    return CCMPI_ERR_UNSUPPORTED;
+}
+
+int pick_bn(int M, int N, int sms) {
+    auto eff = [&](int bn) {
+        const long long tiles = (long long)((M + BM - 1) / BM) * ((N + bn - 1) / bn);
+        const long long waves = (tiles + sms - 1) / sms;
+        // useful fraction of issued tile slots, discounted by edge waste in N
+        const double edge = (double)N / (double)(((N + bn - 1) / bn) * bn);
+        return edge * (double)tiles / (double)(waves * sms);
+    };
+    if (N <= 128) return 128;
+    return (eff(256) >= 0.92 * eff(128)) ? 256 : 128;
+}
+
+int check_shapes(int M, int N, int K, long long lda, long long ldb, long long ldc, int out_dtype) {
+    CCMPI_REQUIRE(M > 0 && N > 0 && K > 0, "GEMM extents must be positive (M=%d N=%d K=%d)", M, N, K);
+    CCMPI_REQUIRE(K % 8 == 0 && N % 8 == 0 && M % 8 == 0, "GEMM extents must be multiples of 8 (M=%d N=%d K=%d)", M, N, K);
+    CCMPI_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && ldc % 8 == 0, "GEMM leading dimensions must be multiples of 8");
+    CCMPI_REQUIRE(out_dtype == CCMPI_BF16 || out_dtype == CCMPI_F32, "GEMM output must be bf16 or fp32");
+    return CCMPI_OK;
+}
+
+}  // namespace gemm
+
+extern "C" int ccmpi_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                               int a_mn_major, int b_mn_major, int out_dtype, int accumulate, int num_sms,
+                               void* stream) {
+    using namespace gemm;
+    int rc = check_shapes(M, N, K, lda, ldb, ldc, out_dtype);
+    if (rc) return rc;
+    CCMPI_REQUIRE(!accumulate || out_dtype == CCMPI_F32, "accumulate needs an fp32 output");
+    const int sms = num_sms > 0 ? num_sms : ccmpi::device_sm_count();
+    const int BN = pick_bn(M, N, sms);
+    Launch lp;
+    memset(&lp, 0, sizeof(lp));
+    lp.nvr = 1;
+    RankParams& rp = lp.r[0];
+    rc = fill_tmaps(rp, A, A, B, M, N, K, lda, lda, ldb, a_mn_major != 0, b_mn_major != 0, BN,
+                    a_mn_major ? K : M, a_mn_major ? M : K);
+    if (rc) return rc;
+    rp.C = C;
+    rp.ldc = ldc;
+    rp.M = M;
+    rp.N = N;
+    rp.K = K;
+    rp.accumulate = accumulate;
+    const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
+    const int grid = tiles < sms ? tiles : sms;
+    return dispatch<PlainPolicy>(lp, BN, a_mn_major != 0, b_mn_major != 0, out_dtype, grid, (cudaStream_t)stream, false);
+}

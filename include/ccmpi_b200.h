@@ -1,0 +1,173 @@
+/*
+ * ccmpi_b200 -- C ABI of the native runtime and the sm_100a kernels.
+ *
+ * One shared library (libccmpi_b200.so) holds the device runtime (symmetric heap, peer mapping,
+ * NVLS multicast, signal pads, device-resident communicators) and every CUDA kernel; a second
+ * one (libccmpi_host.so, see ccmpi_host.h) is the CPU shared-memory transport. Python binds
+ * both with ctypes, so every entry point takes plain pointers / integers / a cudaStream_t.
+ *
+ * Reference parity notes cite files of anaykulkarni/collective-communication-mpi.
+ * All functions return 0 on success and a negative ccmpi_status on failure;
+ * ccmpi_last_error() returns a human readable message for the calling thread.
+ */
+#ifndef CCMPI_B200_H_
+#define CCMPI_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CCMPI_MAX_RANKS 8   /* one NVSwitch domain */
+#define CCMPI_MAX_VRANKS 4  /* emulated ranks per single-GPU launch (tests) */
+#define CCMPI_MAX_BLOCKS 160
+
+/* signal pad layout, in uint32 words, one pad per (communicator, rank) */
+#define CCMPI_PAD_WORDS 16384                     /* 64 KiB */
+#define CCMPI_PAD_BARRIER 0                       /* [block][src rank] epochs */
+#define CCMPI_PAD_EPOCH (CCMPI_MAX_BLOCKS * CCMPI_MAX_RANKS) /* [block] local epoch */
+#define CCMPI_PAD_USER 2048                       /* fused kernels: chunk / tile flags */
+#define CCMPI_PAD_USER_WORDS (CCMPI_PAD_WORDS - CCMPI_PAD_USER)
+
+typedef enum {
+    CCMPI_OK = 0,
+    CCMPI_ERR_CUDA = -1,
+    CCMPI_ERR_ARG = -2,
+    CCMPI_ERR_UNSUPPORTED = -3,
+    CCMPI_ERR_SYS = -4,
+    CCMPI_ERR_LIMIT = -5
+} ccmpi_status;
+
+typedef enum {
+    CCMPI_F32 = 0,
+    CCMPI_BF16 = 1,
+    CCMPI_F16 = 2,
+    CCMPI_F64 = 3,
+    CCMPI_I32 = 4,
+    CCMPI_I64 = 5,
+    CCMPI_U8 = 6
+} ccmpi_dtype;
+
+/* MPI.SUM / MPI.MIN / MPI.MAX of the reference (mpi_wrapper/comm.py:88-93) */
+typedef enum { CCMPI_SUM = 0, CCMPI_MIN = 1, CCMPI_MAX = 2 } ccmpi_op;
+
+typedef enum {
+    CCMPI_AR_AUTO = 0,
+    CCMPI_AR_ONESHOT = 1, /* every rank pulls every peer, rank-ordered reduce (deterministic) */
+    CCMPI_AR_TWOSHOT = 2, /* reduce own slice from peers, then gather slices */
+    CCMPI_AR_NVLS = 3     /* multimem.ld_reduce + multimem.st through the NVSwitch */
+} ccmpi_ar_algo;
+
+/*
+ * Device-resident communicator: what a kernel needs to reach its peers. `heap[i]` is member i's
+ * symmetric segment as mapped into THIS process, so `heap[i] + off` names the same logical
+ * buffer on every member. Replaces MPI.Comm handles (comm.py:5-7) and the result of
+ * MPI_Comm_split (comm.py:38-39) on the device side.
+ */
+typedef struct ccmpi_dev_comm {
+    int32_t rank;
+    int32_t size;
+    unsigned char* heap[CCMPI_MAX_RANKS];
+    unsigned char* mc_heap;          /* multicast alias of the member heaps, or NULL */
+    uint32_t* pad[CCMPI_MAX_RANKS];  /* member i's signal pad for this communicator */
+} ccmpi_dev_comm;
+
+const char* ccmpi_last_error(void);
+int ccmpi_version(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Runtime (csrc/runtime.cpp): symmetric heap over cuMemCreate / POSIX-fd export / cuMemMap,
+ * fd passing over abstract unix sockets, NVLS multicast objects.
+ * ---------------------------------------------------------------------------------------- */
+
+/* Driver/device capability probe; fills a small int array:
+ * [0] device count, [1] cc major, [2] cc minor, [3] SM count, [4] multicast supported,
+ * [5] VMM supported, [6] posix-fd handle supported, [7] heap granularity (bytes, low 31 bits) */
+int ccmpi_probe(int device, int* out8);
+
+/* Create this rank's segment of a symmetric heap of `bytes` (rounded up to the granularity) on
+ * `device`, and map it. Returns an opaque heap handle (>0). */
+int64_t ccmpi_heap_create(int device, size_t bytes);
+size_t ccmpi_heap_bytes(int64_t heap);
+void* ccmpi_heap_local_ptr(int64_t heap);
+
+/* Exchange segment handles with the other `nranks-1` processes of the job and map their
+ * segments. `job` names the rendezvous (abstract unix sockets "\0ccmpi-<job>-<rank>"), the
+ * python layer guarantees every rank is listening before anyone connects. */
+int ccmpi_heap_listen(int64_t heap, const char* job, int rank);
+int ccmpi_heap_connect_all(int64_t heap, const char* job, int rank, int nranks);
+void* ccmpi_heap_peer_ptr(int64_t heap, int peer);
+
+/* NVLS multicast over a subset of ranks (`members`, world ranks, sorted): the group's first
+ * member creates the object and ships its fd; all members add their device, bind their whole
+ * segment and map the multicast VA. Phases are separate because cuMulticastBindMem must wait
+ * until every member has added its device (python barriers in between).
+ * Returns a group id >= 0, or <0 (CCMPI_ERR_UNSUPPORTED when the platform has no multicast). */
+int ccmpi_mc_create(int64_t heap, const char* job, int rank, const int* members, int nmembers,
+                    int group_tag);
+int ccmpi_mc_bind(int64_t heap, int group);
+void* ccmpi_mc_ptr(int64_t heap, int group);
+int ccmpi_heap_destroy(int64_t heap);
+
+/* Emulated "heap" for single-GPU tests: nranks plain device buffers on one device. */
+int64_t ccmpi_heap_create_emulated(int device, size_t bytes, int nranks);
+
+/* ------------------------------------------------------------------------------------------
+ * Collective kernels (csrc/collectives.cu). `comms` points to `nvr` device communicators in
+ * HOST memory (nvr = 1 in production; nvr > 1 runs that many emulated ranks inside one
+ * cooperative launch on one GPU). Buffers are heap offsets (bytes) unless named *_ptr.
+ * ---------------------------------------------------------------------------------------- */
+int ccmpi_barrier(const ccmpi_dev_comm* comms, int nvr, void* stream);
+
+/* MPI_Allreduce (comm.py:22) and the reduce-then-broadcast myAllreduce (comm.py:63-107),
+ * re-done as one-shot / two-shot / NVLS kernels. dst is a heap offset too. `scale` is applied
+ * to float results (1.0f = none) and `out_dtype` may differ from `dtype` for float types
+ * (DP gradient path: sum, scale by 1/dp, cast). tmp_off: count*sizeof(dtype) bytes of symmetric
+ * scratch for the two-shot variant. */
+int ccmpi_allreduce(const ccmpi_dev_comm* comms, int nvr, int algo, int dtype, int op,
+                    size_t src_off, size_t dst_off, size_t tmp_off, size_t count, float scale,
+                    int out_dtype, int max_blocks, void* stream);
+
+/* MPI_Allgather (comm.py:29). Generalised to a 2-D strided form so the last-axis gathers of
+ * func_impl.py:89-90,107-108 need no transposes: each rank contributes `rows` rows of
+ * `row_bytes`; in dst, row i of rank r lands at dst + i*dst_row_stride + r*row_bytes.
+ * (flat MPI semantics: rows = 1, row_bytes = block bytes.) */
+int ccmpi_allgather(const ccmpi_dev_comm* comms, int nvr, size_t src_off, size_t dst_off,
+                    size_t rows, size_t row_bytes, size_t src_row_stride, size_t dst_row_stride,
+                    int use_mc, int max_blocks, void* stream);
+
+/* MPI_Reduce_scatter_block (comm.py:36) with the same 2-D form for func_impl.py:182-186:
+ * src has `rows` rows of size*row_bytes; rank r gets column block r of every row, reduced. */
+int ccmpi_reduce_scatter(const ccmpi_dev_comm* comms, int nvr, int dtype, int op, size_t src_off,
+                         size_t dst_off, size_t rows, size_t row_elems, size_t src_row_stride,
+                         size_t dst_row_stride, int use_mc, int max_blocks, void* stream);
+
+/* MPI_Alltoall (comm.py:61) / myAlltoall (comm.py:110-159): block j of src goes to rank j's
+ * dst block `rank`; every peer push is in flight at once. staggered != 0 uses the pairwise
+ * (rank+i)%n visiting order of myAlltoall2 (comm.py:162-199). */
+int ccmpi_alltoall(const ccmpi_dev_comm* comms, int nvr, size_t src_off, size_t dst_off,
+                   size_t seg_bytes, int staggered, int max_blocks, void* stream);
+
+/* put-with-signal mailbox behind Send/Recv/Isend/Irecv/Sendrecv (comm.py:86-193) */
+int ccmpi_put_signal(const ccmpi_dev_comm* comms, int nvr, int peer, size_t src_off,
+                     size_t dst_off, size_t bytes, int flag_index, void* stream);
+int ccmpi_wait_signal(const ccmpi_dev_comm* comms, int nvr, int peer, int flag_index,
+                      void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * tcgen05 GEMM and fused GEMM + collective kernels (csrc/gemm_tcgen05.cu)
+ * C[M,N] = A[M,K] * B[K,N], bf16 inputs, fp32 accumulation in TMEM.
+ *   a_mn_major = 0: A stored row-major [M,K]     1: stored row-major [K,M]
+ *   b_mn_major = 0: B stored row-major [N,K]     1: stored row-major [K,N]
+ *   (the FC GEMMs absent from the reference: y = x W, dx = dy W^T, dW = x^T dy)
+ * ---------------------------------------------------------------------------------------- */
+int ccmpi_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb,
+                    int ldc, int a_mn_major, int b_mn_major, int out_dtype, int accumulate,
+                    int num_sms, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CCMPI_B200_H_ */

@@ -1,0 +1,60 @@
+/*
+ * ccmpi_host -- CPU shared-memory transport (libccmpi_host.so).
+ *
+ * Stands in for "mpi4py + a system MPI" (reference requirements.txt:4, README.md:11-24) when
+ * the arrays live in host memory or the machine has no GPU: one POSIX shared-memory segment
+ * per job, a staging area per rank for collectives (copy in -> barrier -> combine -> barrier,
+ * the way MPI's own shared-memory collectives work), and a FIFO ring per ordered rank pair for
+ * Send / Recv / Isend / Irecv / Sendrecv (mpi_wrapper/comm.py:86-193).
+ *
+ * Communicators are described by the caller: `members` lists the world ranks of the group in
+ * group-rank order, `me` is the caller's index in it, `slot` is the group's barrier slot
+ * (any id < CCMPI_HOST_MAX_COMMS that all members agree on and no overlapping group shares).
+ * All calls return 0 or a negative error; ccmpi_host_last_error() explains.
+ */
+#ifndef CCMPI_HOST_H_
+#define CCMPI_HOST_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CCMPI_HOST_MAX_RANKS 64
+#define CCMPI_HOST_MAX_COMMS 256
+
+const char* ccmpi_host_last_error(void);
+
+/* Attach to (creating if necessary) the job's segment. Returns a handle > 0. */
+int64_t ccmpi_host_attach(const char* job, int rank, int nranks, size_t stage_bytes, size_t ring_bytes,
+                          double timeout_s);
+int ccmpi_host_detach(int64_t h, int unlink_segment);
+
+int ccmpi_host_barrier(int64_t h, int slot, const int* members, int n, int me);
+
+/* dtype / op use the ccmpi_dtype / ccmpi_op numbering of ccmpi_b200.h */
+int ccmpi_host_allreduce(int64_t h, int slot, const int* members, int n, int me, const void* src, void* dst,
+                         size_t count, int dtype, int op);
+int ccmpi_host_allgather(int64_t h, int slot, const int* members, int n, int me, const void* src, void* dst,
+                         size_t bytes_per_rank);
+int ccmpi_host_reduce_scatter(int64_t h, int slot, const int* members, int n, int me, const void* src, void* dst,
+                              size_t count_per_rank, int dtype, int op);
+int ccmpi_host_alltoall(int64_t h, int slot, const int* members, int n, int me, const void* src, void* dst,
+                        size_t seg_bytes);
+
+/* point-to-point, world ranks; (comm_id, tag) travel in the message header and are checked */
+int ccmpi_host_send(int64_t h, int dst, int comm_id, int tag, const void* buf, size_t bytes);
+int ccmpi_host_recv(int64_t h, int src, int comm_id, int tag, void* buf, size_t bytes);
+int64_t ccmpi_host_isend(int64_t h, int dst, int comm_id, int tag, const void* buf, size_t bytes);
+int64_t ccmpi_host_irecv(int64_t h, int src, int comm_id, int tag, void* buf, size_t bytes);
+int ccmpi_host_test(int64_t h, int64_t req);              /* 1 done, 0 pending, <0 error */
+int ccmpi_host_waitall(int64_t h, const int64_t* reqs, int n);
+/* size of the next message queued from `src` (blocks until a header is there) */
+int64_t ccmpi_host_probe(int64_t h, int src);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CCMPI_HOST_H_ */
