@@ -53,6 +53,8 @@ class World:
         self._device_tried = False
         self.device_error: Optional[str] = None
         self.mc_supported = False
+        self.stage = None
+        self.sm_count = 148
         self._next_comm_id = 1     # 0 is the world
         self._closed = False
         if self.size > 1:
@@ -144,6 +146,7 @@ class World:
             h = lib.ccmpi_heap_create_emulated(dev, nbytes, 1)
             N.check(h, "ccmpi_heap_create_emulated")
             self.heap = SymmetricHeap(h, 1, 0, dev, emulated=True)
+            self._alloc_stage()
             return self.heap
         h = lib.ccmpi_heap_create(dev, nbytes)
         N.check(h, "ccmpi_heap_create")
@@ -154,7 +157,14 @@ class World:
         self.host_barrier(0, list(range(self.size)), self.rank)  # every mapping exists
         self.heap = SymmetricHeap(h, self.size, self.rank, dev)
         self.mc_supported = bool(probe[4]) and os.environ.get("CCMPI_NVLS", "1") != "0"
+        self._alloc_stage()
         return self.heap
+
+    def _alloc_stage(self):
+        """Staging arena for host arrays / non-symmetric tensors: in, out, scratch. Allocated
+        here, world-collectively, so the offsets agree on every rank."""
+        nb = int(os.environ.get("CCMPI_STAGE_MB", "64")) << 20
+        self.stage = (self.heap.alloc(nb), self.heap.alloc(nb), self.heap.alloc(nb), nb)
 
     def make_multicast(self, members: List[int], me: int, slot: int, tag: int) -> int:
         """Multicast alias of the members' heaps; returns the device pointer or 0. Collective

@@ -1,0 +1,48 @@
+"""The reference's own test files, byte-for-byte, against this framework.
+
+``scripts/install_reference.sh`` puts the unmodified reference under ``baseline/_ref`` (falling
+back to ``/root/reference`` when that mount exists). Its four test files are run from there, with
+THIS repository first on ``sys.path`` so that ``mpi4py``, ``model.func_impl``, ``mpi_wrapper`` and
+``data.data_parallel_preprocess`` resolve to our implementations, at the rank counts the
+reference's README prescribes (README.md:163,189,200,212).
+"""
+import os
+
+import pytest
+
+from conftest import REPO, run_ranks
+
+CANDIDATES = [os.path.join(REPO, "baseline", "_ref", "tests"), "/root/reference/tests"]
+REF_TESTS = next((d for d in CANDIDATES if os.path.isfile(os.path.join(d, "test_get_info.py"))), None)
+
+pytestmark = pytest.mark.skipif(REF_TESTS is None, reason="reference tests not present (run scripts/install_reference.sh)")
+
+PYTEST = ["-m", "pytest", "-l", "-q", "-p", "collective_communication_mpi_b200.pytest_plugin", "-p", "no:cacheprovider",
+          "--rootdir", "/tmp"]
+
+
+def _run(nranks, fname, transport, expect):
+    p = run_ranks(nranks, PYTEST + (["--with-mpi"] if nranks > 1 else []) + [os.path.join(REF_TESTS, fname)],
+                  transport=transport, env={"CCMPI_FORCE_SHIM": "1"})
+    assert p.returncode == 0, f"{fname} on {nranks} ranks ({transport})\n{p.stdout[-4000:]}\n{p.stderr[-2000:]}"
+    assert expect in p.stdout, p.stdout[-2000:]
+
+
+def test_reference_data_split_file():
+    _run(1, "test_data_split.py", "host", "4 passed")
+
+
+def test_reference_get_info_file_on_8_ranks():
+    _run(8, "test_get_info.py", "host", "2 passed")
+
+
+def test_reference_forward_file_on_4_ranks():
+    _run(4, "test_transformer_forward.py", "host", "2 passed")
+
+
+def test_reference_forward_file_on_8_ranks_with_empty_shards():
+    _run(8, "test_transformer_forward.py", "host", "2 passed")
+
+
+def test_reference_backward_file_on_4_ranks():
+    _run(4, "test_transformer_backward.py", "host", "2 passed")
