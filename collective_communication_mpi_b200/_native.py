@@ -140,14 +140,18 @@ def _declare_device(lib):
         fn = getattr(lib, name)
         fn.restype = res
         fn.argtypes = args
-    # later additions are declared lazily so an older .so still loads during development
-    optional = {
-        "ccmpi_fused_ag_gemm": (i, None),
-        "ccmpi_fused_gemm_rs": (i, None),
+    PV = P(vp)
+    u = C.c_uint
+    fused = {
+        "ccmpi_fused_ag_gemm": (i, [P(DevComm), i, sz, i, sz, PV, PV, i, i, i, i, i, i, i, i, u, i, i, i, vp]),
+        "ccmpi_fused_gemm_rs": (i, [P(DevComm), i, PV, PV, sz, PV, i, i, i, i, i, i, i, i, i, i, u, i, vp]),
+        "ccmpi_fused_gemm_ar": (i, [P(DevComm), i, PV, PV, sz, sz, i, i, i, i, i, i, i, i, i, u, i, i, vp]),
+        "ccmpi_fused_gemm_ag": (i, [P(DevComm), i, PV, PV, sz, i, i, i, i, i, i, i, i, i, i, vp]),
     }
-    for name in optional:
-        if hasattr(lib, name):
-            getattr(lib, name).restype = i
+    for name, (res, args) in fused.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
 
 
 def _declare_host(lib):

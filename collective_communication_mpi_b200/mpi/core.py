@@ -256,6 +256,31 @@ class Comm:
     def Abort(self, errorcode: int = 1):
         os._exit(errorcode)
 
+    # ---- symmetric memory ---------------------------------------------------------------
+    def symm_empty(self, shape, dtype):
+        """A CUDA tensor in the symmetric heap (zero-copy operand for every device collective
+        and fused op). Allocation is collective over the WORLD by convention: every rank must
+        make the same sequence of ``symm_empty`` / ``symm_free`` calls."""
+        heap = self._world.ensure_heap()
+        if heap is None:
+            raise RuntimeError("symmetric memory needs the device plane: " + str(self._world.device_error))
+        if isinstance(shape, int):
+            shape = (shape,)
+        _, t = heap.empty(tuple(shape), dtype)
+        return t
+
+    def symm_free(self, tensor):
+        heap = self._world.heap
+        off = heap.offset_of(tensor)
+        if off is None:
+            raise ValueError("tensor does not live in the symmetric heap")
+        heap.free(off)
+
+    @property
+    def has_multicast(self) -> bool:
+        d = self._device_side()
+        return bool(d and d.has_mc)
+
     # ---- plane selection -----------------------------------------------------------------
     def _device_side(self) -> Optional[_DeviceSide]:
         """Device state, created on first use. Creation is collective over this communicator

@@ -1,0 +1,216 @@
+"""Fused GEMM + collective ops: ONE kernel per op computes tcgen05 tiles and moves operands /
+results over NVLink from inside the kernel (csrc/fused_policies.cuh).
+
+=====================  ==========================================================  ====================
+op                     what it replaces in the reference's dataflow                NCCL-style baseline
+=====================  ==========================================================  ====================
+``ag_gemm``            ``naive_collect_forward_input`` + FC GEMM (func_impl:76)    all_gather ; matmul
+``gemm_ag``            FC GEMM + ``naive_collect_forward_output`` (func_impl:94)   matmul ; all_gather
+``gemm_rs``            dx GEMM + ``naive_collect_backward_x`` (func_impl:150)      matmul ; reduce_scatter
+``gemm_ar``            row-parallel forward (fc_o / fc2): GEMM + all-reduce        matmul ; all_reduce
+=====================  ==========================================================  ====================
+
+``FusedContext`` owns what the kernels need between launches: the symmetric staging buffers
+(double-buffered, because peers write into them), the flag region of the signal pad and the
+launch epoch. One context per (communicator, op, shape); every rank must create and use its
+contexts in the same order (allocation in the symmetric heap is collective by convention).
+
+The ``*_raw`` functions take explicit device communicators and per-rank pointer lists; with more
+than one communicator they run that many *emulated* ranks in one cooperative launch on one GPU,
+which is how the single-GPU tests cover the cross-rank protocol.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Sequence
+
+import torch
+
+from .. import _native as N
+from .collectives import _arr, _sp
+
+_OUT = {torch.bfloat16: N.BF16, torch.float32: N.F32}
+
+
+def _ptrs(tensors: Sequence[Optional[torch.Tensor]]):
+    return (C.c_void_p * len(tensors))(*[(t.data_ptr() if t is not None else None) for t in tensors])
+
+
+# -------------------------------------------------------------------------------------------------
+# raw entry points
+# -------------------------------------------------------------------------------------------------
+def ag_gemm_raw(comms, x_off: int, ldx: int, xfull_off: int, B: List[torch.Tensor], Cout: List[torch.Tensor],
+                M: int, Nn: int, K: int, *, b_kn: bool, flag_base: int, epoch: int, num_comm_ctas: int = 0,
+                num_sms: int = 0, use_mc: bool = True, stream=None):
+    a, n = _arr(comms)
+    rc = N.device_lib().ccmpi_fused_ag_gemm(a, n, x_off, ldx, xfull_off, _ptrs(B), _ptrs(Cout), M, Nn, K,
+                                            B[0].stride(0), Cout[0].stride(0), int(b_kn), _OUT[Cout[0].dtype],
+                                            flag_base, epoch, num_comm_ctas, num_sms, int(use_mc), _sp(stream))
+    N.check(rc, "ccmpi_fused_ag_gemm")
+
+
+def gemm_rs_raw(comms, A: List[torch.Tensor], B: List[torch.Tensor], slots_off: int, Cout: List[torch.Tensor],
+                M: int, Nn: int, K: int, *, a_km: bool = False, b_kn: bool, flag_base: int, epoch: int,
+                num_sms: int = 0, stream=None):
+    a, n = _arr(comms)
+    rc = N.device_lib().ccmpi_fused_gemm_rs(a, n, _ptrs(A), _ptrs(B), slots_off, _ptrs(Cout), M, Nn, K,
+                                            A[0].stride(0), B[0].stride(0), Cout[0].stride(0), int(a_km), int(b_kn),
+                                            _OUT[Cout[0].dtype], flag_base, epoch, num_sms, _sp(stream))
+    N.check(rc, "ccmpi_fused_gemm_rs")
+
+
+def gemm_ar_raw(comms, A: List[torch.Tensor], B: List[torch.Tensor], slots_off: int, out_off: int, M: int, Nn: int,
+                K: int, *, a_km: bool = False, b_kn: bool, out_dtype=torch.bfloat16, flag_base: int, epoch: int,
+                num_sms: int = 0, use_mc: bool = True, stream=None):
+    a, n = _arr(comms)
+    rc = N.device_lib().ccmpi_fused_gemm_ar(a, n, _ptrs(A), _ptrs(B), slots_off, out_off, M, Nn, K, A[0].stride(0),
+                                            B[0].stride(0), int(a_km), int(b_kn), _OUT[out_dtype], flag_base, epoch,
+                                            num_sms, int(use_mc), _sp(stream))
+    N.check(rc, "ccmpi_fused_gemm_ar")
+
+
+def gemm_ag_raw(comms, A: List[torch.Tensor], B: List[torch.Tensor], yfull_off: int, M: int, Nn: int, K: int, *,
+                a_km: bool = False, b_kn: bool, out_dtype=torch.bfloat16, num_sms: int = 0, use_mc: bool = True,
+                stream=None):
+    a, n = _arr(comms)
+    rc = N.device_lib().ccmpi_fused_gemm_ag(a, n, _ptrs(A), _ptrs(B), yfull_off, M, Nn, K, A[0].stride(0),
+                                            B[0].stride(0), int(a_km), int(b_kn), _OUT[out_dtype], num_sms,
+                                            int(use_mc), _sp(stream))
+    N.check(rc, "ccmpi_fused_gemm_ag")
+
+
+# -------------------------------------------------------------------------------------------------
+# stateful per-communicator contexts
+# -------------------------------------------------------------------------------------------------
+FLAG_SLOT_WORDS = 4096  # three independent flag regions per communicator
+
+
+class FusedContext:
+    """State shared by the fused ops on one communicator: flag-region and epoch bookkeeping."""
+
+    def __init__(self, comm):
+        self.comm = comm
+        self.dev = comm.device_comm()
+        self.heap = self.dev.heap
+        self.n = comm.Get_size()
+        self.rank = comm.Get_rank()
+        self._next_slot = 0
+
+    def new_slot(self) -> int:
+        s = self._next_slot
+        if (s + 1) * FLAG_SLOT_WORDS > N.PAD_USER_WORDS:
+            raise RuntimeError("out of flag regions on this communicator (3 fused-op shapes per communicator)")
+        self._next_slot += 1
+        return s * FLAG_SLOT_WORDS
+
+
+def _ctx(comm) -> FusedContext:
+    c = getattr(comm, "_fused_ctx", None)
+    if c is None:
+        c = FusedContext(comm)
+        comm._fused_ctx = c
+    return c
+
+
+class AllGatherGemm:
+    """``y = gather_last_axis(x) @ w`` with the gather fused into the GEMM's K loop.
+
+    ``x``: ``[M, K/n]`` bf16 per rank (copied into / taken from the symmetric heap), ``w``:
+    ``[K, N]`` (``b_kn=True``, the reference's weight layout) or ``[N, K]``."""
+
+    def __init__(self, comm, M: int, K: int, *, num_comm_ctas: int = 0, use_mc: bool = True):
+        self.ctx = _ctx(comm)
+        h, n = self.ctx.heap, self.ctx.n
+        self.M, self.K, self.chunk = M, K, K // n
+        self.x_off, self.x = h.empty((M, self.chunk), torch.bfloat16)
+        self.xfull = [h.empty((M, K), torch.bfloat16) for _ in range(2)] if n > 1 else [h.empty((8, 8), torch.bfloat16)] * 2
+        self.flag_base = self.ctx.new_slot()
+        self.epoch = 0
+        self.num_comm_ctas, self.use_mc = num_comm_ctas, use_mc and self.ctx.dev.has_mc
+
+    def input_buffer(self) -> torch.Tensor:
+        """Symmetric ``[M, K/n]`` tensor: producers that write their output here make the op
+        zero-copy."""
+        return self.x
+
+    def __call__(self, x: torch.Tensor, w: torch.Tensor, *, b_kn: bool = True, out: Optional[torch.Tensor] = None,
+                 out_dtype=torch.bfloat16, num_sms: int = 0, stream=None) -> torch.Tensor:
+        if x.data_ptr() != self.x.data_ptr():
+            self.x.copy_(x.reshape(self.M, self.chunk))
+        Nn = w.shape[1] if b_kn else w.shape[0]
+        if out is None:
+            out = torch.empty((self.M, Nn), dtype=out_dtype, device=w.device)
+        self.epoch += 1
+        xf_off = self.xfull[self.epoch & 1][0]
+        ag_gemm_raw(self.ctx.dev.comms, self.x_off, self.chunk, xf_off, [w], [out], self.M, Nn, self.K, b_kn=b_kn,
+                    flag_base=self.flag_base, epoch=self.epoch, num_comm_ctas=self.num_comm_ctas, num_sms=num_sms,
+                    use_mc=self.use_mc, stream=stream)
+        return out
+
+
+class GemmReduceScatter:
+    """``reduce_scatter_last_axis(a @ b)`` with the scatter + ordered reduction fused into the
+    GEMM epilogue / tail. Result ``[M, N/n]``."""
+
+    def __init__(self, comm, M: int, Nfull: int, *, dtype=torch.bfloat16):
+        self.ctx = _ctx(comm)
+        h, n = self.ctx.heap, self.ctx.n
+        self.M, self.N, self.chunk, self.dtype = M, Nfull, Nfull // n, dtype
+        self.slots = [h.empty((n, M, self.chunk), dtype) for _ in range(2)]
+        self.flag_base = self.ctx.new_slot()
+        self.epoch = 0
+
+    def __call__(self, a: torch.Tensor, b: torch.Tensor, *, a_km: bool = False, b_kn: bool = False,
+                 out: Optional[torch.Tensor] = None, num_sms: int = 0, stream=None) -> torch.Tensor:
+        K = a.shape[0] if a_km else a.shape[1]
+        if out is None:
+            out = torch.empty((self.M, self.chunk), dtype=self.dtype, device=a.device)
+        self.epoch += 1
+        gemm_rs_raw(self.ctx.dev.comms, [a], [b], self.slots[self.epoch & 1][0], [out], self.M, self.N, K, a_km=a_km,
+                    b_kn=b_kn, flag_base=self.flag_base, epoch=self.epoch, num_sms=num_sms, stream=stream)
+        return out
+
+
+class GemmAllReduce:
+    """``all_reduce(a @ b)``: every rank ends with the full ``[M, N]`` sum in a symmetric buffer."""
+
+    def __init__(self, comm, M: int, Nfull: int, *, dtype=torch.bfloat16, use_mc: bool = True):
+        self.ctx = _ctx(comm)
+        h, n = self.ctx.heap, self.ctx.n
+        self.M, self.N, self.chunk, self.dtype = M, Nfull, Nfull // n, dtype
+        self.slots = [h.empty((n, M, self.chunk), dtype) for _ in range(2)]
+        self.outs = [h.empty((M, Nfull), dtype) for _ in range(2)]
+        self.flag_base = self.ctx.new_slot()
+        self.epoch = 0
+        self.use_mc = use_mc and self.ctx.dev.has_mc
+
+    def __call__(self, a: torch.Tensor, b: torch.Tensor, *, a_km: bool = False, b_kn: bool = False, num_sms: int = 0,
+                 stream=None) -> torch.Tensor:
+        K = a.shape[0] if a_km else a.shape[1]
+        self.epoch += 1
+        off, out = self.outs[self.epoch & 1]
+        gemm_ar_raw(self.ctx.dev.comms, [a], [b], self.slots[self.epoch & 1][0], off, self.M, self.N, K, a_km=a_km,
+                    b_kn=b_kn, out_dtype=self.dtype, flag_base=self.flag_base, epoch=self.epoch, num_sms=num_sms,
+                    use_mc=self.use_mc, stream=stream)
+        return out
+
+
+class GemmAllGather:
+    """``gather_last_axis(a @ b)``: each finished tile is stored into every rank's ``[M, N*n]``."""
+
+    def __init__(self, comm, M: int, Nlocal: int, *, dtype=torch.bfloat16, use_mc: bool = True):
+        self.ctx = _ctx(comm)
+        h, n = self.ctx.heap, self.ctx.n
+        self.M, self.N, self.dtype = M, Nlocal, dtype
+        self.outs = [h.empty((M, Nlocal * n), dtype) for _ in range(2)]
+        self.epoch = 0
+        self.use_mc = use_mc and self.ctx.dev.has_mc
+
+    def __call__(self, a: torch.Tensor, b: torch.Tensor, *, a_km: bool = False, b_kn: bool = True, num_sms: int = 0,
+                 stream=None) -> torch.Tensor:
+        K = a.shape[0] if a_km else a.shape[1]
+        self.epoch += 1
+        off, out = self.outs[self.epoch & 1]
+        gemm_ag_raw(self.ctx.dev.comms, [a], [b], off, self.M, self.N, K, a_km=a_km, b_kn=b_kn, out_dtype=self.dtype,
+                    num_sms=num_sms, use_mc=self.use_mc, stream=stream)
+        return out

@@ -56,6 +56,17 @@ __device__ __forceinline__ void block_barrier(const Ctx& x) {
     if (threadIdx.x == 0) *reinterpret_cast<volatile uint32_t*>(self + CCMPI_PAD_EPOCH + x.blk) = epoch;
 }
 
+// Grid-stride loop over [lo, hi) that hands the body U indices at a time (i, i+stride, ...), so a
+// thread has U independent loads (times the number of peers) in flight: NVLink round trips are
+// ~2 us, and bandwidth = bytes in flight / latency.
+template <int U, typename Body>
+__device__ __forceinline__ void for_range_unrolled(size_t lo, size_t hi, const Ctx& x, Body body) {
+    const size_t stride = (size_t)x.nblk * THREADS;
+    size_t i = lo + (size_t)x.blk * THREADS + threadIdx.x;
+    for (; i + (U - 1) * stride < hi; i += U * stride) body(i, stride, std::integral_constant<int, U>());
+    for (; i < hi; i += stride) body(i, stride, std::integral_constant<int, 1>());
+}
+
 // ------------------------------------------------------------------------------------------------
 // element-wise reduce machinery on 16-byte vectors
 // ------------------------------------------------------------------------------------------------
@@ -208,18 +219,27 @@ allreduce_twoshot_kernel(const __grid_constant__ Launch lp, size_t src_off, size
     {
         const size_t lo = per * c.rank, hi = min(nvec, lo + per);
         OutT* tmp = reinterpret_cast<OutT*>(c.heap[c.rank] + tmp_off);
-        for (size_t i = lo + (size_t)x.blk * THREADS + threadIdx.x; i < hi; i += (size_t)x.nblk * THREADS) {
-            uint4 r[CCMPI_MAX_RANKS];
+        auto reduce_body = [&](size_t i, size_t stride, auto uc) {
+            constexpr int U = decltype(uc)::value;
+            uint4 r[U][CCMPI_MAX_RANKS];
 #pragma unroll
-            for (int p = 0; p < CCMPI_MAX_RANKS; ++p)
-                if (p < c.size) r[p] = ptx::ld_v4(c.heap[p] + src_off + i * 16);
-            AccVec<T> acc;
-            acc.init(r[0]);
+            for (int u = 0; u < U; ++u)
 #pragma unroll
-            for (int p = 1; p < CCMPI_MAX_RANKS; ++p)
-                if (p < c.size) acc.template fold<OP>(r[p]);
-            store_scaled<OutT, A, N>(tmp, i * N, acc.e, scale);
-        }
+                for (int p = 0; p < CCMPI_MAX_RANKS; ++p)
+                    if (p < c.size) r[u][p] = ptx::ld_v4(c.heap[p] + src_off + (i + u * stride) * 16);
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                AccVec<T> acc;
+                acc.init(r[u][0]);
+#pragma unroll
+                for (int p = 1; p < CCMPI_MAX_RANKS; ++p)
+                    if (p < c.size) acc.template fold<OP>(r[u][p]);
+                store_scaled<OutT, A, N>(tmp, (i + u * stride) * N, acc.e, scale);
+            }
+        };
+        if (c.size <= 2) for_range_unrolled<4>(lo, hi, x, reduce_body);
+        else if (c.size <= 4) for_range_unrolled<2>(lo, hi, x, reduce_body);
+        else for_range_unrolled<1>(lo, hi, x, reduce_body);
     }
     block_barrier(x);
     {
@@ -229,6 +249,17 @@ allreduce_twoshot_kernel(const __grid_constant__ Launch lp, size_t src_off, size
             const int p = (c.rank + s) % c.size;  // own slice first, then spread over peers
             const size_t lo = per * p, hi = min(nvec, lo + per);
             const uint8_t* from = c.heap[p] + tmp_off;
+            if constexpr (OV == 16) {
+                for_range_unrolled<8>(lo, hi, x, [&](size_t i, size_t stride, auto uc) {
+                    constexpr int U = decltype(uc)::value;
+                    uint4 v[U];
+#pragma unroll
+                    for (int u = 0; u < U; ++u) v[u] = ptx::ld_v4(from + (i + u * stride) * 16);
+#pragma unroll
+                    for (int u = 0; u < U; ++u) ptx::st_v4(dst + (i + u * stride) * 16, v[u]);
+                });
+                continue;
+            }
             for (size_t i = lo + (size_t)x.blk * THREADS + threadIdx.x; i < hi; i += (size_t)x.nblk * THREADS) {
                 if constexpr (OV == 16) {
                     ptx::st_v4(dst + i * 16, ptx::ld_v4(from + i * 16));
@@ -268,6 +299,20 @@ allreduce_nvls_kernel(const __grid_constant__ Launch lp, size_t src_off, size_t 
     uint8_t* mdst = c.mc_heap + dst_off;
     const bool identity = (scale == 1.0f) && std::is_same<T, OutT>::value;
     block_barrier(x);
+    if constexpr (std::is_same<T, OutT>::value) {
+        if (identity) {
+            for_range_unrolled<8>(lo, hi, x, [&](size_t g, size_t stride, auto uc) {
+                constexpr int U = decltype(uc)::value;
+                uint4 v[U];
+#pragma unroll
+                for (int u = 0; u < U; ++u) v[u] = mc_ld_reduce<T>(msrc + (g + u * stride) * 16);
+#pragma unroll
+                for (int u = 0; u < U; ++u) ptx::multimem_st_v4(mdst + (g + u * stride) * 16, v[u]);
+            });
+            block_barrier(x);
+            return;
+        }
+    }
     for (size_t g = lo + (size_t)x.blk * THREADS + threadIdx.x; g < hi; g += (size_t)x.nblk * THREADS) {
         if constexpr (std::is_same<T, OutT>::value) {
             uint4 r = mc_ld_reduce<T>(msrc + g * 16);
@@ -332,22 +377,32 @@ allgather_kernel(const __grid_constant__ Launch lp, size_t src_off, size_t dst_o
     block_barrier(x);  // every member's dst is free to be overwritten
     const uint8_t* src = c.heap[c.rank] + src_off;
     const size_t col0 = (size_t)c.rank * row_bytes;
-    for (size_t i = (size_t)x.blk * THREADS + threadIdx.x; i < total; i += (size_t)x.nblk * THREADS) {
-        const size_t row = i / wpr, w = i - row * wpr;
-        const WT v = *reinterpret_cast<const WT*>(src + row * src_row_stride + w * W);
-        const size_t d = dst_off + row * dst_row_stride + col0 + w * W;
-        if constexpr (MC && W == 16) {
-            ptx::multimem_st_v4(c.mc_heap + d, v);
-        } else {
+    for_range_unrolled<4>(0, total, x, [&](size_t i0, size_t stride, auto uc) {
+        constexpr int U = decltype(uc)::value;
+        WT v[U];
+        size_t d[U];
 #pragma unroll
-            for (int s = 0; s < CCMPI_MAX_RANKS; ++s) {
-                if (s < c.size) {
-                    const int p = (c.rank + s) % c.size;
-                    *reinterpret_cast<WT*>(c.heap[p] + d) = v;
+        for (int u = 0; u < U; ++u) {
+            const size_t i = i0 + u * stride;
+            const size_t row = i / wpr, w = i - row * wpr;
+            v[u] = *reinterpret_cast<const WT*>(src + row * src_row_stride + w * W);
+            d[u] = dst_off + row * dst_row_stride + col0 + w * W;
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if constexpr (MC && W == 16) {
+                ptx::multimem_st_v4(c.mc_heap + d[u], v[u]);
+            } else {
+#pragma unroll
+                for (int s = 0; s < CCMPI_MAX_RANKS; ++s) {
+                    if (s < c.size) {
+                        const int p = (c.rank + s) % c.size;
+                        *reinterpret_cast<WT*>(c.heap[p] + d[u]) = v[u];
+                    }
                 }
             }
         }
-    }
+    });
     block_barrier(x);  // all pushes have landed everywhere
 }
 
@@ -370,26 +425,44 @@ reduce_scatter_kernel(const __grid_constant__ Launch lp, size_t src_off, size_t 
         constexpr int N = 16 / sizeof(T);
         const size_t vpr = row_elems / N;
         const size_t total = rows * vpr;
-        for (size_t i = (size_t)x.blk * THREADS + threadIdx.x; i < total; i += (size_t)x.nblk * THREADS) {
-            const size_t row = i / vpr, w = i - row * vpr;
-            const size_t s = src_off + row * src_row_stride + col0 + w * 16;
-            uint4 out;
-            if constexpr (MC) {
-                out = mc_ld_reduce<T>(c.mc_heap + s);
-            } else {
-                uint4 r[CCMPI_MAX_RANKS];
+        auto body = [&](size_t i0, size_t stride, auto uc) {
+            constexpr int U = decltype(uc)::value;
+            size_t so[U], dofs[U];
 #pragma unroll
-                for (int p = 0; p < CCMPI_MAX_RANKS; ++p)
-                    if (p < c.size) r[p] = ptx::ld_v4(c.heap[p] + s);
-                AccVec<T> acc;
-                acc.init(r[0]);
-#pragma unroll
-                for (int p = 1; p < CCMPI_MAX_RANKS; ++p)
-                    if (p < c.size) acc.template fold<OP>(r[p]);
-                out = acc.pack();
+            for (int u = 0; u < U; ++u) {
+                const size_t i = i0 + u * stride;
+                const size_t row = i / vpr, w = i - row * vpr;
+                so[u] = src_off + row * src_row_stride + col0 + w * 16;
+                dofs[u] = row * dst_row_stride + w * 16;
             }
-            ptx::st_v4(dst + row * dst_row_stride + w * 16, out);
-        }
+            if constexpr (MC) {
+                uint4 out[U];
+#pragma unroll
+                for (int u = 0; u < U; ++u) out[u] = mc_ld_reduce<T>(c.mc_heap + so[u]);
+#pragma unroll
+                for (int u = 0; u < U; ++u) ptx::st_v4(dst + dofs[u], out[u]);
+            } else {
+                uint4 r[U][CCMPI_MAX_RANKS];
+#pragma unroll
+                for (int u = 0; u < U; ++u)
+#pragma unroll
+                    for (int p = 0; p < CCMPI_MAX_RANKS; ++p)
+                        if (p < c.size) r[u][p] = ptx::ld_v4(c.heap[p] + so[u]);
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    AccVec<T> acc;
+                    acc.init(r[u][0]);
+#pragma unroll
+                    for (int p = 1; p < CCMPI_MAX_RANKS; ++p)
+                        if (p < c.size) acc.template fold<OP>(r[u][p]);
+                    ptx::st_v4(dst + dofs[u], acc.pack());
+                }
+            }
+        };
+        if (MC) for_range_unrolled<8>(0, total, x, body);
+        else if (c.size <= 2) for_range_unrolled<4>(0, total, x, body);
+        else if (c.size <= 4) for_range_unrolled<2>(0, total, x, body);
+        else for_range_unrolled<1>(0, total, x, body);
     } else {
         const size_t total = rows * row_elems;
         for (size_t i = (size_t)x.blk * THREADS + threadIdx.x; i < total; i += (size_t)x.nblk * THREADS) {
@@ -428,12 +501,26 @@ alltoall_kernel(const __grid_constant__ Launch lp, size_t src_off, size_t dst_of
         }
     } else {
         const size_t total = wps * c.size;
-        for (size_t i = (size_t)x.blk * THREADS + threadIdx.x; i < total; i += (size_t)x.nblk * THREADS) {
-            const size_t w = i / c.size;
-            const int p = (int)((i - w * c.size + c.rank) % c.size);
-            reinterpret_cast<WT*>(c.heap[p] + dst_off + (size_t)c.rank * seg_bytes)[w] =
-                reinterpret_cast<const WT*>(src + (size_t)p * seg_bytes)[w];
-        }
+        // peer-major within a warp-sized run keeps both the local loads and the remote stores
+        // coalesced; consecutive runs rotate over the peers so every link is busy at once
+        const size_t runs_per_seg = (wps + 31) / 32;
+        for_range_unrolled<4>(0, runs_per_seg * 32 * c.size, x, [&](size_t i0, size_t stride, auto uc) {
+            constexpr int U = decltype(uc)::value;
+            WT v[U];
+            size_t w[U];
+            int p[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const size_t i = i0 + u * stride;
+                const size_t run = i / 32;
+                p[u] = (int)((run + c.rank) % c.size);
+                w[u] = (run / c.size) * 32 + (i & 31);
+                if (w[u] < wps) v[u] = reinterpret_cast<const WT*>(src + (size_t)p[u] * seg_bytes)[w[u]];
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+                if (w[u] < wps) reinterpret_cast<WT*>(c.heap[p[u]] + dst_off + (size_t)c.rank * seg_bytes)[w[u]] = v[u];
+        });
     }
     block_barrier(x);
 }
@@ -483,11 +570,12 @@ static int fill_launch(Launch& lp, const ccmpi_dev_comm* comms, int nvr) {
 }
 
 static int clamp_blocks(size_t work_items, int max_blocks) {
-    int cap = max_blocks > 0 ? max_blocks : 64;
+    int cap = max_blocks > 0 ? max_blocks : 128;
     if (cap > CCMPI_MAX_BLOCKS) cap = CCMPI_MAX_BLOCKS;
     size_t want = (work_items + THREADS - 1) / THREADS;
-    // a few vectors per thread before adding blocks: these kernels are latency-, then link-bound
-    want = (want + 3) / 4;
+    // a few vectors per thread before adding blocks: small messages are latency-bound and a
+    // barrier among few blocks is cheaper; large ones need every SM's worth of loads in flight
+    want = (want + 7) / 8;
     if (want < 1) want = 1;
     return (int)(want < (size_t)cap ? want : (size_t)cap);
 }

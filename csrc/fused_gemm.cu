@@ -1,0 +1,167 @@
+// Host entry points of the fused GEMM + collective kernels (device side: fused_policies.cuh).
+//
+// Each entry takes `nvr` device communicators (1 in production; >1 = emulated ranks inside one
+// cooperative launch on one GPU, used by the single-GPU tests) and, per rank, the local operand
+// pointers. Buffers that peers touch are given as symmetric-heap offsets.
+#include "fused_policies.cuh"
+#include "gemm_host.h"
+
+using namespace gemm;
+
+namespace {
+
+int common_checks(const ccmpi_dev_comm* comms, int nvr, int flag_words_needed, int flag_base) {
+    CCMPI_REQUIRE(comms && nvr >= 1 && nvr <= CCMPI_MAX_VRANKS, "nvr=%d out of range", nvr);
+    CCMPI_REQUIRE(nvr == 1 || nvr == comms[0].size, "emulation needs exactly one virtual rank per member (nvr=%d, size=%d)",
+                  nvr, comms[0].size);
+    CCMPI_REQUIRE(flag_base >= 0 && flag_base + flag_words_needed <= CCMPI_PAD_USER_WORDS,
+                  "fused op needs %d flag words at base %d, the pad has %d: use smaller M or a bigger tile", flag_words_needed,
+                  flag_base, CCMPI_PAD_USER_WORDS);
+    return CCMPI_OK;
+}
+
+int grid_for(int nvr, int sms, int tiles, int extra) {
+    int per_rank = sms / nvr;
+    if (per_rank > tiles + extra) per_rank = tiles + extra;
+    return per_rank;
+}
+
+}  // namespace
+
+// all-gather -> GEMM (K-gather): C_r[M][N] = [x_0 | ... | x_{n-1}] * B_r, x_r = rank r's [M][K/n] shard
+extern "C" int ccmpi_fused_ag_gemm(const ccmpi_dev_comm* comms, int nvr, size_t x_off, int ldx, size_t xfull_off,
+                                   const void* const* B, void* const* C, int M, int N, int K, int ldb, int ldc,
+                                   int b_kn, int out_dtype, int flag_base, unsigned epoch, int num_comm_ctas,
+                                   int num_sms, int use_mc, void* stream) {
+    int rc = check_shapes(M, N, K, ldx, ldb, ldc, out_dtype);
+    if (rc) return rc;
+    const int n = comms ? comms[0].size : 0;
+    const int m_blocks = (M + BM - 1) / BM;
+    rc = common_checks(comms, nvr, n * m_blocks, flag_base);
+    if (rc) return rc;
+    CCMPI_REQUIRE(K % n == 0 && (K / n) % BK == 0, "K/n = %d must be a multiple of %d", K / n, BK);
+    CCMPI_REQUIRE((x_off | xfull_off) % 16 == 0, "symmetric offsets must be 16-byte aligned");
+    const int chunk = K / n;
+    const int sms = (num_sms > 0 ? num_sms : ccmpi::device_sm_count());
+    int ncomm = n > 1 ? (num_comm_ctas > 0 ? num_comm_ctas : 16) : 0;
+    if (ncomm > m_blocks) ncomm = m_blocks;
+    const int per_rank_budget = sms / nvr;
+    CCMPI_REQUIRE(per_rank_budget > ncomm, "not enough SMs (%d per rank) for %d communication CTAs", per_rank_budget, ncomm);
+    const int BN = pick_bn(M, N, per_rank_budget - ncomm);
+    const int tiles = m_blocks * ((N + BN - 1) / BN);
+    int gemm_ctas = per_rank_budget - ncomm;
+    if (gemm_ctas > tiles) gemm_ctas = tiles;
+    Launch lp;
+    memset(&lp, 0, sizeof(lp));
+    lp.nvr = nvr;
+    for (int v = 0; v < nvr; ++v) {
+        RankParams& rp = lp.r[v];
+        const ccmpi_dev_comm& c = comms[v];
+        const void* xfull = c.heap[c.rank] + xfull_off;
+        const void* xloc = c.heap[c.rank] + x_off;
+        rc = fill_tmaps(rp, xfull, xloc, B[v], M, N, K, K, ldx, ldb, false, b_kn != 0, BN, M, chunk);
+        if (rc) return rc;
+        rp.C = C[v];
+        rp.ldc = ldc;
+        rp.M = M; rp.N = N; rp.K = K;
+        rp.comm = c;
+        rp.off0 = x_off; rp.off1 = xfull_off;
+        rp.chunk = chunk;
+        rp.flag_base = flag_base;
+        rp.epoch = epoch;
+        rp.num_comm_ctas = ncomm;
+        rp.aux0 = ldx;
+        rp.aux1 = use_mc;
+    }
+    return dispatch<AgKPolicy>(lp, BN, false, b_kn != 0, out_dtype, (gemm_ctas + ncomm) * nvr, (cudaStream_t)stream, nvr > 1);
+}
+
+namespace {
+// shared by reduce-scatter and all-reduce flavours
+template <typename Policy>
+int gemm_scatter(const ccmpi_dev_comm* comms, int nvr, const void* const* A, const void* const* B, size_t slots_off,
+                 void* const* C, size_t out_off, int M, int N, int K, int lda, int ldb, int ldc, int a_km, int b_kn,
+                 int out_dtype, int flag_base, unsigned epoch, int num_sms, int use_mc, void* stream) {
+    int rc = check_shapes(M, N, K, lda, ldb, ldc, out_dtype);
+    if (rc) return rc;
+    const int n = comms ? comms[0].size : 0;
+    CCMPI_REQUIRE(n >= 1 && N % n == 0, "N = %d must be divisible by the communicator size %d", N, n);
+    const int chunk = N / n;
+    CCMPI_REQUIRE(chunk % 128 == 0, "N/n = %d must be a multiple of 128", chunk);
+    const int BN = (chunk % 256 == 0) ? 256 : 128;
+    const int m_blocks = (M + BM - 1) / BM;
+    rc = common_checks(comms, nvr, m_blocks * (chunk / BN) * n, flag_base);
+    if (rc) return rc;
+    CCMPI_REQUIRE((slots_off | out_off) % 16 == 0, "symmetric offsets must be 16-byte aligned");
+    const int sms = (num_sms > 0 ? num_sms : ccmpi::device_sm_count());
+    const int tiles = m_blocks * (N / BN);
+    const int per_rank = grid_for(nvr, sms, tiles, 0);
+    Launch lp;
+    memset(&lp, 0, sizeof(lp));
+    lp.nvr = nvr;
+    for (int v = 0; v < nvr; ++v) {
+        RankParams& rp = lp.r[v];
+        rc = fill_tmaps(rp, A[v], A[v], B[v], M, N, K, lda, lda, ldb, a_km != 0, b_kn != 0, BN, a_km ? K : M, a_km ? M : K);
+        if (rc) return rc;
+        rp.C = C ? C[v] : nullptr;
+        rp.ldc = ldc;
+        rp.M = M; rp.N = N; rp.K = K;
+        rp.comm = comms[v];
+        rp.off1 = slots_off; rp.off2 = out_off;
+        rp.chunk = chunk;
+        rp.flag_base = flag_base;
+        rp.epoch = epoch;
+        rp.aux0 = BN;
+        rp.aux1 = use_mc;
+    }
+    return dispatch<Policy>(lp, BN, a_km != 0, b_kn != 0, out_dtype, per_rank * nvr, (cudaStream_t)stream, nvr > 1);
+}
+}  // namespace
+
+// GEMM -> reduce-scatter (N-scatter): C_r[M][N/n] = sum over ranks s of (A_s * B_s)[:, r-th column block]
+extern "C" int ccmpi_fused_gemm_rs(const ccmpi_dev_comm* comms, int nvr, const void* const* A, const void* const* B,
+                                   size_t slots_off, void* const* C, int M, int N, int K, int lda, int ldb, int ldc,
+                                   int a_km, int b_kn, int out_dtype, int flag_base, unsigned epoch, int num_sms,
+                                   void* stream) {
+    CCMPI_REQUIRE(C != nullptr, "gemm_rs needs an output pointer per rank");
+    return gemm_scatter<RsNPolicy>(comms, nvr, A, B, slots_off, C, 0, M, N, K, lda, ldb, ldc, a_km, b_kn, out_dtype,
+                                   flag_base, epoch, num_sms, 0, stream);
+}
+
+// GEMM -> all-reduce: out[M][N] (symmetric, row stride N) = sum over ranks s of A_s * B_s, on every rank
+extern "C" int ccmpi_fused_gemm_ar(const ccmpi_dev_comm* comms, int nvr, const void* const* A, const void* const* B,
+                                   size_t slots_off, size_t out_off, int M, int N, int K, int lda, int ldb, int a_km,
+                                   int b_kn, int out_dtype, int flag_base, unsigned epoch, int num_sms, int use_mc,
+                                   void* stream) {
+    return gemm_scatter<ArPolicy>(comms, nvr, A, B, slots_off, nullptr, out_off, M, N, K, lda, ldb, N, a_km, b_kn,
+                                  out_dtype, flag_base, epoch, num_sms, use_mc, stream);
+}
+
+// GEMM -> all-gather of the output: y_full[M][N*n] (symmetric) gets this rank's A*B at column block `rank`
+extern "C" int ccmpi_fused_gemm_ag(const ccmpi_dev_comm* comms, int nvr, const void* const* A, const void* const* B,
+                                   size_t yfull_off, int M, int N, int K, int lda, int ldb, int a_km, int b_kn,
+                                   int out_dtype, int num_sms, int use_mc, void* stream) {
+    int rc = check_shapes(M, N, K, lda, ldb, N, out_dtype);
+    if (rc) return rc;
+    rc = common_checks(comms, nvr, 0, 0);
+    if (rc) return rc;
+    CCMPI_REQUIRE(yfull_off % 16 == 0, "symmetric offsets must be 16-byte aligned");
+    const int sms = (num_sms > 0 ? num_sms : ccmpi::device_sm_count());
+    const int BN = pick_bn(M, N, sms / nvr);
+    const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
+    const int per_rank = grid_for(nvr, sms, tiles, 0);
+    CCMPI_REQUIRE(per_rank <= CCMPI_MAX_BLOCKS, "grid of %d CTAs exceeds the %d barrier slots", per_rank, CCMPI_MAX_BLOCKS);
+    Launch lp;
+    memset(&lp, 0, sizeof(lp));
+    lp.nvr = nvr;
+    for (int v = 0; v < nvr; ++v) {
+        RankParams& rp = lp.r[v];
+        rc = fill_tmaps(rp, A[v], A[v], B[v], M, N, K, lda, lda, ldb, a_km != 0, b_kn != 0, BN, a_km ? K : M, a_km ? M : K);
+        if (rc) return rc;
+        rp.M = M; rp.N = N; rp.K = K;
+        rp.comm = comms[v];
+        rp.off1 = yfull_off;
+        rp.aux1 = use_mc;
+    }
+    return dispatch<AgOutPolicy>(lp, BN, a_km != 0, b_kn != 0, out_dtype, per_rank * nvr, (cudaStream_t)stream, nvr > 1);
+}

@@ -1,0 +1,329 @@
+// Policies that fuse a collective into the persistent tcgen05 GEMM (gemm_kernel.cuh).
+//
+//   AgKPolicy   all-gather -> GEMM, gather axis = GEMM K   (func_impl.py:76-91 + the FC GEMM)
+//   RsNPolicy   GEMM -> reduce-scatter, scatter axis = GEMM N (func_impl.py:150-187 after dx GEMM)
+//   AgOutPolicy GEMM -> all-gather of the output on N       (func_impl.py:94-109 after the FC GEMM)
+//   ArPolicy    GEMM -> all-reduce (row-parallel fc_o / fc2 forward: RsN + broadcast of the result)
+//
+// All cross-GPU traffic is issued from inside the kernel on peer-mapped pointers
+// (ccmpi_dev_comm::heap[peer]) or on the NVLS multicast alias (mc_heap). Flags live in the
+// user area of the communicator's signal pad and carry the launch epoch, so they never need
+// resetting; buffers that peers write into are double-buffered by the caller (epoch parity),
+// which is sufficient because a rank cannot get two launches ahead of a peer whose data it
+// needs.
+#pragma once
+#include "gemm_kernel.cuh"
+
+namespace gemm {
+
+__device__ __forceinline__ uint32_t* user_flag(const ccmpi_dev_comm& c, int rank, int idx) {
+    return c.pad[rank] + CCMPI_PAD_USER + idx;
+}
+
+// Cross-rank barrier for CTA `cta` of every rank, callable by any subset of threads of the CTA
+// that contains thread `t0..t0+size-1` (uses the same pad words as the stand-alone collectives,
+// csrc/collectives.cu: block_barrier). `sync` is the caller's intra-CTA barrier for the
+// participating threads.
+template <typename SyncFn>
+__device__ __forceinline__ void cta_rank_barrier(const ccmpi_dev_comm& c, int cta, int tid, SyncFn sync) {
+    sync();
+    uint32_t* self = c.pad[c.rank];
+    const uint32_t epoch = *reinterpret_cast<volatile uint32_t*>(self + CCMPI_PAD_EPOCH + cta) + 1;
+    if (tid < c.size) {
+        ptx::st_release_sys(c.pad[tid] + CCMPI_PAD_BARRIER + cta * CCMPI_MAX_RANKS + c.rank, epoch);
+        ptx::wait_flag_ge_sys(self + CCMPI_PAD_BARRIER + cta * CCMPI_MAX_RANKS + tid, epoch, 900 + tid);
+    }
+    sync();
+    if (tid == 0) *reinterpret_cast<volatile uint32_t*>(self + CCMPI_PAD_EPOCH + cta) = epoch;
+}
+
+// ================================================================================================
+// all-gather -> GEMM, K-gather.   A = [x_0 | x_1 | ... | x_{n-1}] along K, x_r lives on rank r.
+//   off0 : symmetric offset of x_local  [M][chunk]   (row stride aux0 elements)
+//   off1 : symmetric offset of x_full   [M][K]       (staging the peers push into)
+//   tmap_a  -> this rank's x_full,  tmap_a2 -> this rank's x_local
+// Communication CTAs push this rank's rows, one 128-row block at a time, into every peer's
+// x_full and then raise ready[rank][m_blk] on that peer. The GEMM walks K starting with the local
+// chunk (no wait), then chunks (rank+1)%n, ... each gated on its ready flag.
+// ================================================================================================
+struct AgKPolicy : PlainPolicy {
+    static constexpr bool kCommCtas = true;
+
+    __device__ static int ready_idx(const RankParams& p, int src, int m_blk) {
+        return p.flag_base + src * ((p.M + BM - 1) / BM) + m_blk;
+    }
+
+    __device__ static void kblock(const RankParams& p, const TileCoord& tc, int it, int& k0, const CUtensorMap*& ta,
+                                  int& a_k0, int& a_m0) {
+        const ccmpi_dev_comm& c = p.comm;
+        const int per = p.chunk / BK;              // K-blocks per chunk
+        const int ci = it / per, within = it - ci * per;
+        const int src = (c.rank + ci) % c.size;
+        k0 = src * p.chunk + within * BK;
+        a_m0 = tc.m_blk * BM;
+        if (src == c.rank) {
+            ta = &p.tmap_a2;
+            a_k0 = within * BK;
+        } else {
+            if (within == 0) {
+                ptx::wait_flag_ge_sys(user_flag(c, c.rank, ready_idx(p, src, tc.m_blk)), p.epoch, 500 + src);
+                ptx::fence_proxy_async_all();  // peer's generic-proxy stores -> our TMA reads
+            }
+            ta = &p.tmap_a;
+            a_k0 = k0;
+        }
+    }
+
+    __device__ static void comm_cta(const RankParams& p, int cc, int ncomm) {
+        const ccmpi_dev_comm& c = p.comm;
+        if (c.size == 1) return;
+        const int m_blocks = (p.M + BM - 1) / BM;
+        const int vec_per_row = p.chunk / 8;  // 16-byte vectors per row of the local shard
+        const uint8_t* x = c.heap[c.rank] + p.off0;
+        const size_t src_ld = (size_t)p.aux0 * 2, dst_ld = (size_t)p.K * 2;
+        const size_t col0 = (size_t)c.rank * p.chunk * 2;
+        const bool mc = p.aux1 != 0 && c.mc_heap != nullptr;
+        for (int mb = cc; mb < m_blocks; mb += ncomm) {
+            const int r0 = mb * BM, rows = min(BM, p.M - r0);
+            const int total = rows * vec_per_row;
+            constexpr int U = 8;
+            int i = threadIdx.x;
+            for (; i + (U - 1) * NUM_THREADS < total; i += U * NUM_THREADS) {
+                uint4 v[U];
+                size_t d[U];
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const int j = i + u * NUM_THREADS;
+                    const int row = j / vec_per_row, w = j - row * vec_per_row;
+                    v[u] = ptx::ld_nc_v4(x + (size_t)(r0 + row) * src_ld + (size_t)w * 16);
+                    d[u] = p.off1 + (size_t)(r0 + row) * dst_ld + col0 + (size_t)w * 16;
+                }
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    if (mc) {
+                        ptx::multimem_st_v4(c.mc_heap + d[u], v[u]);
+                    } else {
+#pragma unroll
+                        for (int s = 1; s < CCMPI_MAX_RANKS; ++s)
+                            if (s < c.size) ptx::st_v4(c.heap[(c.rank + s) % c.size] + d[u], v[u]);
+                    }
+                }
+            }
+            for (; i < total; i += NUM_THREADS) {
+                const int row = i / vec_per_row, w = i - row * vec_per_row;
+                const uint4 v = ptx::ld_nc_v4(x + (size_t)(r0 + row) * src_ld + (size_t)w * 16);
+                const size_t d = p.off1 + (size_t)(r0 + row) * dst_ld + col0 + (size_t)w * 16;
+                if (mc) {
+                    ptx::multimem_st_v4(c.mc_heap + d, v);
+                } else {
+                    for (int s = 1; s < c.size; ++s) ptx::st_v4(c.heap[(c.rank + s) % c.size] + d, v);
+                }
+            }
+            __syncthreads();  // every thread's stores are issued ...
+            if (threadIdx.x > 0 && threadIdx.x < c.size) {
+                // ... and published: release at system scope is cumulative over the barrier
+                const int peer = (c.rank + threadIdx.x) % c.size;
+                ptx::fence_acq_rel_sys();
+                ptx::st_release_sys(user_flag(c, peer, ready_idx(p, c.rank, mb)), p.epoch);
+            }
+        }
+    }
+};
+
+// ================================================================================================
+// GEMM -> reduce-scatter, N-scatter.  C_partial[M][N] is produced tile by tile; column block
+// [r*chunk, (r+1)*chunk) belongs to rank r.
+//   off1 : symmetric offset of the slot buffer  [n sources][M][chunk]  (OutT)
+//   C    : this rank's reduced output            [M][chunk], row stride ldc
+// The epilogue stores each partial tile into the OWNER's slot for this source rank and raises
+// flag[tile][source] there. Tiles owned by peers are computed first. When a CTA runs out of
+// tiles its epilogue warps turn into reducers: they wait for all n sources of an owned tile and
+// sum the slots in rank order 0..n-1 (the order of np.sum(axis=0) in func_impl.py:186).
+// ================================================================================================
+//   aux0 : the launch's BN (tile width), so one policy type serves every tile shape
+struct RsNPolicy : PlainPolicy {
+    static constexpr bool kCommCtas = false;
+
+    __device__ static int nb_per_owner(const RankParams& p) { return p.chunk / p.aux0; }
+    __device__ static int flag_idx(const RankParams& p, int m_blk, int n_local, int src) {
+        return p.flag_base + ((m_blk * nb_per_owner(p) + n_local) * p.comm.size + src);
+    }
+
+    // owner groups in order rank+1, rank+2, ..., rank (own tiles last)
+    __device__ static TileCoord tile(const RankParams& p, int t, int mb, int nb) {
+        const int per_owner = mb * nb_per_owner(p);
+        const int g = t / per_owner, in_g = t - g * per_owner;
+        const int owner = (p.comm.rank + 1 + g) % p.comm.size;
+        TileCoord tc = raster(in_g, mb, nb_per_owner(p));
+        tc.n_blk += owner * nb_per_owner(p);
+        return tc;
+    }
+
+    template <typename OutT>
+    __device__ static void store(const RankParams& p, const TileCoord& tc, int row, int col0, const uint32_t (&v)[32]) {
+        if (row >= p.M) return;
+        const ccmpi_dev_comm& c = p.comm;
+        const int owner = col0 / p.chunk;
+        const int lcol = col0 - owner * p.chunk;
+        OutT* slot = reinterpret_cast<OutT*>(c.heap[owner] + p.off1) +
+                     ((size_t)c.rank * p.M + row) * p.chunk + lcol;
+        store_row32<OutT>(slot, v, 32, false);
+    }
+
+    __device__ static void tile_done(const RankParams& p, const TileCoord& tc, int epi_tid) {
+        epi_bar_sync();
+        if (epi_tid == 0) {
+            const ccmpi_dev_comm& c = p.comm;
+            const int owner = tc.n_blk / nb_per_owner(p);
+            const int n_local = tc.n_blk - owner * nb_per_owner(p);
+            ptx::fence_acq_rel_sys();
+            ptx::st_release_sys(user_flag(c, owner, flag_idx(p, tc.m_blk, n_local, c.rank)), p.epoch);
+        }
+    }
+
+    // Reduce one owned tile: 128 threads, 16-byte vectors, rank-ordered fp32 accumulation.
+    template <typename OutT, bool BROADCAST>
+    __device__ static void reduce_tile(const RankParams& p, int m_blk, int n_local, int epi_tid) {
+        const ccmpi_dev_comm& c = p.comm;
+        if (epi_tid < c.size)
+            ptx::wait_flag_ge_sys(user_flag(c, c.rank, flag_idx(p, m_blk, n_local, epi_tid)), p.epoch, 600 + epi_tid);
+        epi_bar_sync();
+        constexpr int EPV = 16 / sizeof(OutT);          // elements per 16-byte vector
+        const int BN = p.aux0;
+        const int VPR = BN / EPV;                       // vectors per tile row
+        const int rows = min(BM, p.M - m_blk * BM);
+        const OutT* slots = reinterpret_cast<const OutT*>(c.heap[c.rank] + p.off1);
+        for (int v = epi_tid; v < rows * VPR; v += EPI_THREADS) {
+            const int row = m_blk * BM + v / VPR;
+            const int lcol = n_local * BN + (v % VPR) * EPV;
+            float acc[EPV];
+            uint4 raw[CCMPI_MAX_RANKS];
+#pragma unroll
+            for (int s = 0; s < CCMPI_MAX_RANKS; ++s)
+                if (s < c.size) raw[s] = ptx::ld_v4(slots + ((size_t)s * p.M + row) * p.chunk + lcol);
+#pragma unroll
+            for (int s = 0; s < CCMPI_MAX_RANKS; ++s) {
+                if (s < c.size) {
+                    if constexpr (sizeof(OutT) == 2) {
+                        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw[s]);
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const float2 f = __bfloat1622float2(h[e]);
+                            acc[2 * e] = s == 0 ? f.x : acc[2 * e] + f.x;
+                            acc[2 * e + 1] = s == 0 ? f.y : acc[2 * e + 1] + f.y;
+                        }
+                    } else {
+                        const float* f = reinterpret_cast<const float*>(&raw[s]);
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) acc[e] = s == 0 ? f[e] : acc[e] + f[e];
+                    }
+                }
+            }
+            uint4 out;
+            if constexpr (sizeof(OutT) == 2) {
+                out.x = pack_bf16(__float_as_uint(acc[0]), __float_as_uint(acc[1]));
+                out.y = pack_bf16(__float_as_uint(acc[2]), __float_as_uint(acc[3]));
+                out.z = pack_bf16(__float_as_uint(acc[4]), __float_as_uint(acc[5]));
+                out.w = pack_bf16(__float_as_uint(acc[6]), __float_as_uint(acc[7]));
+            } else {
+                out = make_uint4(__float_as_uint(acc[0]), __float_as_uint(acc[1]), __float_as_uint(acc[2]),
+                                 __float_as_uint(acc[3]));
+            }
+            if constexpr (!BROADCAST) {
+                ptx::st_v4(reinterpret_cast<OutT*>(p.C) + (size_t)row * p.ldc + lcol, out);
+            } else {
+                // all-reduce flavour: the reduced tile goes to every rank's full-width output
+                // (off2: symmetric [M][N], row stride N)
+                const size_t d = p.off2 + ((size_t)row * p.N + (size_t)c.rank * p.chunk + lcol) * sizeof(OutT);
+                if (p.aux1 != 0 && c.mc_heap != nullptr) {
+                    ptx::multimem_st_v4(c.mc_heap + d, out);
+                } else {
+#pragma unroll
+                    for (int s = 0; s < CCMPI_MAX_RANKS; ++s)
+                        if (s < c.size) ptx::st_v4(c.heap[(c.rank + s) % c.size] + d, out);
+                }
+            }
+        }
+    }
+
+    template <typename OutT>
+    __device__ static void tail(const RankParams& p, int cta, int nctas, int epi_tid) {
+        const int mb = (p.M + BM - 1) / BM, per = nb_per_owner(p);
+        for (int i = cta; i < mb * per; i += nctas) {
+            const TileCoord tc = raster(i, mb, per);
+            reduce_tile<OutT, false>(p, tc.m_blk, tc.n_blk, epi_tid);
+        }
+    }
+};
+
+// GEMM -> all-reduce: RsN, but the reducer broadcasts and a final cross-rank barrier makes sure
+// every rank's output is complete when its kernel ends.
+struct ArPolicy : RsNPolicy {
+    // peers' kernels store into our output: they must not start before we are done with the
+    // previous contents
+    __device__ static void prologue(const RankParams& p, int cta, int epi_tid) {
+        cta_rank_barrier(p.comm, cta, epi_tid, [] { epi_bar_sync(); });
+    }
+    template <typename OutT>
+    __device__ static void tail(const RankParams& p, int cta, int nctas, int epi_tid) {
+        const int mb = (p.M + BM - 1) / BM, per = nb_per_owner(p);
+        for (int i = cta; i < mb * per; i += nctas) {
+            const TileCoord tc = raster(i, mb, per);
+            reduce_tile<OutT, true>(p, tc.m_blk, tc.n_blk, epi_tid);
+        }
+        if (epi_tid == 0) ptx::fence_acq_rel_sys();
+        cta_rank_barrier(p.comm, cta, epi_tid, [] { epi_bar_sync(); });
+    }
+};
+
+// ================================================================================================
+// GEMM -> all-gather of the output along N.  y_local[M][N] is this rank's column block of
+// y_full[M][N*n]; every finished tile is stored straight into every rank's y_full.
+//   off1 : symmetric offset of y_full  [M][N * size]  (OutT)
+// A cross-rank barrier before the first remote store (peers have finished reading the previous
+// y_full) and one at the end (all tiles have landed everywhere) bracket the stores; the first
+// overlaps the first tile's mainloop.
+// ================================================================================================
+struct AgOutPolicy : PlainPolicy {
+    __device__ static void prologue(const RankParams& p, int cta, int epi_tid) {
+        cta_rank_barrier(p.comm, cta, epi_tid, [] { epi_bar_sync(); });
+    }
+    template <typename OutT>
+    __device__ static void tail(const RankParams& p, int cta, int nctas, int epi_tid) {
+        if (epi_tid == 0) ptx::fence_acq_rel_sys();
+        cta_rank_barrier(p.comm, cta, epi_tid, [] { epi_bar_sync(); });
+    }
+    template <typename OutT>
+    __device__ static void store(const RankParams& p, const TileCoord& tc, int row, int col0, const uint32_t (&v)[32]) {
+        if (row >= p.M) return;
+        const ccmpi_dev_comm& c = p.comm;
+        const int ncols = min(32, p.N - col0);
+        if (ncols <= 0) return;
+        const size_t full_ld = (size_t)p.N * c.size;
+        const size_t d = p.off1 + ((size_t)row * full_ld + (size_t)c.rank * p.N + col0) * sizeof(OutT);
+        if (p.aux1 != 0 && c.mc_heap != nullptr && ncols == 32) {
+            // one multimem.st per 16 bytes; the switch replicates it to every member
+            if constexpr (sizeof(OutT) == 2) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    uint4 q;
+                    q.x = pack_bf16(v[8 * j + 0], v[8 * j + 1]);
+                    q.y = pack_bf16(v[8 * j + 2], v[8 * j + 3]);
+                    q.z = pack_bf16(v[8 * j + 4], v[8 * j + 5]);
+                    q.w = pack_bf16(v[8 * j + 6], v[8 * j + 7]);
+                    ptx::multimem_st_v4(c.mc_heap + d + 16 * j, q);
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    ptx::multimem_st_v4(c.mc_heap + d + 16 * j, make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]));
+            }
+        } else {
+#pragma unroll
+            for (int s = 0; s < CCMPI_MAX_RANKS; ++s)
+                if (s < c.size) store_row32<OutT>(reinterpret_cast<OutT*>(c.heap[(c.rank + s) % c.size] + d), v, ncols, false);
+        }
+    }
+};
+
+}  // namespace gemm

@@ -76,6 +76,8 @@ struct PlainPolicy {
                                   p.accumulate != 0);
         }
     }
+    // called by all 128 epilogue threads before their first tile
+    __device__ static void prologue(const RankParams& p, int cta, int epi_tid) {}
     // called by all 128 epilogue threads after every tile
     __device__ static void tile_done(const RankParams& p, const TileCoord& tc, int epi_tid) {}
     // called by all epilogue threads once the CTA has no more tiles
@@ -97,7 +99,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_kernel(const __grid_const
     // virtual-rank decomposition (nvr == 1 in production)
     const int nvr = lp.nvr;
     const int vr = blockIdx.x % nvr;
-    const int cta = blockIdx.x / nvr;
+    int cta = blockIdx.x / nvr;
     const int nctas_all = gridDim.x / nvr;
     const RankParams& p = lp.r[vr];
 
@@ -105,12 +107,14 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_kernel(const __grid_const
     const int lane = threadIdx.x & 31;
 
     if constexpr (Policy::kCommCtas) {
-        // trailing CTAs of each rank move data; they never touch TMEM / mbarriers
+        // The LEADING CTAs of each rank move data (lowest block indices are scheduled first, so
+        // they are resident even if something else holds a few SMs); they never touch TMEM.
         const int ncomm = p.num_comm_ctas;
-        if (cta >= nctas_all - ncomm) {
-            Policy::comm_cta(p, cta - (nctas_all - ncomm), ncomm);
+        if (cta < ncomm) {
+            Policy::comm_cta(p, cta, ncomm);
             return;
         }
+        cta -= ncomm;
     }
     const int nctas = nctas_all - (Policy::kCommCtas ? p.num_comm_ctas : 0);
 
@@ -189,11 +193,13 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_kernel(const __grid_const
                 ptx::umma_commit(&sm.tmem_full[acc]);    // accumulator complete -> epilogue
             }
         }
+        __syncwarp();
     } else {
         // ===================== epilogue warps =====================
         const int q = warp & 3;                  // TMEM lane quarter this warp may access
         const int epi_tid = (warp - EPI_WARP0) * 32 + lane;
         int local = 0;
+        Policy::prologue(p, cta, epi_tid);
         for (int t = cta; t < ntiles; t += nctas, ++local) {
             const TileCoord tc = Policy::tile(p, t, m_blocks, n_blocks);
             const int acc = local & 1;

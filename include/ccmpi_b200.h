@@ -167,6 +167,43 @@ int ccmpi_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, 
                     int ldc, int a_mn_major, int b_mn_major, int out_dtype, int accumulate,
                     int num_sms, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Fused GEMM + collective kernels (csrc/fused_gemm.cu, csrc/fused_policies.cuh). One kernel
+ * computes tcgen05 tiles AND moves them / their operands over NVLink (peer stores or NVLS
+ * multimem) so the transfer overlaps the math tile by tile. Per-rank operand pointers come as
+ * arrays of `nvr` entries; buffers that peers touch are symmetric-heap offsets. `flag_base`
+ * selects a region of the signal pad's user words, `epoch` must grow by one per launch on a
+ * given (communicator, flag_base) and be the same on every rank; buffers that peers write into
+ * (x_full, slots) should alternate between two copies from launch to launch.
+ * ---------------------------------------------------------------------------------------- */
+
+/* all-gather -> GEMM on the gathered K axis (func_impl.py:76-91 + the consuming FC GEMM):
+ * C[M][N] = [x_0 | ... | x_{n-1}] * B with x_r = rank r's [M][K/n] shard at x_off (row stride
+ * ldx elements); xfull_off: [M][K] staging the peers push into. */
+int ccmpi_fused_ag_gemm(const ccmpi_dev_comm* comms, int nvr, size_t x_off, int ldx, size_t xfull_off,
+                        const void* const* B, void* const* C, int M, int N, int K, int ldb, int ldc,
+                        int b_kn, int out_dtype, int flag_base, unsigned epoch, int num_comm_ctas,
+                        int num_sms, int use_mc, void* stream);
+
+/* GEMM -> reduce-scatter on N (the dx GEMM + func_impl.py:150-187): C[M][N/n] = rank-ordered sum
+ * over ranks of (A*B)[:, own column block]; slots_off: [n][M][N/n] staging (out dtype). */
+int ccmpi_fused_gemm_rs(const ccmpi_dev_comm* comms, int nvr, const void* const* A, const void* const* B,
+                        size_t slots_off, void* const* C, int M, int N, int K, int lda, int ldb, int ldc,
+                        int a_km, int b_kn, int out_dtype, int flag_base, unsigned epoch, int num_sms,
+                        void* stream);
+
+/* GEMM -> all-reduce (row-parallel fc_o / fc2 forward): out_off: symmetric [M][N] result. */
+int ccmpi_fused_gemm_ar(const ccmpi_dev_comm* comms, int nvr, const void* const* A, const void* const* B,
+                        size_t slots_off, size_t out_off, int M, int N, int K, int lda, int ldb, int a_km,
+                        int b_kn, int out_dtype, int flag_base, unsigned epoch, int num_sms, int use_mc,
+                        void* stream);
+
+/* GEMM whose epilogue all-gathers the output on N (the FC GEMM + func_impl.py:94-109):
+ * yfull_off: symmetric [M][N*n]; this rank's A*B lands in column block `rank` on every member. */
+int ccmpi_fused_gemm_ag(const ccmpi_dev_comm* comms, int nvr, const void* const* A, const void* const* B,
+                        size_t yfull_off, int M, int N, int K, int lda, int ldb, int a_km, int b_kn,
+                        int out_dtype, int num_sms, int use_mc, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

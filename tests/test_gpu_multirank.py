@@ -1,0 +1,42 @@
+"""Real multi-GPU runs (one process per GPU, symmetric heap over NVLink). Needs >= 2 GPUs; on a
+1-GPU box only the single-rank device path is exercised."""
+import pytest
+
+from conftest import gpu_count, run_ranks
+
+pytestmark = pytest.mark.gpu
+
+
+def _ok(proc, token):
+    assert proc.returncode == 0, f"rc={proc.returncode}\n--- stdout\n{proc.stdout[-4000:]}\n--- stderr\n{proc.stderr[-3000:]}"
+    assert token in proc.stdout, proc.stdout[-2000:]
+
+
+def _ranks_for_box(wanted):
+    n = gpu_count()
+    if n < 2:
+        pytest.skip("needs at least 2 GPUs")
+    return [k for k in wanted if k <= n]
+
+
+@pytest.mark.parametrize("cuda", [False, True])
+def test_collectives_on_device_plane(cuda):
+    for n in _ranks_for_box([2, 4, 8]):
+        _ok(run_ranks(n, ["tests/workers/w_collectives.py"] + (["--cuda"] if cuda else []), transport="device"),
+            f"COLLECTIVES OK ranks={n} cuda={cuda}")
+
+
+@pytest.mark.parametrize("cuda", [False, True])
+def test_tp_steps_on_device_plane(cuda):
+    for n in _ranks_for_box([4, 8]):
+        _ok(run_ranks(n, ["tests/workers/w_tp_steps.py"] + (["--cuda"] if cuda else []), transport="device"),
+            f"TP STEPS OK ranks={n} cuda={cuda}")
+
+
+def test_single_rank_device_world():
+    if gpu_count() < 1:
+        pytest.skip("needs a GPU")
+    code = ("import torch\nfrom mpi4py import MPI\nc = MPI.COMM_WORLD\n"
+            "x = torch.arange(10, device='cuda'); y = torch.empty_like(x)\n"
+            "c.Allreduce(x, y); assert torch.equal(x, y); print('ONE OK')\n")
+    _ok(run_ranks(1, ["-c", code], transport="device"), "ONE OK")
