@@ -1,0 +1,78 @@
+"""Model families built from the tensor-parallel FC layers.
+
+``TransformerFCBlock`` -- the FC layers of one transformer block in the reference's naming
+(fc_q / fc_k / fc_v / fc_o of ``get_info``, func_impl.py:65-70, plus fc1 / fc2 of BASELINE's
+configs), feature-sharded activations in, feature-sharded activations out. The reference has no
+attention (or any compute); the three projections are mixed by a cheap elementwise gate so every
+weight receives a gradient.
+
+``MLPStack`` -- a plain stack of square FC layers for the data-parallel configuration (1 B
+parameters at 16 x 8192^2).
+
+``TrainStep`` -- forward + backward + DP gradient reduction + SGD in one call.
+"""
+from __future__ import annotations
+
+from typing import List
+
+import torch
+from torch import nn
+
+from ..parallel.dp import GradSink, sgd_step
+from ..parallel.tp_layers import ColumnParallelLinear, RowParallelLinear
+
+
+class TransformerFCBlock(nn.Module):
+    def __init__(self, mp_comm, tokens: int, hidden: int, ffn_mult: int = 4, *, seed: int = 0, num_comm_ctas: int = 0):
+        super().__init__()
+        self.hidden, self.mp = hidden, mp_comm.Get_size()
+        # fc_q, fc_k, fc_v share their input: one gather, one GEMM with the three shards side by side
+        self.fc_qkv = ColumnParallelLinear(mp_comm, tokens, hidden, 3 * hidden, seed=seed + 1, num_comm_ctas=num_comm_ctas)
+        self.fc_o = RowParallelLinear(mp_comm, tokens, hidden, hidden, seed=seed + 2, num_comm_ctas=num_comm_ctas)
+        self.fc1 = ColumnParallelLinear(mp_comm, tokens, hidden, ffn_mult * hidden, seed=seed + 3, num_comm_ctas=num_comm_ctas)
+        self.fc2 = RowParallelLinear(mp_comm, tokens, ffn_mult * hidden, hidden, seed=seed + 4, num_comm_ctas=num_comm_ctas)
+
+    def tp_layers(self) -> List[nn.Module]:
+        return [self.fc_qkv, self.fc_o, self.fc1, self.fc2]
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        q, k, v = self.fc_qkv(x).chunk(3, dim=-1)
+        a = v * torch.sigmoid(q * k)            # stand-in for attention: elementwise, keeps sharding
+        h = x + self.fc_o(a)
+        u = torch.nn.functional.gelu(self.fc1(h), approximate="tanh")
+        return h + self.fc2(u)
+
+
+class MLPStack(nn.Module):
+    def __init__(self, mp_comm, tokens: int, width: int, depth: int, *, seed: int = 0):
+        super().__init__()
+        self.layers = nn.ModuleList(
+            [ColumnParallelLinear(mp_comm, tokens, width, width, seed=seed + i) for i in range(depth)])
+
+    def tp_layers(self) -> List[nn.Module]:
+        return list(self.layers)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        for i, layer in enumerate(self.layers):
+            x = layer(x)
+            if i + 1 < len(self.layers):
+                x = torch.relu(x)
+        return x
+
+
+class TrainStep:
+    """One optimisation step of ``model`` on a 2-D grid: fused-TP forward/backward on ``mp_comm``
+    (inside the layers), bucketed + overlapped gradient all-reduce on ``dp_comm``, SGD."""
+
+    def __init__(self, model, dp_comm, *, lr: float = 1e-3, bucket_mb: int = 64, overlap: bool = True):
+        self.model, self.lr = model, lr
+        self.sink = GradSink(dp_comm, model.tp_layers(), bucket_mb=bucket_mb, overlap=overlap)
+        self.weights = [l.weight.data for l in model.tp_layers()]
+
+    def __call__(self, x: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        y = self.model(x)
+        loss = torch.nn.functional.mse_loss(y.float(), target.float())
+        loss.backward()
+        self.sink.finish()
+        sgd_step(self.weights, self.sink.grads(), self.lr)
+        return loss.detach()

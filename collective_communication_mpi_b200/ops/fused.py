@@ -82,7 +82,13 @@ def gemm_ag_raw(comms, A: List[torch.Tensor], B: List[torch.Tensor], yfull_off: 
 # -------------------------------------------------------------------------------------------------
 # stateful per-communicator contexts
 # -------------------------------------------------------------------------------------------------
-FLAG_SLOT_WORDS = 4096  # three independent flag regions per communicator
+def _ag_flag_words(M: int, n: int) -> int:
+    return n * ((M + 127) // 128)
+
+
+def _rs_flag_words(M: int, chunk: int, n: int) -> int:
+    bn = 256 if chunk % 256 == 0 else 128
+    return ((M + 127) // 128) * (chunk // bn) * n
 
 
 class FusedContext:
@@ -94,14 +100,18 @@ class FusedContext:
         self.heap = self.dev.heap
         self.n = comm.Get_size()
         self.rank = comm.Get_rank()
-        self._next_slot = 0
+        self._next_word = 0
 
-    def new_slot(self) -> int:
-        s = self._next_slot
-        if (s + 1) * FLAG_SLOT_WORDS > N.PAD_USER_WORDS:
-            raise RuntimeError("out of flag regions on this communicator (3 fused-op shapes per communicator)")
-        self._next_slot += 1
-        return s * FLAG_SLOT_WORDS
+    def new_slot(self, words: int) -> int:
+        """Reserve ``words`` flag words of this communicator's signal pad (never released: flag
+        regions of different fused ops must not overlap because each carries its own epochs)."""
+        base = self._next_word
+        words = (words + 15) // 16 * 16
+        if base + words > N.PAD_USER_WORDS:
+            raise RuntimeError(f"signal pad exhausted: {base} + {words} flag words > {N.PAD_USER_WORDS}; "
+                               "share fused-op contexts between layers of the same shape or use fewer tokens per call")
+        self._next_word += words
+        return base
 
 
 def _ctx(comm) -> FusedContext:
@@ -124,7 +134,7 @@ class AllGatherGemm:
         self.M, self.K, self.chunk = M, K, K // n
         self.x_off, self.x = h.empty((M, self.chunk), torch.bfloat16)
         self.xfull = [h.empty((M, K), torch.bfloat16) for _ in range(2)] if n > 1 else [h.empty((8, 8), torch.bfloat16)] * 2
-        self.flag_base = self.ctx.new_slot()
+        self.flag_base = self.ctx.new_slot(_ag_flag_words(M, n))
         self.epoch = 0
         self.num_comm_ctas, self.use_mc = num_comm_ctas, use_mc and self.ctx.dev.has_mc
 
@@ -157,7 +167,7 @@ class GemmReduceScatter:
         h, n = self.ctx.heap, self.ctx.n
         self.M, self.N, self.chunk, self.dtype = M, Nfull, Nfull // n, dtype
         self.slots = [h.empty((n, M, self.chunk), dtype) for _ in range(2)]
-        self.flag_base = self.ctx.new_slot()
+        self.flag_base = self.ctx.new_slot(_rs_flag_words(M, self.chunk, n))
         self.epoch = 0
 
     def __call__(self, a: torch.Tensor, b: torch.Tensor, *, a_km: bool = False, b_kn: bool = False,
@@ -180,7 +190,7 @@ class GemmAllReduce:
         self.M, self.N, self.chunk, self.dtype = M, Nfull, Nfull // n, dtype
         self.slots = [h.empty((n, M, self.chunk), dtype) for _ in range(2)]
         self.outs = [h.empty((M, Nfull), dtype) for _ in range(2)]
-        self.flag_base = self.ctx.new_slot()
+        self.flag_base = self.ctx.new_slot(_rs_flag_words(M, self.chunk, n))
         self.epoch = 0
         self.use_mc = use_mc and self.ctx.dev.has_mc
 

@@ -1,0 +1,169 @@
+"""Tensor-parallel FC layers on the fused kernels, in the reference's activation layout.
+
+The reference keeps activations *feature-sharded*: every MP rank holds ``(b, s, d/mp)`` and the
+communication steps gather / scatter the last axis (func_impl.py:76-187). With the weight
+partitioning of ``get_info`` (func_impl.py:65-70) that gives two layer kinds, both mapping a
+sharded input to a sharded output with exactly ONE fused kernel per GEMM:
+
+``ColumnParallelLinear`` (fc_q / fc_k / fc_v / fc1; weight ``[in, out/mp]``)
+    fwd  ``y_loc = gather(x_loc) @ W``          all-gather -> GEMM   (gather axis = K)
+    bwd  ``dx_loc = rscatter(dy_loc @ W^T)``    GEMM -> reduce-scatter (scatter axis = N)
+         ``dW = gather(x_loc)^T @ dy_loc``      plain GEMM on the gathered x kept from fwd
+
+``RowParallelLinear`` (fc_o / fc2; weight ``[in/mp, out]``)
+    fwd  ``y_loc = rscatter(x_loc @ W)``        GEMM -> reduce-scatter
+    bwd  ``dx_loc = gather(dy_loc) @ W^T``      all-gather -> GEMM
+         ``dW = x_loc^T @ gather(dy_loc)``      plain GEMM on the gathered dy kept from that kernel
+
+(``naive_collect_forward_output`` -- gathering the *output* as well -- is available as
+``gather_output=True``; a following layer would only re-shard it.)
+
+Token count ``M = b*s`` is fixed per layer instance: staging buffers live in the symmetric heap
+and are allocated once. Weights are plain ``[in, out]``-shaped bf16 arrays like the reference's.
+All ranks must build their layers in the same order (symmetric allocation is collective by
+convention).
+"""
+from __future__ import annotations
+
+import math
+from typing import Optional
+
+import torch
+from torch import nn
+
+from ..ops import fused as F
+from ..ops.gemm import gemm, matmul_tn
+
+
+class _ColumnFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, layer):
+        ctx.layer = layer
+        y, x_full = layer._fwd(x, weight)
+        # x_full aliases the symmetric heap, whose views all share one autograd version counter
+        # (any in-place write anywhere in the heap bumps it), so it is kept as a plain attribute;
+        # its lifetime is managed by the layer's double buffering, not by autograd.
+        ctx.x_full = x_full
+        ctx.save_for_backward(weight)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (weight,) = ctx.saved_tensors
+        dx, dw = ctx.layer._bwd(dy.contiguous(), ctx.x_full, weight)
+        ctx.x_full = None
+        return dx, dw, None
+
+
+class _RowFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, layer):
+        ctx.layer = layer
+        ctx.save_for_backward(x, weight)
+        return layer._fwd(x, weight)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight = ctx.saved_tensors
+        dx, dw = ctx.layer._bwd(dy.contiguous(), x, weight)
+        return dx, dw, None
+
+
+def _weight_grad(layer, x, dy):
+    """dW = x^T dy. With a gradient sink attached (``parallel/dp.py``) the GEMM writes straight
+    into the data-parallel bucket in symmetric memory and the reducer is told the bucket entry is
+    ready; autograd then gets ``None`` for the weight."""
+    sink = getattr(layer, "grad_sink", None)
+    if sink is None:
+        return matmul_tn(x, dy, out_dtype=layer.grad_dtype, num_sms=layer.num_sms)
+    matmul_tn(x, dy, out=sink.view_for(layer.weight), num_sms=layer.num_sms)
+    sink.ready(layer.weight)
+    return None
+
+
+def _init_weight(rows: int, cols: int, fan_in: int, device, seed: int) -> nn.Parameter:
+    g = torch.Generator(device=device).manual_seed(seed)
+    w = torch.randn(rows, cols, device=device, generator=g, dtype=torch.float32) * (1.0 / math.sqrt(fan_in))
+    return nn.Parameter(w.to(torch.bfloat16))
+
+
+class ColumnParallelLinear(nn.Module):
+    """``[M, in/mp] -> [M, out/mp]`` (or ``[M, out]`` with ``gather_output``)."""
+
+    def __init__(self, mp_comm, tokens: int, in_features: int, out_features: int, *, gather_output: bool = False,
+                 grad_dtype=torch.bfloat16, seed: int = 0, num_comm_ctas: int = 0):
+        super().__init__()
+        self.comm, self.mp = mp_comm, mp_comm.Get_size()
+        self.M, self.K, self.N = tokens, in_features, out_features // self.mp
+        self.gather_output = gather_output
+        self.grad_dtype = grad_dtype
+        dev = torch.device("cuda", torch.cuda.current_device())
+        self.weight = _init_weight(in_features, self.N, in_features, dev, seed * 1000 + mp_comm.Get_rank())
+        self.ag = F.AllGatherGemm(mp_comm, tokens, in_features, num_comm_ctas=num_comm_ctas)
+        self.rs = F.GemmReduceScatter(mp_comm, tokens, in_features)
+        self.out_ag = F.GemmAllGather(mp_comm, tokens, self.N) if gather_output and self.mp > 1 else None
+        self.num_sms = 0
+
+    def input_buffer(self) -> torch.Tensor:
+        """Write the layer input here (symmetric memory) to skip one device copy."""
+        return self.ag.input_buffer()
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return _ColumnFn.apply(x.reshape(self.M, -1), self.weight, self)
+
+    # -- kernels ---------------------------------------------------------------------------
+    def _fwd(self, x, w):
+        if self.mp == 1:
+            y = gemm(x, w, b_kn=True, num_sms=self.num_sms)
+            return y, x
+        y = self.ag(x, w, b_kn=True, num_sms=self.num_sms)
+        x_full = self.ag.xfull[self.ag.epoch & 1][1]
+        if self.out_ag is not None:
+            # reference semantics (func_impl.py:94-109): also gather the output
+            y = self.out_ag(x_full, w, b_kn=True)
+        return y, x_full
+
+    def _bwd(self, dy, x_full, w):
+        if self.out_ag is not None:
+            r = self.comm.Get_rank()
+            dy = dy[:, r * self.N:(r + 1) * self.N].contiguous()     # func_impl.py:111-147
+        dw = _weight_grad(self, x_full, dy)
+        if self.mp == 1:
+            dx = gemm(dy, w, num_sms=self.num_sms)
+        else:
+            dx = self.rs(dy, w, b_kn=False, num_sms=self.num_sms)
+        return dx, dw
+
+
+class RowParallelLinear(nn.Module):
+    """``[M, in/mp] -> [M, out/mp]``: partial products are reduce-scattered on the feature axis."""
+
+    def __init__(self, mp_comm, tokens: int, in_features: int, out_features: int, *, grad_dtype=torch.bfloat16,
+                 seed: int = 0, num_comm_ctas: int = 0):
+        super().__init__()
+        self.comm, self.mp = mp_comm, mp_comm.Get_size()
+        self.M, self.K, self.N = tokens, in_features // self.mp, out_features
+        self.grad_dtype = grad_dtype
+        dev = torch.device("cuda", torch.cuda.current_device())
+        self.weight = _init_weight(self.K, out_features, in_features, dev, seed * 1000 + mp_comm.Get_rank())
+        self.rs = F.GemmReduceScatter(mp_comm, tokens, out_features)
+        self.ag = F.AllGatherGemm(mp_comm, tokens, out_features, num_comm_ctas=num_comm_ctas)
+        self.num_sms = 0
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return _RowFn.apply(x.reshape(self.M, -1), self.weight, self)
+
+    def _fwd(self, x, w):
+        if self.mp == 1:
+            return gemm(x, w, b_kn=True, num_sms=self.num_sms)
+        return self.rs(x, w, b_kn=True, num_sms=self.num_sms)
+
+    def _bwd(self, dy, x, w):
+        if self.mp == 1:
+            dx = gemm(dy, w, num_sms=self.num_sms)
+            dy_full = dy
+        else:
+            dx = self.ag(dy, w, b_kn=False, num_sms=self.num_sms)
+            dy_full = self.ag.xfull[self.ag.epoch & 1][1]
+        dw = _weight_grad(self, x, dy_full)
+        return dx, dw

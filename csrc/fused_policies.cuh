@@ -42,8 +42,9 @@ __device__ __forceinline__ void cta_rank_barrier(const ccmpi_dev_comm& c, int ct
 //   off0 : symmetric offset of x_local  [M][chunk]   (row stride aux0 elements)
 //   off1 : symmetric offset of x_full   [M][K]       (staging the peers push into)
 //   tmap_a  -> this rank's x_full,  tmap_a2 -> this rank's x_local
-// Communication CTAs push this rank's rows, one 128-row block at a time, into every peer's
-// x_full and then raise ready[rank][m_blk] on that peer. The GEMM walks K starting with the local
+// Communication CTAs push this rank's rows, one 128-row block at a time, into every member's
+// x_full (their own included, so the gathered activation is complete for the backward dW GEMM)
+// and then raise ready[rank][m_blk] on each peer. The GEMM walks K starting with the local
 // chunk (no wait), then chunks (rank+1)%n, ... each gated on its ready flag.
 // ================================================================================================
 struct AgKPolicy : PlainPolicy {
@@ -104,7 +105,7 @@ struct AgKPolicy : PlainPolicy {
                         ptx::multimem_st_v4(c.mc_heap + d[u], v[u]);
                     } else {
 #pragma unroll
-                        for (int s = 1; s < CCMPI_MAX_RANKS; ++s)
+                        for (int s = 0; s < CCMPI_MAX_RANKS; ++s)  // s = 0: own copy, so x_full is whole
                             if (s < c.size) ptx::st_v4(c.heap[(c.rank + s) % c.size] + d[u], v[u]);
                     }
                 }
@@ -116,7 +117,7 @@ struct AgKPolicy : PlainPolicy {
                 if (mc) {
                     ptx::multimem_st_v4(c.mc_heap + d, v);
                 } else {
-                    for (int s = 1; s < c.size; ++s) ptx::st_v4(c.heap[(c.rank + s) % c.size] + d, v);
+                    for (int s = 0; s < c.size; ++s) ptx::st_v4(c.heap[(c.rank + s) % c.size] + d, v);
                 }
             }
             __syncthreads();  // every thread's stores are issued ...

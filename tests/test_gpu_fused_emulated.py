@@ -34,17 +34,18 @@ def test_allgather_gemm_k_gather(emu, M, N, K, b_kn):
     xf = [heap.alloc(M * K * 2) for _ in range(2)]
     xs = [_rand(M, chunk, seed=10 + r) for r in range(nr)]
     ws = [_rand(K, N, seed=20 + r) for r in range(nr)]              # each rank has its own weight shard
-    x_full = torch.cat(xs, dim=1).float()
     for epoch in (1, 2, 3):                                          # repeated launches: flags carry the epoch
         for r in range(nr):
             heap.view(x_off, (M, chunk), BF, rank=r).copy_(xs[r] * epoch)
+        # the oracle sees exactly the bf16 values the kernel sees
+        x_full = torch.cat([heap.view(x_off, (M, chunk), BF, rank=r) for r in range(nr)], dim=1).float()
         outs = [torch.zeros(M, N, device="cuda", dtype=torch.float32) for _ in range(nr)]
         B = [w if b_kn else w.t().contiguous() for w in ws]
         F.ag_gemm_raw(comms, x_off, chunk, xf[epoch & 1], B, outs, M, N, K, b_kn=b_kn, flag_base=0, epoch=epoch,
                       num_comm_ctas=4, use_mc=False)
         torch.cuda.synchronize()
         for r in range(nr):
-            torch.testing.assert_close(outs[r], (x_full * epoch) @ ws[r].float(), rtol=1e-3, atol=2e-2)
+            torch.testing.assert_close(outs[r], x_full @ ws[r].float(), rtol=1e-3, atol=2e-2)
 
 
 @pytest.mark.parametrize("M,chunk,K,b_kn,dt", [(256, 256, 512, False, BF), (384, 128, 256, False, torch.float32),

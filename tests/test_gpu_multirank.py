@@ -40,3 +40,16 @@ def test_single_rank_device_world():
             "x = torch.arange(10, device='cuda'); y = torch.empty_like(x)\n"
             "c.Allreduce(x, y); assert torch.equal(x, y); print('ONE OK')\n")
     _ok(run_ranks(1, ["-c", code], transport="device"), "ONE OK")
+
+
+@pytest.mark.parametrize("mp,dp", [(2, 1), (1, 2), (2, 2), (4, 2), (2, 4), (8, 1)])
+def test_tp_layers_and_train_step_match_dense_model(mp, dp):
+    if gpu_count() < mp * dp:
+        pytest.skip(f"needs {mp * dp} GPUs")
+    _ok(run_ranks(mp * dp, ["tests/workers/w_layers.py", str(mp), str(dp)], transport="device"), f"LAYERS OK mp={mp} dp={dp}")
+
+
+def test_single_gpu_train_step():
+    if gpu_count() < 1:
+        pytest.skip("needs a GPU")
+    _ok(run_ranks(1, ["tests/workers/w_layers.py", "1", "1"], transport="device"), "LAYERS OK mp=1 dp=1")

@@ -1,0 +1,102 @@
+"""Rank-side check of the tensor-parallel layers / model / train step against a dense fp32
+PyTorch model assembled from the gathered weight shards. Args: MP DP."""
+import sys
+
+import torch
+
+from mpi4py import MPI
+from model.func_impl import get_info
+from data.data_parallel_preprocess import split_data
+from collective_communication_mpi_b200.models import TrainStep, TransformerFCBlock
+
+mp, dp = int(sys.argv[1]), int(sys.argv[2])
+world = MPI.COMM_WORLD
+rank, n = world.Get_rank(), world.Get_size()
+assert n == mp * dp
+torch.cuda.set_device(rank)
+mp_idx, dp_idx, mp_comm, dp_comm, _, _ = get_info(comm=world, rank=rank, mp_size=mp, dp_size=dp, fc_layer="fc_q",
+                                                  in_dim=512, out_dim=512)
+H, TOK = 512, 256
+model = TransformerFCBlock(mp_comm, TOK, H, ffn_mult=4, seed=7, num_comm_ctas=2)
+
+# global batch: dp replicas x TOK tokens, feature-sharded over mp
+g = torch.Generator().manual_seed(123)
+X = torch.randn(dp * TOK, H, generator=g) * 0.5
+T = torch.randn(dp * TOK, H, generator=g) * 0.5
+xs, ts = split_data(X, T, mp_size=mp, dp_size=dp, rank=rank)
+sh = H // mp
+x_loc = xs[:, mp_idx * sh:(mp_idx + 1) * sh].contiguous().cuda().bfloat16()
+t_loc = ts[:, mp_idx * sh:(mp_idx + 1) * sh].contiguous().cuda().bfloat16()
+
+
+def full_weight(layer, axis):
+    parts = mp_comm.allgather(layer.weight.detach().float().cpu())
+    return torch.cat(list(parts), dim=axis).cuda()
+
+
+Wqkv_parts = mp_comm.allgather(model.fc_qkv.weight.detach().float().cpu())   # each [H, 3H/mp] = q|k|v shards
+Wo, W1, W2 = full_weight(model.fc_o, 0), full_weight(model.fc1, 1), full_weight(model.fc2, 0)
+
+
+def dense_forward(x_full):
+    """Same math on unsharded fp32 tensors; q/k/v columns are interleaved per rank like the shards."""
+    outs = []
+    for r in range(mp):
+        q, k, v = (x_full @ Wqkv_parts[r].cuda()).chunk(3, dim=-1)
+        outs.append(v * torch.sigmoid(q * k))
+    a = torch.cat(outs, dim=-1)
+    h = x_full + a @ Wo
+    u = torch.nn.functional.gelu(h @ W1, approximate="tanh")
+    return h + u @ W2
+
+
+x_full = xs.cuda().float().bfloat16().float()
+ref = dense_forward(x_full)
+y = model(x_loc)
+torch.cuda.synchronize()
+got = y.float()
+want = ref[:, mp_idx * sh:(mp_idx + 1) * sh]
+err = (got - want).abs().max().item()
+assert err < 0.06 * max(1.0, want.abs().max().item()), f"forward mismatch {err}"
+
+# ---- one training step: gradients (averaged over dp) vs autograd on the dense model ------------
+before = [l.weight.detach().clone() for l in model.tp_layers()]
+step = TrainStep(model, dp_comm, lr=0.5, bucket_mb=1)
+loss = step(x_loc, t_loc)
+torch.cuda.synchronize()
+
+params = [p.clone().requires_grad_(True) for p in [*[w.cuda() for w in Wqkv_parts], Wo, W1, W2]]
+
+
+def dense_loss(x_full, t_full):
+    outs = []
+    for r in range(mp):
+        q, k, v = (x_full @ params[r]).chunk(3, dim=-1)
+        outs.append(v * torch.sigmoid(q * k))
+    a = torch.cat(outs, dim=-1)
+    h = x_full + a @ params[mp]
+    u = torch.nn.functional.gelu(h @ params[mp + 1], approximate="tanh")
+    yy = h + u @ params[mp + 2]
+    # every rank's loss is the mean over ITS shard; the model-parallel sum of those is mp x the
+    # mean over the full width
+    return sum(torch.nn.functional.mse_loss(yy[:, r * sh:(r + 1) * sh], t_full[:, r * sh:(r + 1) * sh]) for r in range(mp))
+
+
+total = 0.0
+for d in range(dp):
+    xd = X[d * TOK:(d + 1) * TOK].cuda().bfloat16().float()
+    td = T[d * TOK:(d + 1) * TOK].cuda().bfloat16().float()
+    total = total + dense_loss(xd, td) / dp
+total.backward()
+g_qkv = params[mp_idx].grad
+g_o = params[mp].grad[mp_idx * sh:(mp_idx + 1) * sh]
+g_1 = params[mp + 1].grad[:, mp_idx * (4 * H // mp):(mp_idx + 1) * (4 * H // mp)]
+g_2 = params[mp + 2].grad[mp_idx * (4 * H // mp):(mp_idx + 1) * (4 * H // mp)]
+for name, layer, w0, gref in zip(("qkv", "o", "fc1", "fc2"), model.tp_layers(), before, (g_qkv, g_o, g_1, g_2)):
+    g_used = (w0.float() - layer.weight.detach().float()) / 0.5          # what SGD applied
+    scale = gref.abs().max().item()
+    e = (g_used - gref).abs().max().item()
+    assert e < 0.08 * scale + 2e-3, f"{name}: grad mismatch {e} (scale {scale})"
+world.Barrier()
+if rank == 0:
+    print(f"LAYERS OK mp={mp} dp={dp} loss={loss.item():.4f} ar_launches={step.sink.launches}")
