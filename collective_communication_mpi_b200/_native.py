@@ -47,6 +47,15 @@ class NativeError(RuntimeError):
     pass
 
 
+# Number of kernels of THIS library launched by this process (every python wrapper that ends in a
+# kernel launch bumps it); bench.py reports the count inside its timed region.
+LAUNCHES = [0]
+
+
+def count_launch(n: int = 1) -> None:
+    LAUNCHES[0] += n
+
+
 _lock = threading.Lock()
 _dev = None
 _host = None

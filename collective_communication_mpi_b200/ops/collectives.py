@@ -57,6 +57,7 @@ def _sp(stream) -> C.c_void_p:
 def barrier(comms, stream=None):
     a, n = _arr(comms)
     N.check(N.device_lib().ccmpi_barrier(a, n, _sp(stream)), "ccmpi_barrier")
+    N.count_launch()
 
 
 def allreduce(comms, dtype: int, op: int, src_off: int, dst_off: int, count: int, *, tmp_off: int = 0,
@@ -64,6 +65,7 @@ def allreduce(comms, dtype: int, op: int, src_off: int, dst_off: int, count: int
     a, n = _arr(comms)
     N.check(N.device_lib().ccmpi_allreduce(a, n, algo, dtype, op, src_off, dst_off, tmp_off, count,
                                            C.c_float(scale), out_dtype, max_blocks, _sp(stream)), "ccmpi_allreduce")
+    N.count_launch()
 
 
 def allgather(comms, src_off: int, dst_off: int, rows: int, row_bytes: int, src_row_stride: int,
@@ -71,6 +73,7 @@ def allgather(comms, src_off: int, dst_off: int, rows: int, row_bytes: int, src_
     a, n = _arr(comms)
     N.check(N.device_lib().ccmpi_allgather(a, n, src_off, dst_off, rows, row_bytes, src_row_stride,
                                            dst_row_stride, int(use_mc), max_blocks, _sp(stream)), "ccmpi_allgather")
+    N.count_launch()
 
 
 def reduce_scatter(comms, dtype: int, op: int, src_off: int, dst_off: int, rows: int, row_elems: int,
@@ -80,6 +83,7 @@ def reduce_scatter(comms, dtype: int, op: int, src_off: int, dst_off: int, rows:
     N.check(N.device_lib().ccmpi_reduce_scatter(a, n, dtype, op, src_off, dst_off, rows, row_elems,
                                                 src_row_stride, dst_row_stride, int(use_mc), max_blocks,
                                                 _sp(stream)), "ccmpi_reduce_scatter")
+    N.count_launch()
 
 
 def alltoall(comms, src_off: int, dst_off: int, seg_bytes: int, *, staggered: bool = False, max_blocks: int = 0,
@@ -87,13 +91,16 @@ def alltoall(comms, src_off: int, dst_off: int, seg_bytes: int, *, staggered: bo
     a, n = _arr(comms)
     N.check(N.device_lib().ccmpi_alltoall(a, n, src_off, dst_off, seg_bytes, int(staggered), max_blocks,
                                           _sp(stream)), "ccmpi_alltoall")
+    N.count_launch()
 
 
 def put_signal(comm: N.DevComm, peer: int, src_off: int, dst_off: int, nbytes: int, flag: int, stream=None):
     a, n = _arr([comm])
     N.check(N.device_lib().ccmpi_put_signal(a, n, peer, src_off, dst_off, nbytes, flag, _sp(stream)), "ccmpi_put_signal")
+    N.count_launch()
 
 
 def wait_signal(comm: N.DevComm, peer: int, flag: int, stream=None):
     a, n = _arr([comm])
     N.check(N.device_lib().ccmpi_wait_signal(a, n, peer, flag, _sp(stream)), "ccmpi_wait_signal")
+    N.count_launch()

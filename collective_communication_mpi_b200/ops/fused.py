@@ -47,6 +47,7 @@ def ag_gemm_raw(comms, x_off: int, ldx: int, xfull_off: int, B: List[torch.Tenso
                                             B[0].stride(0), Cout[0].stride(0), int(b_kn), _OUT[Cout[0].dtype],
                                             flag_base, epoch, num_comm_ctas, num_sms, int(use_mc), _sp(stream))
     N.check(rc, "ccmpi_fused_ag_gemm")
+    N.count_launch()
 
 
 def gemm_rs_raw(comms, A: List[torch.Tensor], B: List[torch.Tensor], slots_off: int, Cout: List[torch.Tensor],
@@ -57,6 +58,7 @@ def gemm_rs_raw(comms, A: List[torch.Tensor], B: List[torch.Tensor], slots_off: 
                                             A[0].stride(0), B[0].stride(0), Cout[0].stride(0), int(a_km), int(b_kn),
                                             _OUT[Cout[0].dtype], flag_base, epoch, num_sms, _sp(stream))
     N.check(rc, "ccmpi_fused_gemm_rs")
+    N.count_launch()
 
 
 def gemm_ar_raw(comms, A: List[torch.Tensor], B: List[torch.Tensor], slots_off: int, out_off: int, M: int, Nn: int,
@@ -67,6 +69,7 @@ def gemm_ar_raw(comms, A: List[torch.Tensor], B: List[torch.Tensor], slots_off: 
                                             B[0].stride(0), int(a_km), int(b_kn), _OUT[out_dtype], flag_base, epoch,
                                             num_sms, int(use_mc), _sp(stream))
     N.check(rc, "ccmpi_fused_gemm_ar")
+    N.count_launch()
 
 
 def gemm_ag_raw(comms, A: List[torch.Tensor], B: List[torch.Tensor], yfull_off: int, M: int, Nn: int, K: int, *,
@@ -77,6 +80,7 @@ def gemm_ag_raw(comms, A: List[torch.Tensor], B: List[torch.Tensor], yfull_off: 
                                             B[0].stride(0), int(a_km), int(b_kn), _OUT[out_dtype], num_sms,
                                             int(use_mc), _sp(stream))
     N.check(rc, "ccmpi_fused_gemm_ag")
+    N.count_launch()
 
 
 # -------------------------------------------------------------------------------------------------

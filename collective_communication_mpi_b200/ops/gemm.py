@@ -72,6 +72,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_km: bool = False, b_kn: bool = F
         N.BF16 if out_dtype == torch.bfloat16 else N.F32, int(accumulate), int(num_sms),
         C.c_void_p(_stream_ptr(stream)))
     N.check(rc, "ccmpi_gemm_bf16")
+    N.count_launch()
     return out
 
 
