@@ -201,6 +201,9 @@ def run_gpu(args, impl: str):
             "gemm_tflops_per_gpu": round(tflops_per_gpu, 1),
         })
     comm.Barrier()
+    if impl == "nccl":
+        import torch.distributed as dist
+        dist.destroy_process_group()
 
 
 def main():

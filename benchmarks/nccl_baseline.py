@@ -66,6 +66,9 @@ class _Row(torch.autograd.Function):
 class NcclTrainStep:
     def __init__(self, rank, world, mp, dp, tokens, hidden, ffn_mult, lr=1e-4):
         if not dist.is_initialized():
+            import os
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            os.environ.setdefault("MASTER_PORT", "29531")
             dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", torch.cuda.current_device()))
         self.mp, self.dp, self.lr = mp, dp, lr
         self.mp_group = self.dp_group = None
