@@ -204,6 +204,25 @@ int ccmpi_fused_gemm_ag(const ccmpi_dev_comm* comms, int nvr, const void* const*
                         size_t yfull_off, int M, int N, int K, int lda, int ldb, int a_km, int b_kn,
                         int out_dtype, int num_sms, int use_mc, void* stream);
 
+/* No counterpart in the reference: it never allocates device memory because it has no device
+ * code. This is the GEMM -> reduce-scatter kernel of ccmpi_fused_gemm_rs for a ONE-GPU
+ * communicator (C[M][N] = A * B), for callers that must not allocate device memory when they
+ * call -- servers that gave the GPU to their own arena, plug-ins under another framework's
+ * memory planner, loops that cannot take cudaMalloc's device-wide synchronisation. Its staging
+ * buffer and flag words live in a static device array inside the library (64 KiB + 16 MiB, held
+ * by every GPU that loads the library until the process exits), so the caller passes only A, B
+ * and C; nothing is allocated, by this call or by anything it uses.
+ *   - M * N * sizeof(output element) must be <= ccmpi_gemm_rs_local_noalloc_max_bytes() (16 MiB);
+ *     larger problems return CCMPI_ERR_LIMIT. N must be a multiple of 128.
+ *   - All calls on a device share the array and it keeps the previous call's contents; each call
+ *     zeroes the flag words on `stream` first. Calls that overlap on the GPU race on it.
+ *   - The first call on each device resolves the array's device address; make that call before
+ *     any stream capture on that device.
+ * Operand layout flags as in ccmpi_gemm_bf16. */
+int ccmpi_gemm_rs_local_noalloc(const void* A, const void* B, void* C, int M, int N, int K, int lda,
+                                int ldb, int ldc, int a_km, int b_kn, int out_dtype, void* stream);
+size_t ccmpi_gemm_rs_local_noalloc_max_bytes(void);
+
 #ifdef __cplusplus
 }
 #endif
