@@ -54,6 +54,12 @@ struct AgKPolicy : PlainPolicy {
         return p.flag_base + src * ((p.M + BM - 1) / BM) + m_blk;
     }
 
+    __device__ static int kcoord(const RankParams& p, int it) {
+        const int per = p.chunk / BK;
+        const int ci = it / per;
+        return ((p.comm.rank + ci) % p.comm.size) * p.chunk + (it - ci * per) * BK;
+    }
+
     __device__ static void kblock(const RankParams& p, const TileCoord& tc, int it, int& k0, const CUtensorMap*& ta,
                                   int& a_k0, int& a_m0) {
         const ccmpi_dev_comm& c = p.comm;

@@ -67,6 +67,8 @@ struct PlainPolicy {
         a_k0 = k0;
         a_m0 = tc.m_blk * BM;
     }
+    // K coordinate of iteration `it` (what kblock would use for B), without any waiting
+    __device__ static int kcoord(const RankParams& p, int it) { return it * BK; }
     template <typename OutT>
     __device__ static void store(const RankParams& p, const TileCoord& tc, int row, int col0, const uint32_t (&v)[32]) {
         if (row < p.M) {

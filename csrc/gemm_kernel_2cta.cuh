@@ -1,0 +1,230 @@
+// CTA-pair (cta_group::2) variant of the persistent tcgen05 GEMM kernel.
+//
+// Two CTAs of a 2-CTA cluster (the two SMs of a TPC) compute one 256 x BN tile: each loads ITS
+// 128 rows of A and ITS half of the B tile, the leader's elected thread issues
+// tcgen05.mma.cta_group::2 (M = 256) which reads both CTAs' shared memory and writes each CTA's
+// 128 accumulator rows into that CTA's own TMEM. Per unit of MMA work a CTA pulls 2/3 of the
+// bytes the single-CTA kernel needs (L2 -> SM traffic is what bounds the 128 x 256 single-CTA
+// tile on B200), and the shared-memory read rate per SM is halved.
+//
+// From a policy's point of view nothing changes: every CTA still owns a 128-row m-block and a
+// full BN-wide n-block -- CTA r of a pair gets m_blk = 2*pair_m + r -- so the fused-collective
+// policies (gather flags per m-block, per-tile scatter flags, per-CTA rank barriers) are reused
+// as they are.
+//
+// Barrier topology (per stage s / accumulator a):
+//   full[s]        lives in the leader; 2 arrivals (leader's expect_tx + peer's remote arrive),
+//                  transaction bytes from BOTH CTAs' TMA loads (their mbarrier operand is masked
+//                  to the leader's copy)
+//   empty[s]       one per CTA; tcgen05.commit.multicast arrives on both when the MMAs retire
+//   tmem_full[a]   one per CTA; multicast commit
+//   tmem_empty[a]  lives in the leader; 8 arrivals (4 epilogue warps of each CTA)
+#pragma once
+#include "gemm_kernel.cuh"
+
+namespace gemm {
+
+template <int BN>
+struct Cfg2 {
+    static constexpr int A_BYTES = BM * BK * 2;          // this CTA's 128 rows of A
+    static constexpr int B_ROWS = BN / 2;                // this CTA's half of the B tile
+    static constexpr int B_BYTES = B_ROWS * BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int STAGES = (200 * 1024) / STAGE_BYTES > 8 ? 8 : (200 * 1024) / STAGE_BYTES;
+    static constexpr int TMEM_COLS = (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+    static_assert(BN % 128 == 0 && BN <= 256, "BN must be 128 or 256 for CTA pairs");
+};
+
+template <int BN, bool A_MN, bool B_MN, typename OutT, typename Policy>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+gemm_kernel_2cta(const __grid_constant__ Launch lp) {
+    using C = Cfg2<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(base + C::STAGES * C::STAGE_BYTES);
+    uint64_t* full = bars;
+    uint64_t* empty = bars + C::STAGES;
+    uint64_t* tmem_full = empty + C::STAGES;
+    uint64_t* tmem_empty = tmem_full + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+    auto smem_a = [&](int s) { return base + s * C::STAGE_BYTES; };
+    auto smem_b = [&](int s) { return base + s * C::STAGE_BYTES + C::A_BYTES; };
+
+    // clusters are consecutive block pairs; emulated ranks interleave at pair granularity
+    const int nvr = lp.nvr;
+    const int pair_global = blockIdx.x >> 1;
+    const int vr = pair_global % nvr;
+    const uint32_t cta_rank = ptx::cluster_ctarank();
+    int cta = (pair_global / nvr) * 2 + (int)cta_rank;
+    const int nctas_all = gridDim.x / nvr;
+    const RankParams& p = lp.r[vr];
+    const bool leader = cta_rank == 0;
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if constexpr (Policy::kCommCtas) {
+        const int ncomm = p.num_comm_ctas;  // even: whole clusters
+        if (cta < ncomm) {
+            Policy::comm_cta(p, cta, ncomm);
+            return;
+        }
+        cta -= ncomm;
+    }
+    const int nctas = nctas_all - (Policy::kCommCtas ? p.num_comm_ctas : 0);
+    const int pair = cta >> 1, npairs = nctas >> 1;
+
+    const int m_blocks = (p.M + BM - 1) / BM;
+    const int m_pairs = (m_blocks + 1) / 2;
+    const int n_blocks = (p.N + BN - 1) / BN;
+    const int k_blocks = (p.K + BK - 1) / BK;
+    const int ntiles = Policy::num_tiles(p, m_pairs, n_blocks);
+
+    auto my_tile = [&](int t) {
+        TileCoord tc = Policy::tile(p, t, m_pairs, n_blocks);
+        tc.m_blk = tc.m_blk * 2 + (int)cta_rank;
+        return tc;
+    };
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tmap(&p.tmap_a);
+        ptx::prefetch_tmap(&p.tmap_a2);
+        ptx::prefetch_tmap(&p.tmap_b);
+#pragma unroll
+        for (int s = 0; s < C::STAGES; ++s) {
+            ptx::mbar_init(&full[s], 2);
+            ptx::mbar_init(&empty[s], 1);
+        }
+        ptx::mbar_init(&tmem_full[0], 1);
+        ptx::mbar_init(&tmem_full[1], 1);
+        ptx::mbar_init(&tmem_empty[0], 8);
+        ptx::mbar_init(&tmem_empty[1], 8);
+        ptx::fence_mbar_init();
+    }
+    if (warp == 1) ptx::tmem_alloc_2sm<C::TMEM_COLS>(tmem_slot);
+    ptx::tc_fence_before();
+    ptx::cluster_sync();  // both CTAs' barriers exist before anyone signals across the pair
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================== TMA producer (both CTAs) =====================
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int t = pair; t < ntiles; t += npairs) {
+                const TileCoord tc = my_tile(t);
+                const bool valid = tc.m_blk < m_blocks;
+                for (int it = 0; it < k_blocks; ++it) {
+                    int k0, a_k0, a_m0;
+                    const CUtensorMap* ta;
+                    if (valid) {
+                        Policy::kblock(p, tc, it, k0, ta, a_k0, a_m0);
+                    } else {
+                        // phantom m-block of an odd tail: its rows are out of range, TMA zero-fills
+                        // them and there is nothing to wait for -- but the B half it loads feeds the
+                        // partner's real rows, so K must advance in the policy's order
+                        k0 = Policy::kcoord(p, it);
+                        ta = &p.tmap_a;
+                        a_k0 = k0;
+                        a_m0 = tc.m_blk * BM;
+                    }
+                    ptx::mbar_wait(&empty[stage], phase ^ 1, 100 + stage);
+                    if (leader) ptx::mbar_arrive_expect_tx(&full[stage], 2 * C::STAGE_BYTES);
+                    else ptx::mbar_arrive_cluster(&full[stage], 0);
+                    if constexpr (!A_MN) {
+                        ptx::tma_load_2d_2sm(smem_a(stage), ta, &full[stage], a_k0, a_m0);
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < BM / 64; ++c)
+                            ptx::tma_load_2d_2sm(smem_a(stage) + c * (BK * 128), ta, &full[stage], a_m0 + c * 64, a_k0);
+                    }
+                    const int n0 = tc.n_blk * BN + (int)cta_rank * C::B_ROWS;
+                    if constexpr (!B_MN) {
+                        ptx::tma_load_2d_2sm(smem_b(stage), &p.tmap_b, &full[stage], k0, n0);
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < C::B_ROWS / 64; ++c)
+                            ptx::tma_load_2d_2sm(smem_b(stage) + c * (BK * 128), &p.tmap_b, &full[stage], n0 + c * 64, k0);
+                    }
+                    if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ===================== MMA issuer (leader CTA only) =====================
+        if (leader && lane == 0) {
+            constexpr uint32_t idesc = ptx::umma_idesc(1, 1, A_MN, B_MN, 2 * BM, BN);
+            int stage = 0;
+            uint32_t phase = 0;
+            int local = 0;
+            for (int t = pair; t < ntiles; t += npairs, ++local) {
+                const int acc = local & 1;
+                const uint32_t acc_phase = (local >> 1) & 1;
+                ptx::mbar_wait(&tmem_empty[acc], acc_phase ^ 1, 200 + acc);
+                ptx::tc_fence_after();
+                const uint32_t tmem_d = tmem_base + acc * BN;
+                for (int it = 0; it < k_blocks; ++it) {
+                    ptx::mbar_wait(&full[stage], phase, 300 + stage);
+                    ptx::tc_fence_after();
+                    const uint32_t a_addr = ptx::smem_u32(smem_a(stage));
+                    const uint32_t b_addr = ptx::smem_u32(smem_b(stage));
+#pragma unroll
+                    for (int ks = 0; ks < BK / UMMA_K; ++ks) {
+                        ptx::umma_f16_ss_2sm(tmem_d, operand_desc<A_MN>(a_addr, ks), operand_desc<B_MN>(b_addr, ks),
+                                             idesc, (it | ks) != 0 ? 1u : 0u);
+                    }
+                    ptx::umma_commit_2sm(&empty[stage], 0b11);
+                    if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                }
+                ptx::umma_commit_2sm(&tmem_full[acc], 0b11);
+            }
+        }
+        __syncwarp();
+    } else {
+        // ===================== epilogue warps (both CTAs, own 128 rows) =====================
+        const int q = warp & 3;
+        const int epi_tid = (warp - EPI_WARP0) * 32 + lane;
+        int local = 0;
+        Policy::prologue(p, cta, epi_tid);
+        for (int t = pair; t < ntiles; t += npairs, ++local) {
+            const TileCoord tc = my_tile(t);
+            const bool valid = tc.m_blk < m_blocks;
+            const int acc = local & 1;
+            const uint32_t acc_phase = (local >> 1) & 1;
+            ptx::mbar_wait(&tmem_full[acc], acc_phase, 400 + acc);
+            ptx::tc_fence_after();
+            const int row = tc.m_blk * BM + q * 32 + lane;
+            const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + acc * BN;
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                uint32_t v[32];
+                ptx::tmem_ld_32x32b_x32(taddr + c, v);
+                ptx::tmem_ld_wait();
+                if (c + 32 >= BN) {
+                    ptx::tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) {
+                        if (leader) ptx::mbar_arrive(&tmem_empty[acc]);
+                        else ptx::mbar_arrive_cluster(&tmem_empty[acc], 0);
+                    }
+                }
+                if (valid) Policy::template store<OutT>(p, tc, row, tc.n_blk * BN + c, v);
+            }
+            if (valid) Policy::tile_done(p, tc, epi_tid);
+        }
+        Policy::template tail<OutT>(p, cta, nctas, epi_tid);
+    }
+
+    // ---- teardown: nobody leaves (or frees TMEM) while the partner may still read its smem ----
+    ptx::tc_fence_before();
+    ptx::cluster_sync();
+    if (warp == 1) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc_2sm<C::TMEM_COLS>(tmem_base);
+    }
+}
+
+}  // namespace gemm

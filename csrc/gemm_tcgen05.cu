@@ -4,13 +4,15 @@
 //     y = x W        (A K-major,  B stored [K][N] -> b_mn_major)
 //     dx = dy W^T    (A K-major,  B stored [N][K] -> K-major)
 //     dW = x^T dy    (A stored [K][M] -> a_mn_major, B stored [K][N] -> b_mn_major)
+#include <cstdlib>
+
 #include "gemm_host.h"
 
 namespace gemm {
 
 // Fill the three TMA descriptors of a rank. A2 (alternate A source) defaults to A.
 int fill_tmaps(RankParams& rp, const void* A, const void* A2, const void* B, int M, int N, int K, long long lda,
-               long long lda2, long long ldb, bool a_mn, bool b_mn, int BN, int a2_rows, int a2_cols) {
+               long long lda2, long long ldb, bool a_mn, bool b_mn, int b_box_rows, int a2_rows, int a2_cols) {
     int rc;
     if (!a_mn) {
         rc = ccmpi::make_tmap_2d(&rp.tmap_a, A, 2, M, K, lda, BM, BK);
@@ -23,7 +25,7 @@ int fill_tmaps(RankParams& rp, const void* A, const void* A2, const void* B, int
     }
     if (rc) return rc;
     if (!b_mn)
-        rc = ccmpi::make_tmap_2d(&rp.tmap_b, B, 2, N, K, ldb, BN, BK);
+        rc = ccmpi::make_tmap_2d(&rp.tmap_b, B, 2, N, K, ldb, b_box_rows, BK);
     else
         rc = ccmpi::make_tmap_2d(&rp.tmap_b, B, 2, K, N, ldb, BK, 64);
     return rc;
@@ -39,6 +41,14 @@ int pick_bn(int M, int N, int sms) {
     };
     if (N <= 128) return 128;
     return (eff(256) >= 0.92 * eff(128)) ? 256 : 128;
+}
+
+bool use_2cta() {
+    static const bool v = [] {
+        const char* e = getenv("CCMPI_GEMM_1CTA");
+        return !(e && e[0] == '1');
+    }();
+    return v;
 }
 
 int check_shapes(int M, int N, int K, long long lda, long long ldb, long long ldc, int out_dtype) {
@@ -59,12 +69,13 @@ extern "C" int ccmpi_gemm_bf16(const void* A, const void* B, void* C, int M, int
     if (rc) return rc;
     CCMPI_REQUIRE(!accumulate || out_dtype == CCMPI_F32, "accumulate needs an fp32 output");
     const int sms = num_sms > 0 ? num_sms : ccmpi::device_sm_count();
-    const int BN = pick_bn(M, N, sms);
+    const bool pairs = use_2cta() && sms >= 2;
+    const int BN = pick_bn(M, N, pairs ? sms / 2 * 2 : sms);
     Launch lp;
     memset(&lp, 0, sizeof(lp));
     lp.nvr = 1;
     RankParams& rp = lp.r[0];
-    rc = fill_tmaps(rp, A, A, B, M, N, K, lda, lda, ldb, a_mn_major != 0, b_mn_major != 0, BN,
+    rc = fill_tmaps(rp, A, A, B, M, N, K, lda, lda, ldb, a_mn_major != 0, b_mn_major != 0, pairs ? BN / 2 : BN,
                     a_mn_major ? K : M, a_mn_major ? M : K);
     if (rc) return rc;
     rp.C = C;
@@ -73,6 +84,11 @@ extern "C" int ccmpi_gemm_bf16(const void* A, const void* B, void* C, int M, int
     rp.N = N;
     rp.K = K;
     rp.accumulate = accumulate;
+    if (pairs) {
+        const int pair_tiles = (((M + BM - 1) / BM + 1) / 2) * ((N + BN - 1) / BN);
+        const int npairs = pair_tiles < sms / 2 ? pair_tiles : sms / 2;
+        return dispatch2<PlainPolicy>(lp, BN, a_mn_major != 0, b_mn_major != 0, out_dtype, 2 * npairs, (cudaStream_t)stream, false);
+    }
     const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
     const int grid = tiles < sms ? tiles : sms;
     return dispatch<PlainPolicy>(lp, BN, a_mn_major != 0, b_mn_major != 0, out_dtype, grid, (cudaStream_t)stream, false);
