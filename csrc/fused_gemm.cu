@@ -3,6 +3,8 @@
 // Each entry takes `nvr` device communicators (1 in production; >1 = emulated ranks inside one
 // cooperative launch on one GPU, used by the single-GPU tests) and, per rank, the local operand
 // pointers. Buffers that peers touch are given as symmetric-heap offsets.
+#include <cstdlib>
+
 #include "fused_policies.cuh"
 #include "gemm_host.h"
 
@@ -43,12 +45,18 @@ extern "C" int ccmpi_fused_ag_gemm(const ccmpi_dev_comm* comms, int nvr, size_t 
     CCMPI_REQUIRE((x_off | xfull_off) % 16 == 0, "symmetric offsets must be 16-byte aligned");
     const int chunk = K / n;
     const int sms = (num_sms > 0 ? num_sms : ccmpi::device_sm_count());
-    int ncomm = n > 1 ? (num_comm_ctas > 0 ? num_comm_ctas : 16) : 0;
+    const bool pairs = use_2cta();
+    // the CTA-pair kernel's comm CTAs drive the bulk-copy engine (~190 KiB in flight each): few are
+    // enough; the single-CTA kernel's register-copy loop needs more of them
+    static const int env_comm = [] { const char* e = getenv("CCMPI_AG_COMM_CTAS"); return e ? atoi(e) : 0; }();
+    int ncomm = n > 1 ? (num_comm_ctas > 0 ? num_comm_ctas : (env_comm > 0 ? env_comm : (pairs ? 4 : 16))) : 0;
     if (ncomm > m_blocks) ncomm = m_blocks;
-    const int per_rank_budget = sms / nvr;
+    if (pairs) ncomm = (ncomm + 1) & ~1;                 // whole clusters
+    int per_rank_budget = sms / nvr;
+    if (pairs) per_rank_budget &= ~1;
     CCMPI_REQUIRE(per_rank_budget > ncomm, "not enough SMs (%d per rank) for %d communication CTAs", per_rank_budget, ncomm);
     const int BN = pick_bn(M, N, per_rank_budget - ncomm);
-    const int tiles = m_blocks * ((N + BN - 1) / BN);
+    const int tiles = pairs ? 2 * (((m_blocks + 1) / 2) * ((N + BN - 1) / BN)) : m_blocks * ((N + BN - 1) / BN);
     int gemm_ctas = per_rank_budget - ncomm;
     if (gemm_ctas > tiles) gemm_ctas = tiles;
     Launch lp;
@@ -59,7 +67,7 @@ extern "C" int ccmpi_fused_ag_gemm(const ccmpi_dev_comm* comms, int nvr, size_t 
         const ccmpi_dev_comm& c = comms[v];
         const void* xfull = c.heap[c.rank] + xfull_off;
         const void* xloc = c.heap[c.rank] + x_off;
-        rc = fill_tmaps(rp, xfull, xloc, B[v], M, N, K, K, ldx, ldb, false, b_kn != 0, BN, M, chunk);
+        rc = fill_tmaps(rp, xfull, xloc, B[v], M, N, K, K, ldx, ldb, false, b_kn != 0, pairs ? BN / 2 : BN, M, chunk);
         if (rc) return rc;
         rp.C = C[v];
         rp.ldc = ldc;
@@ -73,6 +81,8 @@ extern "C" int ccmpi_fused_ag_gemm(const ccmpi_dev_comm* comms, int nvr, size_t 
         rp.aux0 = ldx;
         rp.aux1 = use_mc;
     }
+    if (pairs)
+        return dispatch2<AgKPolicy>(lp, BN, false, b_kn != 0, out_dtype, (gemm_ctas + ncomm) * nvr, (cudaStream_t)stream, nvr > 1);
     return dispatch<AgKPolicy>(lp, BN, false, b_kn != 0, out_dtype, (gemm_ctas + ncomm) * nvr, (cudaStream_t)stream, nvr > 1);
 }
 
@@ -94,14 +104,18 @@ int gemm_scatter(const ccmpi_dev_comm* comms, int nvr, const void* const* A, con
     if (rc) return rc;
     CCMPI_REQUIRE((slots_off | out_off) % 16 == 0, "symmetric offsets must be 16-byte aligned");
     const int sms = (num_sms > 0 ? num_sms : ccmpi::device_sm_count());
-    const int tiles = m_blocks * (N / BN);
-    const int per_rank = grid_for(nvr, sms, tiles, 0);
+    const bool pairs = use_2cta();
+    const int tiles = pairs ? 2 * (((m_blocks + 1) / 2) * (N / BN)) : m_blocks * (N / BN);
+    int per_rank = grid_for(nvr, sms, tiles, 0);
+    if (pairs) per_rank &= ~1;
+    CCMPI_REQUIRE(per_rank >= (pairs ? 2 : 1), "not enough SMs for %d emulated ranks", nvr);
     Launch lp;
     memset(&lp, 0, sizeof(lp));
     lp.nvr = nvr;
     for (int v = 0; v < nvr; ++v) {
         RankParams& rp = lp.r[v];
-        rc = fill_tmaps(rp, A[v], A[v], B[v], M, N, K, lda, lda, ldb, a_km != 0, b_kn != 0, BN, a_km ? K : M, a_km ? M : K);
+        rc = fill_tmaps(rp, A[v], A[v], B[v], M, N, K, lda, lda, ldb, a_km != 0, b_kn != 0, pairs ? BN / 2 : BN,
+                        a_km ? K : M, a_km ? M : K);
         if (rc) return rc;
         rp.C = C ? C[v] : nullptr;
         rp.ldc = ldc;
@@ -114,6 +128,7 @@ int gemm_scatter(const ccmpi_dev_comm* comms, int nvr, const void* const* A, con
         rp.aux0 = BN;
         rp.aux1 = use_mc;
     }
+    if (pairs) return dispatch2<Policy>(lp, BN, a_km != 0, b_kn != 0, out_dtype, per_rank * nvr, (cudaStream_t)stream, nvr > 1);
     return dispatch<Policy>(lp, BN, a_km != 0, b_kn != 0, out_dtype, per_rank * nvr, (cudaStream_t)stream, nvr > 1);
 }
 }  // namespace
@@ -147,21 +162,26 @@ extern "C" int ccmpi_fused_gemm_ag(const ccmpi_dev_comm* comms, int nvr, const v
     if (rc) return rc;
     CCMPI_REQUIRE(yfull_off % 16 == 0, "symmetric offsets must be 16-byte aligned");
     const int sms = (num_sms > 0 ? num_sms : ccmpi::device_sm_count());
+    const bool pairs = use_2cta();
     const int BN = pick_bn(M, N, sms / nvr);
-    const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
-    const int per_rank = grid_for(nvr, sms, tiles, 0);
+    const int m_blocks = (M + BM - 1) / BM;
+    const int tiles = pairs ? 2 * (((m_blocks + 1) / 2) * ((N + BN - 1) / BN)) : m_blocks * ((N + BN - 1) / BN);
+    int per_rank = grid_for(nvr, sms, tiles, 0);
+    if (pairs) per_rank &= ~1;
     CCMPI_REQUIRE(per_rank <= CCMPI_MAX_BLOCKS, "grid of %d CTAs exceeds the %d barrier slots", per_rank, CCMPI_MAX_BLOCKS);
     Launch lp;
     memset(&lp, 0, sizeof(lp));
     lp.nvr = nvr;
     for (int v = 0; v < nvr; ++v) {
         RankParams& rp = lp.r[v];
-        rc = fill_tmaps(rp, A[v], A[v], B[v], M, N, K, lda, lda, ldb, a_km != 0, b_kn != 0, BN, a_km ? K : M, a_km ? M : K);
+        rc = fill_tmaps(rp, A[v], A[v], B[v], M, N, K, lda, lda, ldb, a_km != 0, b_kn != 0, pairs ? BN / 2 : BN,
+                        a_km ? K : M, a_km ? M : K);
         if (rc) return rc;
         rp.M = M; rp.N = N; rp.K = K;
         rp.comm = comms[v];
         rp.off1 = yfull_off;
         rp.aux1 = use_mc;
     }
+    if (pairs) return dispatch2<AgOutPolicy>(lp, BN, a_km != 0, b_kn != 0, out_dtype, per_rank * nvr, (cudaStream_t)stream, nvr > 1);
     return dispatch<AgOutPolicy>(lp, BN, a_km != 0, b_kn != 0, out_dtype, per_rank * nvr, (cudaStream_t)stream, nvr > 1);
 }

@@ -81,6 +81,73 @@ struct AgKPolicy : PlainPolicy {
         }
     }
 
+    // CTA-pair kernel: the same push, driven by ONE thread through the bulk-copy engine. Rows of
+    // the local shard are pulled into shared memory (cp.async.bulk, two 96 KiB halves so the next
+    // batch loads while the current one is being sent) and sent to every member with one bulk
+    // store per row and destination. ~190 KiB in flight per CTA instead of 24 KiB of registers,
+    // so a handful of CTAs saturate the link and the rest of the SMs keep doing MMAs.
+    __device__ static void comm_cta_bulk(const RankParams& p, int cc, int ncomm, uint8_t* smem) {
+        const ccmpi_dev_comm& c = p.comm;
+        if (c.size == 1 || threadIdx.x != 0) return;
+        constexpr int HALF = 96 * 1024;
+        uint64_t* bar = reinterpret_cast<uint64_t*>(smem);
+        uint8_t* buf = smem + 1024;
+        ptx::mbar_init(&bar[0], 1);
+        ptx::mbar_init(&bar[1], 1);
+        ptx::fence_mbar_init();
+        const int m_blocks = (p.M + BM - 1) / BM;
+        const int row_bytes = p.chunk * 2;
+        const int rpb = max(1, min(BM, HALF / row_bytes));      // rows per batch
+        const int bpm = (BM + rpb - 1) / rpb;                    // batches per m-block
+        const int my_blocks = (m_blocks - cc + ncomm - 1) / ncomm;
+        const int total = my_blocks * bpm;
+        const uint8_t* x = c.heap[c.rank] + p.off0;
+        const size_t src_ld = (size_t)p.aux0 * 2, dst_ld = (size_t)p.K * 2;
+        const size_t col0 = (size_t)c.rank * p.chunk * 2;
+        auto batch = [&](int i, int& mb, int& r0, int& n) {
+            const int k = i / bpm, b = i - k * bpm;
+            mb = cc + k * ncomm;
+            r0 = mb * BM + b * rpb;
+            n = min(rpb, min(p.M, mb * BM + BM) - r0);
+            if (n < 0) n = 0;
+        };
+        auto load = [&](int i) {
+            int mb, r0, n;
+            batch(i, mb, r0, n);
+            const int h = i & 1;
+            ptx::mbar_arrive_expect_tx(&bar[h], (uint32_t)(n * row_bytes));
+            for (int r = 0; r < n; ++r)
+                ptx::bulk_g2s(buf + h * HALF + r * row_bytes, x + (size_t)(r0 + r) * src_ld, row_bytes, &bar[h]);
+        };
+        uint32_t ph[2] = {0, 0};
+        if (total > 0) load(0);
+        for (int i = 0; i < total; ++i) {
+            const int h = i & 1;
+            if (i + 1 < total) {
+                ptx::tma_store_wait_read<0>();   // batch i-1 has been read out of the half we refill
+                load(i + 1);
+            }
+            ptx::mbar_wait(&bar[h], ph[h], 700 + h);
+            ph[h] ^= 1;
+            int mb, r0, n;
+            batch(i, mb, r0, n);
+            for (int r = 0; r < n; ++r) {
+                const uint32_t src = ptx::smem_u32(buf + h * HALF + r * row_bytes);
+                const size_t d = p.off1 + (size_t)(r0 + r) * dst_ld + col0;
+                for (int s = 0; s < c.size; ++s) ptx::bulk_s2g(c.heap[(c.rank + s) % c.size] + d, src, row_bytes);
+            }
+            ptx::tma_store_commit();
+            if ((i + 1) % bpm == 0) {
+                // the whole m-block is on its way: wait until it has landed, then tell the peers
+                ptx::tma_store_wait<0>();
+                ptx::fence_proxy_async_all();
+                ptx::fence_acq_rel_sys();
+                for (int s = 1; s < c.size; ++s)
+                    ptx::st_release_sys(user_flag(c, (c.rank + s) % c.size, ready_idx(p, c.rank, mb)), p.epoch);
+            }
+        }
+    }
+
     __device__ static void comm_cta(const RankParams& p, int cc, int ncomm) {
         const ccmpi_dev_comm& c = p.comm;
         if (c.size == 1) return;
@@ -150,6 +217,18 @@ struct AgKPolicy : PlainPolicy {
 //   aux0 : the launch's BN (tile width), so one policy type serves every tile shape
 struct RsNPolicy : PlainPolicy {
     static constexpr bool kCommCtas = false;
+    static constexpr bool kStagedStore = true;
+
+    // CTA-pair kernel: one row chunk of a partial tile, already in shared memory, goes to the
+    // owner's slot for this source rank in a single bulk copy
+    template <typename OutT>
+    __device__ static void bulk_row(const RankParams& p, const TileCoord& tc, int row, int col0, uint32_t smem_row, int bytes) {
+        const ccmpi_dev_comm& c = p.comm;
+        const int owner = col0 / p.chunk;
+        const int lcol = col0 - owner * p.chunk;
+        OutT* slot = reinterpret_cast<OutT*>(c.heap[owner] + p.off1) + ((size_t)c.rank * p.M + row) * p.chunk + lcol;
+        ptx::bulk_s2g(slot, smem_row, bytes);
+    }
 
     __device__ static int nb_per_owner(const RankParams& p) { return p.chunk / p.aux0; }
     __device__ static int flag_idx(const RankParams& p, int m_blk, int n_local, int src) {
@@ -292,6 +371,18 @@ struct ArPolicy : RsNPolicy {
 // overlaps the first tile's mainloop.
 // ================================================================================================
 struct AgOutPolicy : PlainPolicy {
+    static constexpr bool kStagedStore = true;
+
+    template <typename OutT>
+    __device__ static void bulk_row(const RankParams& p, const TileCoord& tc, int row, int col0, uint32_t smem_row, int bytes) {
+        const ccmpi_dev_comm& c = p.comm;
+        const size_t full_ld = (size_t)p.N * c.size;
+        const size_t d = p.off1 + ((size_t)row * full_ld + (size_t)c.rank * p.N + col0) * sizeof(OutT);
+#pragma unroll
+        for (int s = 0; s < CCMPI_MAX_RANKS; ++s)
+            if (s < c.size) ptx::bulk_s2g(c.heap[(c.rank + s) % c.size] + d, smem_row, bytes);
+    }
+
     __device__ static void prologue(const RankParams& p, int cta, int epi_tid) {
         cta_rank_barrier(p.comm, cta, epi_tid, [] { epi_bar_sync(); });
     }

@@ -54,6 +54,7 @@ __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;"
 // ------------------------------------------------------------------------------------------------
 struct PlainPolicy {
     static constexpr bool kCommCtas = false;
+    static constexpr bool kStagedStore = false;   // CTA-pair kernel: stage tiles in smem + bulk copies
 
     struct State {};
 
@@ -87,6 +88,7 @@ struct PlainPolicy {
     __device__ static void tail(const RankParams& p, int cta, int nctas, int epi_tid) {}
     // body of a communication CTA (only if kCommCtas)
     __device__ static void comm_cta(const RankParams& p, int comm_cta, int ncomm) {}
+    __device__ static void comm_cta_bulk(const RankParams& p, int comm_cta, int ncomm, uint8_t* smem) {}
 };
 
 // ------------------------------------------------------------------------------------------------

@@ -24,22 +24,32 @@
 
 namespace gemm {
 
-template <int BN>
+// Staged epilogue (policies whose tiles leave the GPU): every epilogue lane parks 256 bytes of its
+// output row in shared memory and ships them with one cp.async.bulk per destination, so NVLink
+// sees 256-byte bursts instead of 16-byte stores from registers. Rows are padded by 16 bytes,
+// which makes the lanes' 16-byte shared stores conflict-free.
+constexpr int STG_CHUNK_BYTES = 256;
+constexpr int STG_ROW_STRIDE = STG_CHUNK_BYTES + 16;
+constexpr int STG_BYTES = 4 * 32 * STG_ROW_STRIDE;       // 4 epilogue warps x 32 rows
+
+template <int BN, bool STAGED = false>
 struct Cfg2 {
     static constexpr int A_BYTES = BM * BK * 2;          // this CTA's 128 rows of A
     static constexpr int B_ROWS = BN / 2;                // this CTA's half of the B tile
     static constexpr int B_BYTES = B_ROWS * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int STAGES = (200 * 1024) / STAGE_BYTES > 8 ? 8 : (200 * 1024) / STAGE_BYTES;
+    static constexpr int RING_BUDGET = 200 * 1024 - (STAGED ? STG_BYTES : 0);
+    static constexpr int STAGES = RING_BUDGET / STAGE_BYTES > 8 ? 8 : RING_BUDGET / STAGE_BYTES;
     static constexpr int TMEM_COLS = (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256 + (STAGED ? STG_BYTES : 0);
     static_assert(BN % 128 == 0 && BN <= 256, "BN must be 128 or 256 for CTA pairs");
+    static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget exceeded");
 };
 
 template <int BN, bool A_MN, bool B_MN, typename OutT, typename Policy>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 gemm_kernel_2cta(const __grid_constant__ Launch lp) {
-    using C = Cfg2<BN>;
+    using C = Cfg2<BN, Policy::kStagedStore>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint64_t* bars = reinterpret_cast<uint64_t*>(base + C::STAGES * C::STAGE_BYTES);
@@ -48,6 +58,7 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
     uint64_t* tmem_full = empty + C::STAGES;
     uint64_t* tmem_empty = tmem_full + 2;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+    uint8_t* stg_base = reinterpret_cast<uint8_t*>(bars) + 256;
     auto smem_a = [&](int s) { return base + s * C::STAGE_BYTES; };
     auto smem_b = [&](int s) { return base + s * C::STAGE_BYTES + C::A_BYTES; };
 
@@ -67,7 +78,7 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
     if constexpr (Policy::kCommCtas) {
         const int ncomm = p.num_comm_ctas;  // even: whole clusters
         if (cta < ncomm) {
-            Policy::comm_cta(p, cta, ncomm);
+            Policy::comm_cta_bulk(p, cta, ncomm, base);
             return;
         }
         cta -= ncomm;
@@ -198,20 +209,63 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
             ptx::tc_fence_after();
             const int row = tc.m_blk * BM + q * 32 + lane;
             const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + acc * BN;
+            if constexpr (!Policy::kStagedStore) {
 #pragma unroll 1
-            for (int c = 0; c < BN; c += 32) {
-                uint32_t v[32];
-                ptx::tmem_ld_32x32b_x32(taddr + c, v);
-                ptx::tmem_ld_wait();
-                if (c + 32 >= BN) {
-                    ptx::tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) {
-                        if (leader) ptx::mbar_arrive(&tmem_empty[acc]);
-                        else ptx::mbar_arrive_cluster(&tmem_empty[acc], 0);
+                for (int c = 0; c < BN; c += 32) {
+                    uint32_t v[32];
+                    ptx::tmem_ld_32x32b_x32(taddr + c, v);
+                    ptx::tmem_ld_wait();
+                    if (c + 32 >= BN) {
+                        ptx::tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) {
+                            if (leader) ptx::mbar_arrive(&tmem_empty[acc]);
+                            else ptx::mbar_arrive_cluster(&tmem_empty[acc], 0);
+                        }
                     }
+                    if (valid) Policy::template store<OutT>(p, tc, row, tc.n_blk * BN + c, v);
                 }
-                if (valid) Policy::template store<OutT>(p, tc, row, tc.n_blk * BN + c, v);
+            } else {
+                constexpr int CW = STG_CHUNK_BYTES / (int)sizeof(OutT);   // columns per staged chunk
+                const uint32_t my_row = ptx::smem_u32(stg_base) + ((warp - EPI_WARP0) * 32 + lane) * STG_ROW_STRIDE;
+#pragma unroll 1
+                for (int c0 = 0; c0 < BN; c0 += CW) {
+                    ptx::tma_store_wait_read<0>();   // this lane's previous copies have left its row buffer
+#pragma unroll 1
+                    for (int c = c0; c < c0 + CW; c += 32) {
+                        uint32_t v[32];
+                        ptx::tmem_ld_32x32b_x32(taddr + c, v);
+                        ptx::tmem_ld_wait();
+                        if (c + 32 >= BN) {
+                            ptx::tc_fence_before();
+                            __syncwarp();
+                            if (lane == 0) {
+                                if (leader) ptx::mbar_arrive(&tmem_empty[acc]);
+                                else ptx::mbar_arrive_cluster(&tmem_empty[acc], 0);
+                            }
+                        }
+                        const uint32_t dst = my_row + (c - c0) * (int)sizeof(OutT);
+                        if constexpr (sizeof(OutT) == 2) {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j)
+                                ptx::st_shared_v4(dst + 16 * j, make_uint4(pack_bf16(v[8 * j], v[8 * j + 1]), pack_bf16(v[8 * j + 2], v[8 * j + 3]),
+                                                                           pack_bf16(v[8 * j + 4], v[8 * j + 5]), pack_bf16(v[8 * j + 6], v[8 * j + 7])));
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                ptx::st_shared_v4(dst + 16 * j, make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]));
+                        }
+                    }
+                    ptx::fence_proxy_async_smem();   // own generic writes -> own bulk copy (async proxy)
+                    const int col0 = tc.n_blk * BN + c0;
+                    if (valid && row < p.M && col0 < p.N) {
+                        const int ncols = min(CW, p.N - col0);
+                        Policy::template bulk_row<OutT>(p, tc, row, col0, my_row, ncols * (int)sizeof(OutT));
+                    }
+                    ptx::tma_store_commit();
+                }
+                ptx::tma_store_wait<0>();            // this lane's rows have landed
+                ptx::fence_proxy_async_all();        // ... and are ordered before the flag traffic below
             }
             if (valid) Policy::tile_done(p, tc, epi_tid);
         }
