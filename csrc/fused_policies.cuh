@@ -156,7 +156,7 @@ struct AgKPolicy : PlainPolicy {
         const uint8_t* x = c.heap[c.rank] + p.off0;
         const size_t src_ld = (size_t)p.aux0 * 2, dst_ld = (size_t)p.K * 2;
         const size_t col0 = (size_t)c.rank * p.chunk * 2;
-        const bool mc = p.aux1 != 0 && c.mc_heap != nullptr;
+        const bool mc = (p.aux1 & 1) != 0 && c.mc_heap != nullptr;
         for (int mb = cc; mb < m_blocks; mb += ncomm) {
             const int r0 = mb * BM, rows = min(BM, p.M - r0);
             const int total = rows * vec_per_row;
@@ -321,7 +321,7 @@ struct RsNPolicy : PlainPolicy {
                 // all-reduce flavour: the reduced tile goes to every rank's full-width output
                 // (off2: symmetric [M][N], row stride N)
                 const size_t d = p.off2 + ((size_t)row * p.N + (size_t)c.rank * p.chunk + lcol) * sizeof(OutT);
-                if (p.aux1 != 0 && c.mc_heap != nullptr) {
+                if ((p.aux1 & 1) != 0 && c.mc_heap != nullptr) {
                     ptx::multimem_st_v4(c.mc_heap + d, out);
                 } else {
 #pragma unroll
@@ -399,7 +399,7 @@ struct AgOutPolicy : PlainPolicy {
         if (ncols <= 0) return;
         const size_t full_ld = (size_t)p.N * c.size;
         const size_t d = p.off1 + ((size_t)row * full_ld + (size_t)c.rank * p.N + col0) * sizeof(OutT);
-        if (p.aux1 != 0 && c.mc_heap != nullptr && ncols == 32) {
+        if ((p.aux1 & 1) != 0 && c.mc_heap != nullptr && ncols == 32) {
             // one multimem.st per 16 bytes; the switch replicates it to every member
             if constexpr (sizeof(OutT) == 2) {
 #pragma unroll

@@ -78,7 +78,8 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
     if constexpr (Policy::kCommCtas) {
         const int ncomm = p.num_comm_ctas;  // even: whole clusters
         if (cta < ncomm) {
-            Policy::comm_cta_bulk(p, cta, ncomm, base);
+            if (p.aux1 & 2) Policy::comm_cta_bulk(p, cta, ncomm, base);   // bit 1: drive the bulk-copy engine
+            else Policy::comm_cta(p, cta, ncomm);                         // default: vectorised register copies
             return;
         }
         cta -= ncomm;
