@@ -46,6 +46,7 @@ def main():
     ap.add_argument("--blocks", type=int, default=0, help="max blocks for our kernels (0 = default)")
     ap.add_argument("--out", default=None)
     args = ap.parse_args()
+    os.environ.setdefault("CCMPI_HEAP_MB", str(max(2048, 3 * args.max_mb + 512)))
     comm = MPI.COMM_WORLD
     rank, n = comm.Get_rank(), comm.Get_size()
     torch.cuda.set_device(rank)

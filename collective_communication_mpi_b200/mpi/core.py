@@ -519,9 +519,10 @@ class Comm:
             out = torch.empty((n,) + tuple(shape), dtype=src.dtype, device=src.device)
             self.Allgather(src, out)
             return [out[i] for i in range(n)]
+        dev = sendobj.device if _is_torch(sendobj) and sendobj.is_cuda else None
         blobs = self._world.host_allgather_bytes(self._cid, self._members, self._me,
-                                                 pickle.dumps(sendobj, protocol=pickle.HIGHEST_PROTOCOL))
-        return [pickle.loads(b) for b in blobs]
+                                                 pickle.dumps(_to_wire(sendobj), protocol=pickle.HIGHEST_PROTOCOL))
+        return [_from_wire(pickle.loads(b), dev) for b in blobs]
 
     def alltoall(self, sendobj):
         """Object all-to-all: element j of the list goes to rank j (func_impl.py:184)."""
@@ -547,8 +548,9 @@ class Comm:
             self.Alltoall(src, out)
             return [out[i] for i in range(n)]
         # ragged / arbitrary objects: everyone publishes its whole list, takes column `me`
-        rows = self._world.host_allgather_obj(self._cid, self._members, self._me, items)
-        return [rows[j][self._me] for j in range(n)]
+        dev = next((x.device for x in items if _is_torch(x) and x.is_cuda), None)
+        rows = self._world.host_allgather_obj(self._cid, self._members, self._me, [_to_wire(x) for x in items])
+        return [_from_wire(rows[j][self._me], dev) for j in range(n)]
 
     # ---- last-axis collectives (the TP activation layout of func_impl.py) -------------------
     def gather_last_axis(self, x):
@@ -661,6 +663,16 @@ def _array_meta(x):
     if _is_torch(x):
         return ("torch", tuple(x.shape), int(x.numel()), str(x.dtype) + str(x.device.type))
     return None
+
+
+def _to_wire(obj):
+    """CUDA tensors are pickled as CPU tensors: a device tensor unpickled in another process would
+    materialise on the SENDER's GPU."""
+    return obj.cpu() if _is_torch(obj) and obj.is_cuda else obj
+
+
+def _from_wire(obj, device):
+    return obj.to(device) if device is not None and _is_torch(obj) else obj
 
 
 def _np_dtype_of(b: _Buf):

@@ -76,6 +76,9 @@ class GradSink:
     def _reduce(self, b):
         if self.dp == 1:
             return
+        # the bucket produced last (first layer's gradients) has nothing left to hide behind: give
+        # it every SM; earlier buckets share the GPU with the remaining backward GEMMs
+        last = b is self.buckets[-1]
         count = b["hi"] - b["lo"]
         off = self.flat_off + b["lo"] * 2
         tmp_off = self.dev.heap.offset_of(self.tmp) + b["lo"] * 2 if self.tmp is not None else 0
@@ -86,7 +89,7 @@ class GradSink:
             ev.record(cur)
             st.wait_event(ev)
         CO.allreduce(self.dev.comms, N.BF16, N.SUM, off, off, count, tmp_off=tmp_off, algo=self.algo,
-                     scale=1.0 / self.dp, max_blocks=self.max_blocks, stream=st)
+                     scale=1.0 / self.dp, max_blocks=(0 if last else self.max_blocks), stream=st)
         self.launches += 1
 
     def finish(self):

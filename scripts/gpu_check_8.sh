@@ -4,7 +4,7 @@
 mkdir -p gpurun_out
 NG=$(nvidia-smi -L | wc -l)
 echo "== $NG GPUs"; nvidia-smi topo -m | head -11 > gpurun_out/topo_${NG}gpu.txt
-timeout 900 python -m pytest tests/test_gpu_multirank.py -x -q 2>&1 | tail -6 | tee gpurun_out/pytest_multirank_${NG}gpu.txt
+timeout 900 python -m pytest tests/test_gpu_multirank.py -q > gpurun_out/pytest_multirank_${NG}gpu.txt 2>&1; tail -4 gpurun_out/pytest_multirank_${NG}gpu.txt
 port=29700
 for n in 8 4; do for impl in ours nccl; do
   port=$((port+1))
