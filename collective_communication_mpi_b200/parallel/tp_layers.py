@@ -99,14 +99,15 @@ class ColumnParallelLinear(nn.Module):
         self.grad_dtype = grad_dtype
         dev = torch.device("cuda", torch.cuda.current_device())
         self.weight = _init_weight(in_features, self.N, in_features, dev, seed * 1000 + mp_comm.Get_rank())
-        self.ag = F.AllGatherGemm(mp_comm, tokens, in_features, num_comm_ctas=num_comm_ctas)
-        self.rs = F.GemmReduceScatter(mp_comm, tokens, in_features)
+        # a 1-member group needs no staging buffers or flags: plain GEMMs
+        self.ag = F.AllGatherGemm(mp_comm, tokens, in_features, num_comm_ctas=num_comm_ctas) if self.mp > 1 else None
+        self.rs = F.GemmReduceScatter(mp_comm, tokens, in_features) if self.mp > 1 else None
         self.out_ag = F.GemmAllGather(mp_comm, tokens, self.N) if gather_output and self.mp > 1 else None
         self.num_sms = 0
 
     def input_buffer(self) -> torch.Tensor:
         """Write the layer input here (symmetric memory) to skip one device copy."""
-        return self.ag.input_buffer()
+        return self.ag.input_buffer() if self.ag is not None else None
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         return _ColumnFn.apply(x.reshape(self.M, -1), self.weight, self)
@@ -146,8 +147,8 @@ class RowParallelLinear(nn.Module):
         self.grad_dtype = grad_dtype
         dev = torch.device("cuda", torch.cuda.current_device())
         self.weight = _init_weight(self.K, out_features, in_features, dev, seed * 1000 + mp_comm.Get_rank())
-        self.rs = F.GemmReduceScatter(mp_comm, tokens, out_features)
-        self.ag = F.AllGatherGemm(mp_comm, tokens, out_features, num_comm_ctas=num_comm_ctas)
+        self.rs = F.GemmReduceScatter(mp_comm, tokens, out_features) if self.mp > 1 else None
+        self.ag = F.AllGatherGemm(mp_comm, tokens, out_features, num_comm_ctas=num_comm_ctas) if self.mp > 1 else None
         self.num_sms = 0
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:

@@ -584,7 +584,13 @@ template <typename... Args>
 static int launch(void (*kern)(Args...), int nvr, int blocks, cudaStream_t stream, Args... args) {
     void* ptrs[] = {(void*)&args...};
     if (nvr > 1) {
-        // emulated ranks spin on one another: co-residency must be guaranteed
+        // emulated ranks spin on one another: co-residency must be guaranteed, so the grid is
+        // clamped to what the device can hold at once (every kernel here is grid-stride)
+        int per_sm = 0;
+        CCMPI_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)kern, THREADS, 0));
+        const int cap = per_sm * ccmpi::device_sm_count() / nvr;
+        CCMPI_REQUIRE(cap >= 1, "device cannot hold %d emulated ranks at once", nvr);
+        if (blocks > cap) blocks = cap;
         CCMPI_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)kern, dim3(blocks * nvr), dim3(THREADS), ptrs, 0, stream));
     } else {
         CCMPI_CUDA_CHECK(cudaLaunchKernel((const void*)kern, dim3(blocks), dim3(THREADS), ptrs, 0, stream));
