@@ -173,7 +173,7 @@ def run_gpu(args, impl: str):
             loss = step(xb, tb)
             prefetch.release()
             losses.push(loss)
-            if losses.pending > 1:
+            if losses.pending > 2:      # the host consumes each loss two steps after it was produced
                 losses.pop()
         while losses.pending:
             losses.pop()

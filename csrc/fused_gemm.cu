@@ -46,14 +46,7 @@ extern "C" int ccmpi_fused_ag_gemm(const ccmpi_dev_comm* comms, int nvr, size_t 
     const int chunk = K / n;
     const int sms = (num_sms > 0 ? num_sms : ccmpi::device_sm_count());
     const bool pairs = use_2cta();
-    // measured on 2 x B200 (scripts/sweep_comm.sh): 12 register-copy CTAs beat both fewer / more of
-    // them and the single-thread bulk-copy variant (CCMPI_AG_BULK=1), whose per-op engine overhead
-    // caps a CTA near 27 GB/s at 4 KiB rows
-    static const int env_comm = [] { const char* e = getenv("CCMPI_AG_COMM_CTAS"); return e ? atoi(e) : 0; }();
-    static const int env_bulk = [] { const char* e = getenv("CCMPI_AG_BULK"); return e ? atoi(e) : 0; }();
-    int ncomm = n > 1 ? (num_comm_ctas > 0 ? num_comm_ctas : (env_comm > 0 ? env_comm : 12)) : 0;
-    if (ncomm > m_blocks) ncomm = m_blocks;
-    if (pairs) ncomm = (ncomm + 1) & ~1;                 // whole clusters
+    const int ncomm = 0;  // the gather is pushed by every CTA's epilogue warps (AgKPolicy::prologue)
     int per_rank_budget = sms / nvr;
     if (pairs) per_rank_budget &= ~1;
     CCMPI_REQUIRE(per_rank_budget > ncomm, "not enough SMs (%d per rank) for %d communication CTAs", per_rank_budget, ncomm);
@@ -81,7 +74,8 @@ extern "C" int ccmpi_fused_ag_gemm(const ccmpi_dev_comm* comms, int nvr, size_t 
         rp.epoch = epoch;
         rp.num_comm_ctas = ncomm;
         rp.aux0 = ldx;
-        rp.aux1 = (use_mc ? 1 : 0) | (env_bulk ? 2 : 0);
+        rp.aux1 = use_mc ? 1 : 0;
+        rp.aux2 = gemm_ctas;   // contributions per ready flag and launch: keep num_sms fixed per context
     }
     if (pairs)
         return dispatch2<AgKPolicy>(lp, BN, false, b_kn != 0, out_dtype, (gemm_ctas + ncomm) * nvr, (cudaStream_t)stream, nvr > 1);

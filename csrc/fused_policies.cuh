@@ -42,13 +42,12 @@ __device__ __forceinline__ void cta_rank_barrier(const ccmpi_dev_comm& c, int ct
 //   off0 : symmetric offset of x_local  [M][chunk]   (row stride aux0 elements)
 //   off1 : symmetric offset of x_full   [M][K]       (staging the peers push into)
 //   tmap_a  -> this rank's x_full,  tmap_a2 -> this rank's x_local
-// Communication CTAs push this rank's rows, one 128-row block at a time, into every member's
-// x_full (their own included, so the gathered activation is complete for the backward dW GEMM)
-// and then raise ready[rank][m_blk] on each peer. The GEMM walks K starting with the local
-// chunk (no wait), then chunks (rank+1)%n, ... each gated on its ready flag.
+//   aux2 : CTAs per rank of this launch (contributions per ready flag and launch)
+// The GEMM walks K starting with the local chunk (no wait), then chunks (rank+1)%n, ... each
+// gated on ready[src][m_blk], which counts the pushing CTAs of rank `src` (see prologue()).
 // ================================================================================================
 struct AgKPolicy : PlainPolicy {
-    static constexpr bool kCommCtas = true;
+    static constexpr bool kCommCtas = false;
 
     __device__ static int ready_idx(const RankParams& p, int src, int m_blk) {
         return p.flag_base + src * ((p.M + BM - 1) / BM) + m_blk;
@@ -73,7 +72,7 @@ struct AgKPolicy : PlainPolicy {
             a_k0 = within * BK;
         } else {
             if (within == 0) {
-                ptx::wait_flag_ge_sys(user_flag(c, c.rank, ready_idx(p, src, tc.m_blk)), p.epoch, 500 + src);
+                ptx::wait_flag_ge_sys(user_flag(c, c.rank, ready_idx(p, src, tc.m_blk)), p.epoch * (unsigned)p.aux2, 500 + src);
                 ptx::fence_proxy_async_all();  // peer's generic-proxy stores -> our TMA reads
             }
             ta = &p.tmap_a;
@@ -81,126 +80,91 @@ struct AgKPolicy : PlainPolicy {
         }
     }
 
-    // CTA-pair kernel: the same push, driven by ONE thread through the bulk-copy engine. Rows of
-    // the local shard are pulled into shared memory (cp.async.bulk, two 96 KiB halves so the next
-    // batch loads while the current one is being sent) and sent to every member with one bulk
-    // store per row and destination. ~190 KiB in flight per CTA instead of 24 KiB of registers,
-    // so a handful of CTAs saturate the link and the rest of the SMs keep doing MMAs.
-    __device__ static void comm_cta_bulk(const RankParams& p, int cc, int ncomm, uint8_t* smem) {
-        const ccmpi_dev_comm& c = p.comm;
-        if (c.size == 1 || threadIdx.x != 0) return;
-        constexpr int HALF = 96 * 1024;
-        uint64_t* bar = reinterpret_cast<uint64_t*>(smem);
-        uint8_t* buf = smem + 1024;
-        ptx::mbar_init(&bar[0], 1);
-        ptx::mbar_init(&bar[1], 1);
-        ptx::fence_mbar_init();
-        const int m_blocks = (p.M + BM - 1) / BM;
-        const int row_bytes = p.chunk * 2;
-        const int rpb = max(1, min(BM, HALF / row_bytes));      // rows per batch
-        const int bpm = (BM + rpb - 1) / rpb;                    // batches per m-block
-        const int my_blocks = (m_blocks - cc + ncomm - 1) / ncomm;
-        const int total = my_blocks * bpm;
-        const uint8_t* x = c.heap[c.rank] + p.off0;
-        const size_t src_ld = (size_t)p.aux0 * 2, dst_ld = (size_t)p.K * 2;
-        const size_t col0 = (size_t)c.rank * p.chunk * 2;
-        auto batch = [&](int i, int& mb, int& r0, int& n) {
-            const int k = i / bpm, b = i - k * bpm;
-            mb = cc + k * ncomm;
-            r0 = mb * BM + b * rpb;
-            n = min(rpb, min(p.M, mb * BM + BM) - r0);
-            if (n < 0) n = 0;
-        };
-        auto load = [&](int i) {
-            int mb, r0, n;
-            batch(i, mb, r0, n);
-            const int h = i & 1;
-            ptx::mbar_arrive_expect_tx(&bar[h], (uint32_t)(n * row_bytes));
-            for (int r = 0; r < n; ++r)
-                ptx::bulk_g2s(buf + h * HALF + r * row_bytes, x + (size_t)(r0 + r) * src_ld, row_bytes, &bar[h]);
-        };
-        uint32_t ph[2] = {0, 0};
-        if (total > 0) load(0);
-        for (int i = 0; i < total; ++i) {
-            const int h = i & 1;
-            if (i + 1 < total) {
-                ptx::tma_store_wait_read<0>();   // batch i-1 has been read out of the half we refill
-                load(i + 1);
-            }
-            ptx::mbar_wait(&bar[h], ph[h], 700 + h);
-            ph[h] ^= 1;
-            int mb, r0, n;
-            batch(i, mb, r0, n);
-            for (int r = 0; r < n; ++r) {
-                const uint32_t src = ptx::smem_u32(buf + h * HALF + r * row_bytes);
-                const size_t d = p.off1 + (size_t)(r0 + r) * dst_ld + col0;
-                for (int s = 0; s < c.size; ++s) ptx::bulk_s2g(c.heap[(c.rank + s) % c.size] + d, src, row_bytes);
-            }
-            ptx::tma_store_commit();
-            if ((i + 1) % bpm == 0) {
-                // the whole m-block is on its way: wait until it has landed, then tell the peers
-                ptx::tma_store_wait<0>();
-                ptx::fence_proxy_async_all();
-                ptx::fence_acq_rel_sys();
-                for (int s = 1; s < c.size; ++s)
-                    ptx::st_release_sys(user_flag(c, (c.rank + s) % c.size, ready_idx(p, c.rank, mb)), p.epoch);
-            }
-        }
+    // The gather itself. There are no dedicated communication CTAs: the four epilogue warps of
+    // EVERY CTA are idle whenever no accumulator is ready (always so at kernel start), and in
+    // those gaps -- never while a finished accumulator is waiting -- they push this rank's shard -- 16-byte vectors, 8 loads in flight per thread, ~19 k threads
+    // chip-wide -- into every member's x_full (their own included, which leaves the gathered
+    // activation whole for the backward dW GEMM), in ascending m-block order, i.e. in the order
+    // the peers' tile rasters will ask for it. After each unrolled batch a CTA adds 1 to
+    // ready[rank][m_blk] on every peer for each m-block it has finished its share of; a flag is
+    // complete when all `aux2` (= CTAs per rank) contributions of this launch are in. Meanwhile
+    // the producer / MMA warps already work on the local K-chunk.
+    static constexpr bool kBackground = true;
+    static constexpr bool kPushFirst = true;
+    struct State {
+        long long base;   // first vector index of this CTA's next batch
+        int flagged;      // m-blocks [0, flagged) already signalled by this CTA
+        int m_blocks;
+    };
+    __device__ static void init_state(State& st, const RankParams& p, int cta, int nctas) {
+        st.base = (long long)cta * EPI_THREADS;
+        st.flagged = 0;
+        st.m_blocks = p.comm.size == 1 ? 0 : (p.M + BM - 1) / BM;
     }
 
-    __device__ static void comm_cta(const RankParams& p, int cc, int ncomm) {
+    // One batch of the push: 8 vectors per epilogue thread. Returns false once everything is out.
+    template <typename OutT>
+    __device__ static bool background(const RankParams& p, State& st, int cta, int nctas, int epi_tid, volatile uint32_t* bcast) {
+        if (st.flagged >= st.m_blocks) return false;
         const ccmpi_dev_comm& c = p.comm;
-        if (c.size == 1) return;
-        const int m_blocks = (p.M + BM - 1) / BM;
-        const int vec_per_row = p.chunk / 8;  // 16-byte vectors per row of the local shard
+        const int vpr = p.chunk / 8;                        // 16-byte vectors per shard row
+        const long long total = (long long)p.M * vpr;
+        const long long per_blk = (long long)BM * vpr;
+        const long long stride = (long long)nctas * EPI_THREADS;
         const uint8_t* x = c.heap[c.rank] + p.off0;
         const size_t src_ld = (size_t)p.aux0 * 2, dst_ld = (size_t)p.K * 2;
         const size_t col0 = (size_t)c.rank * p.chunk * 2;
         const bool mc = (p.aux1 & 1) != 0 && c.mc_heap != nullptr;
-        for (int mb = cc; mb < m_blocks; mb += ncomm) {
-            const int r0 = mb * BM, rows = min(BM, p.M - r0);
-            const int total = rows * vec_per_row;
-            constexpr int U = 8;
-            int i = threadIdx.x;
-            for (; i + (U - 1) * NUM_THREADS < total; i += U * NUM_THREADS) {
-                uint4 v[U];
-                size_t d[U];
+        constexpr int U = 8;
+        uint4 v[U];
+        size_t d[U];
+        bool ok[U];
 #pragma unroll
-                for (int u = 0; u < U; ++u) {
-                    const int j = i + u * NUM_THREADS;
-                    const int row = j / vec_per_row, w = j - row * vec_per_row;
-                    v[u] = ptx::ld_nc_v4(x + (size_t)(r0 + row) * src_ld + (size_t)w * 16);
-                    d[u] = p.off1 + (size_t)(r0 + row) * dst_ld + col0 + (size_t)w * 16;
-                }
-#pragma unroll
-                for (int u = 0; u < U; ++u) {
-                    if (mc) {
-                        ptx::multimem_st_v4(c.mc_heap + d[u], v[u]);
-                    } else {
-#pragma unroll
-                        for (int s = 0; s < CCMPI_MAX_RANKS; ++s)  // s = 0: own copy, so x_full is whole
-                            if (s < c.size) ptx::st_v4(c.heap[(c.rank + s) % c.size] + d[u], v[u]);
-                    }
-                }
-            }
-            for (; i < total; i += NUM_THREADS) {
-                const int row = i / vec_per_row, w = i - row * vec_per_row;
-                const uint4 v = ptx::ld_nc_v4(x + (size_t)(r0 + row) * src_ld + (size_t)w * 16);
-                const size_t d = p.off1 + (size_t)(r0 + row) * dst_ld + col0 + (size_t)w * 16;
-                if (mc) {
-                    ptx::multimem_st_v4(c.mc_heap + d, v);
-                } else {
-                    for (int s = 0; s < c.size; ++s) ptx::st_v4(c.heap[(c.rank + s) % c.size] + d, v);
-                }
-            }
-            __syncthreads();  // every thread's stores are issued ...
-            if (threadIdx.x > 0 && threadIdx.x < c.size) {
-                // ... and published: release at system scope is cumulative over the barrier
-                const int peer = (c.rank + threadIdx.x) % c.size;
-                ptx::fence_acq_rel_sys();
-                ptx::st_release_sys(user_flag(c, peer, ready_idx(p, c.rank, mb)), p.epoch);
+        for (int u = 0; u < U; ++u) {
+            const long long i = st.base + epi_tid + u * stride;
+            ok[u] = i < total;
+            if (ok[u]) {
+                const long long row = i / vpr;
+                const int w = (int)(i - row * vpr);
+                v[u] = ptx::ld_nc_v4(x + (size_t)row * src_ld + (size_t)w * 16);
+                d[u] = p.off1 + (size_t)row * dst_ld + col0 + (size_t)w * 16;
             }
         }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (ok[u]) {
+                if (mc) {
+                    ptx::multimem_st_v4(c.mc_heap + d[u], v[u]);
+                } else {
+#pragma unroll
+                    for (int s = 0; s < CCMPI_MAX_RANKS; ++s)
+                        if (s < c.size) ptx::st_v4(c.heap[(c.rank + s) % c.size] + d[u], v[u]);
+                }
+            }
+        }
+        // every vector of this CTA below `next` is on its way
+        const long long next = st.base + U * stride;
+        int done = (int)min((long long)st.m_blocks, next / per_blk);
+        if (next >= total) done = st.m_blocks;
+        epi_bar_sync();
+        if (epi_tid == 0 && done > st.flagged) {
+            // one system-scope fence orders every push of this CTA (cumulative over the barrier)
+            // before the flag updates; the updates themselves can then be relaxed and pipelined
+            ptx::fence_acq_rel_sys();
+            for (int j = st.flagged; j < done; ++j)
+                for (int s = 1; s < c.size; ++s)
+                    ptx::red_relaxed_sys_add(user_flag(c, (c.rank + s) % c.size, ready_idx(p, c.rank, j)), 1u);
+        }
+        st.flagged = done;
+        st.base = next;
+        return true;
+    }
+
+    // whatever has not been pushed by the time this CTA runs out of tiles goes out now: peers
+    // depend on it
+    template <typename OutT>
+    __device__ static void tail(const RankParams& p, State& st, int cta, int nctas, int epi_tid, volatile uint32_t* bcast) {
+        while (background<OutT>(p, st, cta, nctas, epi_tid, bcast)) {}
     }
 };
 
@@ -235,11 +199,14 @@ struct RsNPolicy : PlainPolicy {
         return p.flag_base + ((m_blk * nb_per_owner(p) + n_local) * p.comm.size + src);
     }
 
-    // owner groups in order rank+1, rank+2, ..., rank (own tiles last)
+    // Owners are interleaved tile by tile: rank+1, rank+2, ..., rank, rank+1, ... That spreads the
+    // remote stores over the whole kernel instead of bursting them at the start, and -- every
+    // rank using the mirrored order -- a peer's partial for one of our tiles arrives at about the
+    // time we finish the same tile ourselves, ready for the background reducer.
     __device__ static TileCoord tile(const RankParams& p, int t, int mb, int nb) {
-        const int per_owner = mb * nb_per_owner(p);
-        const int g = t / per_owner, in_g = t - g * per_owner;
-        const int owner = (p.comm.rank + 1 + g) % p.comm.size;
+        const int n = p.comm.size;
+        const int g = t % n, in_g = t / n;
+        const int owner = (p.comm.rank + 1 + g) % n;
         TileCoord tc = raster(in_g, mb, nb_per_owner(p));
         tc.n_blk += owner * nb_per_owner(p);
         return tc;
@@ -279,64 +246,109 @@ struct RsNPolicy : PlainPolicy {
         const int VPR = BN / EPV;                       // vectors per tile row
         const int rows = min(BM, p.M - m_blk * BM);
         const OutT* slots = reinterpret_cast<const OutT*>(c.heap[c.rank] + p.off1);
-        for (int v = epi_tid; v < rows * VPR; v += EPI_THREADS) {
-            const int row = m_blk * BM + v / VPR;
-            const int lcol = n_local * BN + (v % VPR) * EPV;
-            float acc[EPV];
-            uint4 raw[CCMPI_MAX_RANKS];
+        constexpr int U = 4;   // vectors per thread in flight (x n sources): the slots sit in HBM / far L2
+        for (int v0 = epi_tid; v0 < rows * VPR; v0 += U * EPI_THREADS) {
+            uint4 raw[U][CCMPI_MAX_RANKS];
 #pragma unroll
-            for (int s = 0; s < CCMPI_MAX_RANKS; ++s)
-                if (s < c.size) raw[s] = ptx::ld_v4(slots + ((size_t)s * p.M + row) * p.chunk + lcol);
-#pragma unroll
-            for (int s = 0; s < CCMPI_MAX_RANKS; ++s) {
-                if (s < c.size) {
-                    if constexpr (sizeof(OutT) == 2) {
-                        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw[s]);
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            const float2 f = __bfloat1622float2(h[e]);
-                            acc[2 * e] = s == 0 ? f.x : acc[2 * e] + f.x;
-                            acc[2 * e + 1] = s == 0 ? f.y : acc[2 * e + 1] + f.y;
-                        }
-                    } else {
-                        const float* f = reinterpret_cast<const float*>(&raw[s]);
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) acc[e] = s == 0 ? f[e] : acc[e] + f[e];
-                    }
-                }
-            }
-            uint4 out;
-            if constexpr (sizeof(OutT) == 2) {
-                out.x = pack_bf16(__float_as_uint(acc[0]), __float_as_uint(acc[1]));
-                out.y = pack_bf16(__float_as_uint(acc[2]), __float_as_uint(acc[3]));
-                out.z = pack_bf16(__float_as_uint(acc[4]), __float_as_uint(acc[5]));
-                out.w = pack_bf16(__float_as_uint(acc[6]), __float_as_uint(acc[7]));
-            } else {
-                out = make_uint4(__float_as_uint(acc[0]), __float_as_uint(acc[1]), __float_as_uint(acc[2]),
-                                 __float_as_uint(acc[3]));
-            }
-            if constexpr (!BROADCAST) {
-                ptx::st_v4(reinterpret_cast<OutT*>(p.C) + (size_t)row * p.ldc + lcol, out);
-            } else {
-                // all-reduce flavour: the reduced tile goes to every rank's full-width output
-                // (off2: symmetric [M][N], row stride N)
-                const size_t d = p.off2 + ((size_t)row * p.N + (size_t)c.rank * p.chunk + lcol) * sizeof(OutT);
-                if ((p.aux1 & 1) != 0 && c.mc_heap != nullptr) {
-                    ptx::multimem_st_v4(c.mc_heap + d, out);
-                } else {
+            for (int u = 0; u < U; ++u) {
+                const int v = v0 + u * EPI_THREADS;
+                if (v < rows * VPR) {
+                    const int row = m_blk * BM + v / VPR;
+                    const int lcol = n_local * BN + (v % VPR) * EPV;
 #pragma unroll
                     for (int s = 0; s < CCMPI_MAX_RANKS; ++s)
-                        if (s < c.size) ptx::st_v4(c.heap[(c.rank + s) % c.size] + d, out);
+                        if (s < c.size) raw[u][s] = ptx::ld_v4(slots + ((size_t)s * p.M + row) * p.chunk + lcol);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int v = v0 + u * EPI_THREADS;
+                if (v >= rows * VPR) continue;
+                const int row = m_blk * BM + v / VPR;
+                const int lcol = n_local * BN + (v % VPR) * EPV;
+                float acc[EPV];
+#pragma unroll
+                for (int s = 0; s < CCMPI_MAX_RANKS; ++s) {
+                    if (s < c.size) {
+                        if constexpr (sizeof(OutT) == 2) {
+                            const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw[u][s]);
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                const float2 f = __bfloat1622float2(h[e]);
+                                acc[2 * e] = s == 0 ? f.x : acc[2 * e] + f.x;
+                                acc[2 * e + 1] = s == 0 ? f.y : acc[2 * e + 1] + f.y;
+                            }
+                        } else {
+                            const float* f = reinterpret_cast<const float*>(&raw[u][s]);
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) acc[e] = s == 0 ? f[e] : acc[e] + f[e];
+                        }
+                    }
+                }
+                uint4 out;
+                if constexpr (sizeof(OutT) == 2) {
+                    out.x = pack_bf16(__float_as_uint(acc[0]), __float_as_uint(acc[1]));
+                    out.y = pack_bf16(__float_as_uint(acc[2]), __float_as_uint(acc[3]));
+                    out.z = pack_bf16(__float_as_uint(acc[4]), __float_as_uint(acc[5]));
+                    out.w = pack_bf16(__float_as_uint(acc[6]), __float_as_uint(acc[7]));
+                } else {
+                    out = make_uint4(__float_as_uint(acc[0]), __float_as_uint(acc[1]), __float_as_uint(acc[2]),
+                                     __float_as_uint(acc[3]));
+                }
+                if constexpr (!BROADCAST) {
+                    ptx::st_v4(reinterpret_cast<OutT*>(p.C) + (size_t)row * p.ldc + lcol, out);
+                } else {
+                    // all-reduce flavour: the reduced tile goes to every rank's full-width output
+                    // (off2: symmetric [M][N], row stride N)
+                    const size_t d = p.off2 + ((size_t)row * p.N + (size_t)c.rank * p.chunk + lcol) * sizeof(OutT);
+                    if ((p.aux1 & 1) != 0 && c.mc_heap != nullptr) {
+                        ptx::multimem_st_v4(c.mc_heap + d, out);
+                    } else {
+#pragma unroll
+                        for (int s = 0; s < CCMPI_MAX_RANKS; ++s)
+                            if (s < c.size) ptx::st_v4(c.heap[(c.rank + s) % c.size] + d, out);
+                    }
                 }
             }
         }
     }
 
-    template <typename OutT>
-    __device__ static void tail(const RankParams& p, int cta, int nctas, int epi_tid) {
+    // Reducing owned tiles is background work too: between two of its own tiles a CTA checks
+    // whether every source of its next owned tile has arrived and, if so, reduces it right away,
+    // so that little is left for the tail.
+    static constexpr bool kBackground = true;
+    struct State { int next; };
+    __device__ static void init_state(State& st, const RankParams& p, int cta, int nctas) { st.next = cta; }
+
+    template <typename OutT, bool BROADCAST>
+    __device__ static bool try_reduce(const RankParams& p, State& st, int nctas, int epi_tid, volatile uint32_t* bcast) {
         const int mb = (p.M + BM - 1) / BM, per = nb_per_owner(p);
-        for (int i = cta; i < mb * per; i += nctas) {
-            const TileCoord tc = raster(i, mb, per);
+        if (st.next >= mb * per) return false;
+        const TileCoord tc = raster(st.next, mb, per);
+        const ccmpi_dev_comm& c = p.comm;
+        if (epi_tid == 0) {
+            uint32_t ok = 1;
+            for (int s = 0; s < c.size; ++s)
+                ok &= (int32_t)(ptx::ld_acquire_sys(user_flag(c, c.rank, flag_idx(p, tc.m_blk, tc.n_blk, s))) - p.epoch) >= 0 ? 1u : 0u;
+            *bcast = ok;
+        }
+        epi_bar_sync();
+        const bool ready = *bcast != 0;
+        epi_bar_sync();
+        if (!ready) return false;
+        reduce_tile<OutT, BROADCAST>(p, tc.m_blk, tc.n_blk, epi_tid);   // its flag wait returns at once
+        st.next += nctas;
+        return true;
+    }
+    template <typename OutT>
+    __device__ static bool background(const RankParams& p, State& st, int cta, int nctas, int epi_tid, volatile uint32_t* bcast) {
+        return try_reduce<OutT, false>(p, st, nctas, epi_tid, bcast);
+    }
+    template <typename OutT>
+    __device__ static void tail(const RankParams& p, State& st, int cta, int nctas, int epi_tid, volatile uint32_t* bcast) {
+        const int mb = (p.M + BM - 1) / BM, per = nb_per_owner(p);
+        for (; st.next < mb * per; st.next += nctas) {
+            const TileCoord tc = raster(st.next, mb, per);
             reduce_tile<OutT, false>(p, tc.m_blk, tc.n_blk, epi_tid);
         }
     }
@@ -347,14 +359,18 @@ struct RsNPolicy : PlainPolicy {
 struct ArPolicy : RsNPolicy {
     // peers' kernels store into our output: they must not start before we are done with the
     // previous contents
-    __device__ static void prologue(const RankParams& p, int cta, int epi_tid) {
+    __device__ static void prologue(const RankParams& p, int cta, int nctas, int epi_tid) {
         cta_rank_barrier(p.comm, cta, epi_tid, [] { epi_bar_sync(); });
     }
     template <typename OutT>
-    __device__ static void tail(const RankParams& p, int cta, int nctas, int epi_tid) {
+    __device__ static bool background(const RankParams& p, State& st, int cta, int nctas, int epi_tid, volatile uint32_t* bcast) {
+        return try_reduce<OutT, true>(p, st, nctas, epi_tid, bcast);
+    }
+    template <typename OutT>
+    __device__ static void tail(const RankParams& p, State& st, int cta, int nctas, int epi_tid, volatile uint32_t* bcast) {
         const int mb = (p.M + BM - 1) / BM, per = nb_per_owner(p);
-        for (int i = cta; i < mb * per; i += nctas) {
-            const TileCoord tc = raster(i, mb, per);
+        for (; st.next < mb * per; st.next += nctas) {
+            const TileCoord tc = raster(st.next, mb, per);
             reduce_tile<OutT, true>(p, tc.m_blk, tc.n_blk, epi_tid);
         }
         if (epi_tid == 0) ptx::fence_acq_rel_sys();
@@ -383,11 +399,11 @@ struct AgOutPolicy : PlainPolicy {
             if (s < c.size) ptx::bulk_s2g(c.heap[(c.rank + s) % c.size] + d, smem_row, bytes);
     }
 
-    __device__ static void prologue(const RankParams& p, int cta, int epi_tid) {
+    __device__ static void prologue(const RankParams& p, int cta, int nctas, int epi_tid) {
         cta_rank_barrier(p.comm, cta, epi_tid, [] { epi_bar_sync(); });
     }
     template <typename OutT>
-    __device__ static void tail(const RankParams& p, int cta, int nctas, int epi_tid) {
+    __device__ static void tail(const RankParams& p, State& st, int cta, int nctas, int epi_tid, volatile uint32_t* bcast) {
         if (epi_tid == 0) ptx::fence_acq_rel_sys();
         cta_rank_barrier(p.comm, cta, epi_tid, [] { epi_bar_sync(); });
     }

@@ -56,7 +56,16 @@ struct PlainPolicy {
     static constexpr bool kCommCtas = false;
     static constexpr bool kStagedStore = false;   // CTA-pair kernel: stage tiles in smem + bulk copies
 
+    // Background work: something the epilogue warps do while no accumulator is ready (pushing a
+    // gathered operand, reducing scattered tiles). `State` carries its progress.
     struct State {};
+    static constexpr bool kBackground = false;
+    __device__ static void init_state(State& st, const RankParams& p, int cta, int nctas) {}
+    // one bounded slice of background work; false = nothing (more) to do right now.
+    // `bcast` is a shared-memory word the 128 epilogue threads may use to agree on a decision.
+    template <typename OutT>
+    __device__ static bool background(const RankParams& p, State& st, int cta, int nctas, int epi_tid, volatile uint32_t* bcast) { return false; }
+    static constexpr bool kPushFirst = false;
 
     __device__ static int num_tiles(const RankParams& p, int mb, int nb) { return mb * nb; }
     __device__ static TileCoord tile(const RankParams& p, int t, int mb, int nb) { return raster(t, mb, nb); }
@@ -80,15 +89,14 @@ struct PlainPolicy {
         }
     }
     // called by all 128 epilogue threads before their first tile
-    __device__ static void prologue(const RankParams& p, int cta, int epi_tid) {}
+    __device__ static void prologue(const RankParams& p, int cta, int nctas, int epi_tid) {}
     // called by all 128 epilogue threads after every tile
     __device__ static void tile_done(const RankParams& p, const TileCoord& tc, int epi_tid) {}
     // called by all epilogue threads once the CTA has no more tiles
     template <typename OutT>
-    __device__ static void tail(const RankParams& p, int cta, int nctas, int epi_tid) {}
+    __device__ static void tail(const RankParams& p, State& st, int cta, int nctas, int epi_tid, volatile uint32_t* bcast) {}
     // body of a communication CTA (only if kCommCtas)
     __device__ static void comm_cta(const RankParams& p, int comm_cta, int ncomm) {}
-    __device__ static void comm_cta_bulk(const RankParams& p, int comm_cta, int ncomm, uint8_t* smem) {}
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -203,7 +211,15 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_kernel(const __grid_const
         const int q = warp & 3;                  // TMEM lane quarter this warp may access
         const int epi_tid = (warp - EPI_WARP0) * 32 + lane;
         int local = 0;
-        Policy::prologue(p, cta, epi_tid);
+        typename Policy::State st;
+        volatile uint32_t* bcast = sm.tmem_base + 1;
+        Policy::init_state(st, p, cta, nctas);
+        Policy::prologue(p, cta, nctas, epi_tid);
+        if constexpr (Policy::kBackground) {
+            // single-CTA kernel: no interleaving, pushes are finished up front
+            if (Policy::kPushFirst)
+                while (Policy::template background<OutT>(p, st, cta, nctas, epi_tid, bcast)) {}
+        }
         for (int t = cta; t < ntiles; t += nctas, ++local) {
             const TileCoord tc = Policy::tile(p, t, m_blocks, n_blocks);
             const int acc = local & 1;
@@ -227,7 +243,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_kernel(const __grid_const
             }
             Policy::tile_done(p, tc, epi_tid);
         }
-        Policy::template tail<OutT>(p, cta, nctas, epi_tid);
+        Policy::template tail<OutT>(p, st, cta, nctas, epi_tid, bcast);
     }
 
     // ---- teardown ----

@@ -78,8 +78,7 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
     if constexpr (Policy::kCommCtas) {
         const int ncomm = p.num_comm_ctas;  // even: whole clusters
         if (cta < ncomm) {
-            if (p.aux1 & 2) Policy::comm_cta_bulk(p, cta, ncomm, base);   // bit 1: drive the bulk-copy engine
-            else Policy::comm_cta(p, cta, ncomm);                         // default: vectorised register copies
+            Policy::comm_cta(p, cta, ncomm);
             return;
         }
         cta -= ncomm;
@@ -200,12 +199,28 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
         const int q = warp & 3;
         const int epi_tid = (warp - EPI_WARP0) * 32 + lane;
         int local = 0;
-        Policy::prologue(p, cta, epi_tid);
+        typename Policy::State st;
+        volatile uint32_t* bcast = tmem_slot + 2;          // two words: ping-pong decision broadcast
+        Policy::init_state(st, p, cta, nctas);
+        Policy::prologue(p, cta, nctas, epi_tid);
+        uint32_t poll = 0;
         for (int t = pair; t < ntiles; t += npairs, ++local) {
             const TileCoord tc = my_tile(t);
             const bool valid = tc.m_blk < m_blocks;
             const int acc = local & 1;
             const uint32_t acc_phase = (local >> 1) & 1;
+            if constexpr (Policy::kBackground) {
+                // While the MMAs of this tile are still running, spend the time on the policy's
+                // background work, one bounded slice at a time; the decision is taken by one
+                // thread and shared, because slices contain barriers of the 128 epilogue threads.
+                for (;;) {
+                    volatile uint32_t* w = bcast + (poll++ & 1);
+                    if (epi_tid == 0) *w = ptx::mbar_test_wait(&tmem_full[acc], acc_phase) ? 1u : 0u;
+                    epi_bar_sync();
+                    if (*w != 0) break;
+                    if (!Policy::template background<OutT>(p, st, cta, nctas, epi_tid, bcast + 2)) break;
+                }
+            }
             ptx::mbar_wait(&tmem_full[acc], acc_phase, 400 + acc);
             ptx::tc_fence_after();
             const int row = tc.m_blk * BM + q * 32 + lane;
@@ -270,7 +285,7 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
             }
             if (valid) Policy::tile_done(p, tc, epi_tid);
         }
-        Policy::template tail<OutT>(p, cta, nctas, epi_tid);
+        Policy::template tail<OutT>(p, st, cta, nctas, epi_tid, bcast + 2);
     }
 
     // ---- teardown: nobody leaves (or frees TMEM) while the partner may still read its smem ----

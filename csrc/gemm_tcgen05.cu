@@ -40,7 +40,9 @@ int pick_bn(int M, int N, int sms) {
         return edge * (double)tiles / (double)(waves * sms);
     };
     if (N <= 128) return 128;
-    return (eff(256) >= 0.92 * eff(128)) ? 256 : 128;
+    // the 256-wide tile does ~1.4x the work per byte moved; the narrow one only pays off when the
+    // wide one would leave a large part of the last wave idle
+    return (eff(256) >= 0.75 * eff(128)) ? 256 : 128;
 }
 
 bool use_2cta() {

@@ -56,7 +56,7 @@ struct alignas(64) RankParams {
     int flag_base;        // first user flag word used by this launch
     unsigned int epoch;   // value flags must reach for this launch
     int num_comm_ctas;    // CTAs (per rank) that move data instead of computing tiles
-    int aux0, aux1;
+    int aux0, aux1, aux2;
 };
 
 struct Launch {
