@@ -384,7 +384,7 @@ allgather_kernel(const __grid_constant__ Launch lp, size_t src_off, size_t dst_o
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             const size_t i = i0 + u * stride;
-            const size_t row = i / wpr, w = i - row * wpr;
+            const size_t row = rows == 1 ? 0 : i / wpr, w = i - row * wpr;       // flat case: no 64-bit divide
             v[u] = *reinterpret_cast<const WT*>(src + row * src_row_stride + w * W);
             d[u] = dst_off + row * dst_row_stride + col0 + w * W;
         }
@@ -431,7 +431,7 @@ reduce_scatter_kernel(const __grid_constant__ Launch lp, size_t src_off, size_t 
 #pragma unroll
             for (int u = 0; u < U; ++u) {
                 const size_t i = i0 + u * stride;
-                const size_t row = i / vpr, w = i - row * vpr;
+                const size_t row = rows == 1 ? 0 : i / vpr, w = i - row * vpr;   // flat case: no 64-bit divide
                 so[u] = src_off + row * src_row_stride + col0 + w * 16;
                 dofs[u] = row * dst_row_stride + w * 16;
             }
@@ -460,7 +460,7 @@ reduce_scatter_kernel(const __grid_constant__ Launch lp, size_t src_off, size_t 
             }
         };
         if (MC) for_range_unrolled<8>(0, total, x, body);
-        else if (c.size <= 2) for_range_unrolled<4>(0, total, x, body);
+        else if (c.size <= 2) for_range_unrolled<8>(0, total, x, body);
         else if (c.size <= 4) for_range_unrolled<2>(0, total, x, body);
         else for_range_unrolled<1>(0, total, x, body);
     } else {
@@ -713,7 +713,7 @@ extern "C" int ccmpi_allreduce(const ccmpi_dev_comm* comms, int nvr, int algo, i
                              ((src_off | dst_off) & 15) == 0 && (bytes % 32) == 0;
         const bool vec_ok = ((src_off | dst_off | tmp_off) & 15) == 0 && bytes % 16 == 0;
         if (bytes <= 256 * 1024 || !vec_ok) algo = CCMPI_AR_ONESHOT;
-        else algo = nvls_ok ? CCMPI_AR_NVLS : CCMPI_AR_TWOSHOT;
+        else algo = (nvls_ok && lp.c[0].size > 2) ? CCMPI_AR_NVLS : CCMPI_AR_TWOSHOT;   // measured: P2P wins at n = 2
     }
     switch (dtype) {
         case CCMPI_F32: return allreduce_op<float>(lp, nvr, algo, op, src_off, dst_off, tmp_off, count, scale, out_dtype, dtype, max_blocks, st);

@@ -119,7 +119,29 @@ def check_point_to_point():
         np.testing.assert_array_equal(buf, np.arange(400_000) + j)
 
 
+def check_device_put_signal():
+    """put-with-signal mailbox kernels (the device-side Send/Recv primitive): ring exchange."""
+    from collective_communication_mpi_b200.ops import collectives as CO
+    dev = world.device_comm()
+    heap = dev.heap
+    src = world.symm_empty(4096, torch.float32)
+    dst = world.symm_empty(4096, torch.float32)
+    nxt, prv = (rank + 1) % n, (rank - 1) % n
+    base = 12000                                   # flag words nobody else uses in this test
+    for it in range(3):
+        src.fill_(float(rank * 10 + it))
+        torch.cuda.synchronize()
+        world.Barrier()
+        CO.put_signal(dev.comm, nxt, heap.offset_of(src), heap.offset_of(dst), src.numel() * 4, base + 2 * rank)
+        CO.wait_signal(dev.comm, prv, base + 2 * prv)
+        torch.cuda.synchronize()
+        assert bool((dst == float(prv * 10 + it)).all()), (rank, it, dst[:4].tolist())
+        world.Barrier()
+
+
 check_buffer_collectives(world, list(range(n)))
+if CUDA and n >= 2:
+    check_device_put_signal()
 if n >= 4:
     # sub-communicators: interleaved groups (the dp_comm pattern: stride = number of groups)
     sub = world.Split(color=rank % 2, key=rank)
