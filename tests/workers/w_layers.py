@@ -15,8 +15,8 @@ rank, n = world.Get_rank(), world.Get_size()
 assert n == mp * dp
 torch.cuda.set_device(rank)
 mp_idx, dp_idx, mp_comm, dp_comm, _, _ = get_info(comm=world, rank=rank, mp_size=mp, dp_size=dp, fc_layer="fc_q",
-                                                  in_dim=512, out_dim=512)
-H, TOK = 512, 256
+                                                  in_dim=1024, out_dim=1024)
+H, TOK = (512 if mp <= 4 else 1024), 256     # every scattered chunk must be >= 128 wide
 model = TransformerFCBlock(mp_comm, TOK, H, ffn_mult=4, seed=7, num_comm_ctas=2)
 
 # global batch: dp replicas x TOK tokens, feature-sharded over mp
