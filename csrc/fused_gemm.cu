@@ -74,7 +74,8 @@ extern "C" int ccmpi_fused_ag_gemm(const ccmpi_dev_comm* comms, int nvr, size_t 
         rp.epoch = epoch;
         rp.num_comm_ctas = ncomm;
         rp.aux0 = ldx;
-        rp.aux1 = use_mc ? 1 : 0;
+        static const int env_push_first = [] { const char* e = getenv("CCMPI_AG_PUSH_FIRST"); return e ? atoi(e) : 0; }();
+        rp.aux1 = (use_mc ? 1 : 0) | (env_push_first ? 4 : 0);
         rp.aux2 = gemm_ctas;   // contributions per ready flag and launch: keep num_sms fixed per context
     }
     if (pairs)

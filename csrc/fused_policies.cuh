@@ -91,20 +91,94 @@ struct AgKPolicy : PlainPolicy {
     // the producer / MMA warps already work on the local K-chunk.
     static constexpr bool kBackground = true;
     static constexpr bool kPushFirst = true;
+    static constexpr bool kNeedsStaging = true;
     struct State {
-        long long base;   // first vector index of this CTA's next batch
+        long long base;   // first work-item index of this CTA's next batch
         int flagged;      // m-blocks [0, flagged) already signalled by this CTA
         int m_blocks;
+        uint32_t stg;     // this lane's staging row in shared memory (0: register path)
+        uint64_t* wbar;   // this warp's mbarrier for the bulk loads
+        uint32_t phase;
     };
-    __device__ static void init_state(State& st, const RankParams& p, int cta, int nctas) {
+    __device__ static void init_state(State& st, const RankParams& p, int cta, int nctas, int epi_tid, uint32_t stg, uint64_t* wbar) {
         st.base = (long long)cta * EPI_THREADS;
         st.flagged = 0;
         st.m_blocks = p.comm.size == 1 ? 0 : (p.M + BM - 1) / BM;
+        st.stg = stg;
+        st.wbar = wbar;
+        st.phase = 0;
+        if (stg != 0) {
+            if ((epi_tid & 31) == 0) {
+                ptx::mbar_init(wbar, 32);
+                ptx::fence_mbar_init();
+            }
+            __syncwarp();
+        }
     }
 
-    // One batch of the push: 8 vectors per epilogue thread. Returns false once everything is out.
+    // Bulk-copy flavour of the push (CTA-pair kernel): every epilogue lane moves one 256-byte
+    // piece of the shard per slice -- cp.async.bulk global -> its staging row, then one
+    // cp.async.bulk per member out of it. The copies run on the TMA engine, so NVLink sees
+    // 256-byte bursts from ~19 k lanes at once instead of 16-byte stores that a few warps per SM
+    // cannot keep in flight.
     template <typename OutT>
     __device__ static bool background(const RankParams& p, State& st, int cta, int nctas, int epi_tid, volatile uint32_t* bcast) {
+        if (st.flagged >= st.m_blocks) return false;
+        if (st.stg == 0) return background_regs<OutT>(p, st, cta, nctas, epi_tid, bcast);
+        const ccmpi_dev_comm& c = p.comm;
+        const int row_bytes = p.chunk * 2;
+        const int PB = (row_bytes % 256 == 0) ? 256 : 128;         // piece size
+        const int ppr = row_bytes / PB;                            // pieces per shard row
+        const long long total = (long long)p.M * ppr;
+        const long long per_blk = (long long)BM * ppr;
+        const long long stride = (long long)nctas * EPI_THREADS;
+        const uint8_t* x = c.heap[c.rank] + p.off0;
+        const size_t src_ld = (size_t)p.aux0 * 2, dst_ld = (size_t)p.K * 2;
+        const size_t col0 = (size_t)c.rank * row_bytes;
+        const long long i = st.base + epi_tid;
+        const bool ok = i < total;
+        ptx::tma_store_wait_read<0>();                             // my previous piece has left my row
+        ptx::mbar_arrive_expect_tx(st.wbar, ok ? (uint32_t)PB : 0u);
+        size_t d = 0;
+        if (ok) {
+            const long long row = i / ppr;
+            const int w = (int)(i - row * ppr);
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(st.stg),
+                         "l"(x + (size_t)row * src_ld + (size_t)w * PB), "r"(PB), "r"(ptx::smem_u32(st.wbar))
+                         : "memory");
+            d = p.off1 + (size_t)row * dst_ld + col0 + (size_t)w * PB;
+        }
+        ptx::mbar_wait(st.wbar, st.phase, 800);
+        st.phase ^= 1;
+        if (ok) {
+#pragma unroll
+            for (int s = 0; s < CCMPI_MAX_RANKS; ++s)
+                if (s < c.size) ptx::bulk_s2g(c.heap[(c.rank + s) % c.size] + d, st.stg, PB);
+        }
+        ptx::tma_store_commit();
+        const long long next = st.base + stride;
+        int done = (int)min((long long)st.m_blocks, next / per_blk);
+        constexpr int GRANULE = 16;
+        done = (done / GRANULE) * GRANULE;
+        if (next >= total) done = st.m_blocks;
+        st.base = next;
+        if (done <= st.flagged) return true;
+        ptx::tma_store_wait<0>();          // my pieces have landed ...
+        ptx::fence_proxy_async_all();      // ... and are ordered before the flag traffic
+        epi_bar_sync();
+        if (epi_tid == 0) {
+            ptx::fence_acq_rel_sys();
+            for (int j = st.flagged; j < done; ++j)
+                for (int s = 1; s < c.size; ++s)
+                    ptx::red_relaxed_sys_add(user_flag(c, (c.rank + s) % c.size, ready_idx(p, c.rank, j)), 1u);
+        }
+        st.flagged = done;
+        return true;
+    }
+
+    // Register flavour (single-CTA kernel, which has no staging rows): 8 vectors per thread.
+    template <typename OutT>
+    __device__ static bool background_regs(const RankParams& p, State& st, int cta, int nctas, int epi_tid, volatile uint32_t* bcast) {
         if (st.flagged >= st.m_blocks) return false;
         const ccmpi_dev_comm& c = p.comm;
         const int vpr = p.chunk / 8;                        // 16-byte vectors per shard row
@@ -145,7 +219,16 @@ struct AgKPolicy : PlainPolicy {
         // every vector of this CTA below `next` is on its way
         const long long next = st.base + U * stride;
         int done = (int)min((long long)st.m_blocks, next / per_blk);
+        // Flags go out once per raster group (16 m-blocks = what the consumers' rasters sweep
+        // before moving on), not once per batch: each signal costs a system-scope fence that
+        // waits for this CTA's remote stores, and the other epilogue threads wait for it.
+        constexpr int GRANULE = 16;
+        done = (done / GRANULE) * GRANULE;
         if (next >= total) done = st.m_blocks;
+        if (done <= st.flagged) {       // uniform across the CTA: nothing to publish yet
+            st.base = next;
+            return true;
+        }
         epi_bar_sync();
         if (epi_tid == 0 && done > st.flagged) {
             // one system-scope fence orders every push of this CTA (cumulative over the barrier)
@@ -182,6 +265,7 @@ struct AgKPolicy : PlainPolicy {
 struct RsNPolicy : PlainPolicy {
     static constexpr bool kCommCtas = false;
     static constexpr bool kStagedStore = true;
+    static constexpr bool kNeedsStaging = true;
 
     // CTA-pair kernel: one row chunk of a partial tile, already in shared memory, goes to the
     // owner's slot for this source rank in a single bulk copy
@@ -318,7 +402,7 @@ struct RsNPolicy : PlainPolicy {
     // so that little is left for the tail.
     static constexpr bool kBackground = true;
     struct State { int next; };
-    __device__ static void init_state(State& st, const RankParams& p, int cta, int nctas) { st.next = cta; }
+    __device__ static void init_state(State& st, const RankParams& p, int cta, int nctas, int epi_tid, uint32_t stg, uint64_t* wbar) { st.next = cta; }
 
     template <typename OutT, bool BROADCAST>
     __device__ static bool try_reduce(const RankParams& p, State& st, int nctas, int epi_tid, volatile uint32_t* bcast) {
@@ -388,6 +472,7 @@ struct ArPolicy : RsNPolicy {
 // ================================================================================================
 struct AgOutPolicy : PlainPolicy {
     static constexpr bool kStagedStore = true;
+    static constexpr bool kNeedsStaging = true;
 
     template <typename OutT>
     __device__ static void bulk_row(const RankParams& p, const TileCoord& tc, int row, int col0, uint32_t smem_row, int bytes) {

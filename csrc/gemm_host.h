@@ -37,14 +37,14 @@ int launch2(const Launch& lp, int grid, cudaStream_t stream, bool cooperative) {
     auto kern = gemm_kernel_2cta<BN, A_MN, B_MN, OutT, Policy>;
     static bool configured = false;
     if (!configured) {
-        CCMPI_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg2<BN, Policy::kStagedStore>::SMEM_BYTES));
+        CCMPI_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg2<BN, Policy::kNeedsStaging>::SMEM_BYTES));
         configured = true;
     }
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof(cfg));
     cfg.gridDim = dim3(grid);          // even: the kernel carries __cluster_dims__(2,1,1)
     cfg.blockDim = dim3(NUM_THREADS);
-    cfg.dynamicSmemBytes = Cfg2<BN, Policy::kStagedStore>::SMEM_BYTES;
+    cfg.dynamicSmemBytes = Cfg2<BN, Policy::kNeedsStaging>::SMEM_BYTES;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeCooperative;

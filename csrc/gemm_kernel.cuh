@@ -55,12 +55,15 @@ __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;"
 struct PlainPolicy {
     static constexpr bool kCommCtas = false;
     static constexpr bool kStagedStore = false;   // CTA-pair kernel: stage tiles in smem + bulk copies
+    static constexpr bool kNeedsStaging = false;  // CTA-pair kernel: reserve the per-lane staging rows
 
     // Background work: something the epilogue warps do while no accumulator is ready (pushing a
     // gathered operand, reducing scattered tiles). `State` carries its progress.
     struct State {};
     static constexpr bool kBackground = false;
-    __device__ static void init_state(State& st, const RankParams& p, int cta, int nctas) {}
+    // `stg` = this lane's 256-byte staging row (0 if the kernel has none), `wbar` = an mbarrier
+    // private to this epilogue warp (nullptr if none)
+    __device__ static void init_state(State& st, const RankParams& p, int cta, int nctas, int epi_tid, uint32_t stg, uint64_t* wbar) {}
     // one bounded slice of background work; false = nothing (more) to do right now.
     // `bcast` is a shared-memory word the 128 epilogue threads may use to agree on a decision.
     template <typename OutT>
@@ -213,7 +216,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_kernel(const __grid_const
         int local = 0;
         typename Policy::State st;
         volatile uint32_t* bcast = sm.tmem_base + 1;
-        Policy::init_state(st, p, cta, nctas);
+        Policy::init_state(st, p, cta, nctas, epi_tid, 0u, nullptr);
         Policy::prologue(p, cta, nctas, epi_tid);
         if constexpr (Policy::kBackground) {
             // single-CTA kernel: no interleaving, pushes are finished up front

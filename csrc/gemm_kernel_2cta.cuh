@@ -49,7 +49,7 @@ struct Cfg2 {
 template <int BN, bool A_MN, bool B_MN, typename OutT, typename Policy>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 gemm_kernel_2cta(const __grid_constant__ Launch lp) {
-    using C = Cfg2<BN, Policy::kStagedStore>;
+    using C = Cfg2<BN, Policy::kNeedsStaging>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint64_t* bars = reinterpret_cast<uint64_t*>(base + C::STAGES * C::STAGE_BYTES);
@@ -201,8 +201,15 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
         int local = 0;
         typename Policy::State st;
         volatile uint32_t* bcast = tmem_slot + 2;          // two words: ping-pong decision broadcast
-        Policy::init_state(st, p, cta, nctas);
+        Policy::init_state(st, p, cta, nctas, epi_tid,
+                           Policy::kNeedsStaging ? ptx::smem_u32(stg_base) + epi_tid * STG_ROW_STRIDE : 0u,
+                           reinterpret_cast<uint64_t*>(tmem_slot + 8) + (warp - EPI_WARP0));
         Policy::prologue(p, cta, nctas, epi_tid);
+        if constexpr (Policy::kBackground) {
+            // diagnostic switch (aux1 bit 2): do all pushes up front instead of in the gaps
+            if (Policy::kPushFirst && (p.aux1 & 4))
+                while (Policy::template background<OutT>(p, st, cta, nctas, epi_tid, bcast + 2)) {}
+        }
         uint32_t poll = 0;
         for (int t = pair; t < ntiles; t += npairs, ++local) {
             const TileCoord tc = my_tile(t);
