@@ -65,11 +65,32 @@ def _headers_digest() -> str:
 
 
 def _stamp(src: Path, flags, hdr: str) -> str:
+    """Content hash of everything that determines an object file. Include paths are left out on
+    purpose: the repository is built in one place and loaded from another (the GPU boxes mount it
+    under a different path), and a stamp that changed with the checkout location would trigger a
+    rebuild -- by every rank at once -- on first import there."""
     h = hashlib.sha1()
     h.update(src.read_bytes())
-    h.update(" ".join(flags).encode())
+    h.update(" ".join(f for f in flags if not f.startswith("-I")).encode())
     h.update(hdr.encode())
     return h.hexdigest()
+
+
+class _BuildLock:
+    """Exclusive inter-process lock: ranks that find the libraries stale build one at a time (the
+    first does the work, the others see up-to-date stamps when their turn comes)."""
+
+    def __enter__(self):
+        import fcntl
+        OBJDIR.mkdir(parents=True, exist_ok=True)
+        self.f = open(OBJDIR / ".lock", "w")
+        fcntl.flock(self.f, fcntl.LOCK_EX)
+        return self
+
+    def __exit__(self, *exc):
+        import fcntl
+        fcntl.flock(self.f, fcntl.LOCK_UN)
+        self.f.close()
 
 
 def _compile(cmd, obj: Path, stamp: str, verbose: bool):
@@ -86,7 +107,15 @@ def _compile(cmd, obj: Path, stamp: str, verbose: bool):
 
 
 def build(verbose: bool = False, force: bool = False) -> dict:
-    """Compile whatever is out of date. Returns ``{"device": path, "host": path}``."""
+    """Compile whatever is out of date. Returns ``{"device": path, "host": path}``. Safe to call
+    from several processes at once."""
+    with _BuildLock():
+        if not force and up_to_date():
+            return {"device": DEVICE_LIB, "host": HOST_LIB}
+        return _build_locked(verbose, force)
+
+
+def _build_locked(verbose: bool, force: bool) -> dict:
     LIBDIR.mkdir(parents=True, exist_ok=True)
     OBJDIR.mkdir(parents=True, exist_ok=True)
     dev, host = _sources()
@@ -114,16 +143,20 @@ def build(verbose: bool = False, force: bool = False) -> dict:
     dev_changed = any(changed[: len(dev)]) or not DEVICE_LIB.exists()
     host_changed = any(changed[len(dev):]) or not HOST_LIB.exists()
     if dev_objs and dev_changed:
-        cmd = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", str(DEVICE_LIB), *map(str, dev_objs),
+        tmp = DEVICE_LIB.with_suffix(f".so.tmp{os.getpid()}")
+        cmd = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", str(tmp), *map(str, dev_objs),
                "-cudart", "static", "-lpthread", "-ldl", "-lrt"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed: {' '.join(cmd)}\n{r.stdout}\n{r.stderr}")
+        os.replace(tmp, DEVICE_LIB)   # a process that already mapped the old file keeps a valid image
     if host_objs and host_changed:
-        cmd = [gxx, "-shared", "-o", str(HOST_LIB), *map(str, host_objs), "-pthread", "-lrt"]
+        tmp = HOST_LIB.with_suffix(f".so.tmp{os.getpid()}")
+        cmd = [gxx, "-shared", "-o", str(tmp), *map(str, host_objs), "-pthread", "-lrt"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed: {' '.join(cmd)}\n{r.stdout}\n{r.stderr}")
+        os.replace(tmp, HOST_LIB)
     return {"device": DEVICE_LIB, "host": HOST_LIB}
 
 
