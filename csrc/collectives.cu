@@ -460,7 +460,7 @@ reduce_scatter_kernel(const __grid_constant__ Launch lp, size_t src_off, size_t 
             }
         };
         if (MC) for_range_unrolled<8>(0, total, x, body);
-        else if (c.size <= 2) for_range_unrolled<8>(0, total, x, body);
+        else if (c.size <= 2) for_range_unrolled<4>(0, total, x, body);   // 8 would spill: r[U][8] registers
         else if (c.size <= 4) for_range_unrolled<2>(0, total, x, body);
         else for_range_unrolled<1>(0, total, x, body);
     } else {
