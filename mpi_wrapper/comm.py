@@ -24,8 +24,11 @@ from __future__ import annotations
 import numpy as np
 from mpi4py import MPI
 
+import time as _time
+
 from collective_communication_mpi_b200 import _native as _N
 from collective_communication_mpi_b200.mpi import core as _core
+from collective_communication_mpi_b200.utils.timing import OpStats as _OpStats
 
 _ALGOS = {"auto": _N.AR_AUTO, "oneshot": _N.AR_ONESHOT, "twoshot": _N.AR_TWOSHOT, "nvls": _N.AR_NVLS,
           "multicast": _N.AR_NVLS}
@@ -45,6 +48,8 @@ class Communicator(object):
     def __init__(self, comm: MPI.Comm):
         self.comm = comm
         self.total_bytes_transferred = 0
+        # beyond the reference's single byte counter: per-op calls / payload bytes / wall seconds
+        self.stats = _OpStats()
 
     # ---- passthroughs (reference :9-16) -------------------------------------------------
     def Get_size(self):
@@ -60,15 +65,21 @@ class Communicator(object):
     def Allreduce(self, src_array, dest_array, op=MPI.SUM):
         assert _count(src_array) == _count(dest_array)
         self._account(2 * _nbytes(src_array))
+        t0 = _time.perf_counter()
         self.comm.Allreduce(src_array, dest_array, op)
+        self.stats.add("Allreduce", _nbytes(src_array), _time.perf_counter() - t0)
 
     def Allgather(self, src_array, dest_array):
         self._account(_nbytes(src_array) + _nbytes(dest_array))
+        t0 = _time.perf_counter()
         self.comm.Allgather(src_array, dest_array)
+        self.stats.add("Allgather", _nbytes(dest_array), _time.perf_counter() - t0)
 
     def Reduce_scatter(self, src_array, dest_array, op=MPI.SUM):
         self._account(_nbytes(src_array) + _nbytes(dest_array))
+        t0 = _time.perf_counter()
         self.comm.Reduce_scatter_block(src_array, dest_array, op)
+        self.stats.add("Reduce_scatter", _nbytes(src_array), _time.perf_counter() - t0)
 
     def Split(self, key, color):
         # (key, color) order is the reference's (comm.py:38), the reverse of MPI's
@@ -79,7 +90,9 @@ class Communicator(object):
         assert _count(src_array) % n == 0, "src_array size must be divisible by the number of processes"
         assert _count(dest_array) % n == 0, "dest_array size must be divisible by the number of processes"
         self._account(_nbytes(src_array) // n + _nbytes(dest_array) // n)
+        t0 = _time.perf_counter()
         self.comm.Alltoall(src_array, dest_array)
+        self.stats.add("Alltoall", _nbytes(src_array), _time.perf_counter() - t0)
 
     # ---- the hand-rolled collectives, re-designed (reference :63-199) -------------------
     def myAllreduce(self, src_array, dest_array, op=MPI.SUM, algo: str = "auto"):
