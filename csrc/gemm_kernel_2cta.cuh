@@ -46,9 +46,15 @@ struct Cfg2 {
     static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget exceeded");
 };
 
-template <int BN, bool A_MN, bool B_MN, typename OutT, typename Policy>
+// EB = bytes per input element: 2 = bf16 (kind::f16), 1 = fp8 e4m3 (kind::f8f6f4, K-major operands
+// only). A K-block is always one 128-byte swizzle row, i.e. 64 bf16 or 128 fp8 elements, and an MMA
+// always consumes 32 bytes of K, so the shared-memory descriptors and the pipeline are identical;
+// only the instruction kind, the instruction descriptor and the K coordinates differ.
+template <int BN, bool A_MN, bool B_MN, typename OutT, typename Policy, int EB = 2>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 gemm_kernel_2cta(const __grid_constant__ Launch lp) {
+    static_assert(EB == 2 || (EB == 1 && !A_MN && !B_MN), "fp8 operands must be K-major");
+    constexpr int KSCALE = 2 / EB;   // policies count K in bf16-sized elements (BK = 64 per block)
     using C = Cfg2<BN, Policy::kNeedsStaging>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -89,7 +95,7 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
     const int m_blocks = (p.M + BM - 1) / BM;
     const int m_pairs = (m_blocks + 1) / 2;
     const int n_blocks = (p.N + BN - 1) / BN;
-    const int k_blocks = (p.K + BK - 1) / BK;
+    const int k_blocks = (p.K + BK * KSCALE - 1) / (BK * KSCALE);
     const int ntiles = Policy::num_tiles(p, m_pairs, n_blocks);
 
     auto my_tile = [&](int t) {
@@ -141,6 +147,10 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
                         a_k0 = k0;
                         a_m0 = tc.m_blk * BM;
                     }
+                    if constexpr (KSCALE != 1) {
+                        k0 *= KSCALE;
+                        a_k0 *= KSCALE;
+                    }
                     ptx::mbar_wait(&empty[stage], phase ^ 1, 100 + stage);
                     if (leader) ptx::mbar_arrive_expect_tx(&full[stage], 2 * C::STAGE_BYTES);
                     else ptx::mbar_arrive_cluster(&full[stage], 0);
@@ -167,7 +177,8 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
     } else if (warp == 1) {
         // ===================== MMA issuer (leader CTA only) =====================
         if (leader && lane == 0) {
-            constexpr uint32_t idesc = ptx::umma_idesc(1, 1, A_MN, B_MN, 2 * BM, BN);
+            constexpr uint32_t idesc = EB == 2 ? ptx::umma_idesc(1, 1, A_MN, B_MN, 2 * BM, BN)     // bf16 x bf16
+                                               : ptx::umma_idesc(0, 0, false, false, 2 * BM, BN);  // e4m3 x e4m3
             int stage = 0;
             uint32_t phase = 0;
             int local = 0;
@@ -184,8 +195,12 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
                     const uint32_t b_addr = ptx::smem_u32(smem_b(stage));
 #pragma unroll
                     for (int ks = 0; ks < BK / UMMA_K; ++ks) {
-                        ptx::umma_f16_ss_2sm(tmem_d, operand_desc<A_MN>(a_addr, ks), operand_desc<B_MN>(b_addr, ks),
-                                             idesc, (it | ks) != 0 ? 1u : 0u);
+                        if constexpr (EB == 2)
+                            ptx::umma_f16_ss_2sm(tmem_d, operand_desc<A_MN>(a_addr, ks), operand_desc<B_MN>(b_addr, ks),
+                                                 idesc, (it | ks) != 0 ? 1u : 0u);
+                        else
+                            ptx::umma_f8_ss_2sm(tmem_d, operand_desc<A_MN>(a_addr, ks), operand_desc<B_MN>(b_addr, ks),
+                                                idesc, (it | ks) != 0 ? 1u : 0u);
                     }
                     ptx::umma_commit_2sm(&empty[stage], 0b11);
                     if (++stage == C::STAGES) { stage = 0; phase ^= 1; }

@@ -204,6 +204,13 @@ int ccmpi_fused_gemm_ag(const ccmpi_dev_comm* comms, int nvr, const void* const*
                         size_t yfull_off, int M, int N, int K, int lda, int ldb, int a_km, int b_kn,
                         int out_dtype, int num_sms, int use_mc, void* stream);
 
+/* EXPERIMENTAL (compiled, not yet run on hardware in round 1): fp8 e4m3 GEMM on the CTA-pair
+ * kernel, C[M][N] = scale * A[M][K] * B[N][K]^T, both operands K-major (tcgen05.mma.kind::f8f6f4).
+ * First step towards the block-scaled fp8 FC layers of BASELINE.md config 3; the reference has no
+ * GEMM at all. */
+int ccmpi_gemm_fp8_e4m3(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb,
+                        int ldc, float scale, int out_dtype, int num_sms, void* stream);
+
 /* No counterpart in the reference: it never allocates device memory because it has no device
  * code. This is the GEMM -> reduce-scatter kernel of ccmpi_fused_gemm_rs for a ONE-GPU
  * communicator (C[M][N] = A * B), for callers that must not allocate device memory when they
