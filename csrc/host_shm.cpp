@@ -525,6 +525,14 @@ extern "C" int ccmpi_host_allreduce(int64_t h, int slot, const int* members, int
         const size_t len = std::min(chunk, count - base);
         memcpy(H->in_area(H->rank), (const char*)src + base * es, len * es);
         if ((rc = barrier(H, slot, n))) return rc;
+        if (len * es <= 32 * 1024) {
+            // small: every member folds all inputs itself, straight into dst -- two barriers, no
+            // result area
+            for (int j = 0; j < n; ++j) srcs[j] = H->in_area(members[j]);
+            if ((rc = reduce_many((char*)dst + base * es, srcs, n, len, dtype, op))) return rc;
+            if ((rc = barrier(H, slot, n))) return rc;
+            continue;
+        }
         const size_t per = (len + n - 1) / n;
         const size_t lo = std::min(len, per * me), hi = std::min(len, lo + per);
         if (hi > lo) {
@@ -536,6 +544,11 @@ extern "C" int ccmpi_host_allreduce(int64_t h, int slot, const int* members, int
             const size_t jlo = std::min(len, per * j), jhi = std::min(len, jlo + per);
             if (jhi > jlo) memcpy((char*)dst + (base + jlo) * es, H->res_area(members[j]) + jlo * es, (jhi - jlo) * es);
         }
+        // Nobody leaves while a member is still reading result areas: the staging areas belong to
+        // the RANK, not to the communicator, and a member that ran ahead into a collective of
+        // another communicator (whose barrier does not include the slow reader) would overwrite
+        // its result area under that reader.
+        if ((rc = barrier(H, slot, n))) return rc;
     }
     return 0;
 }

@@ -14,7 +14,7 @@ sub = w.Split(color=r % 2, key=r)
 for it in range(150):
     if rnd.random() < 0.3:
         time.sleep(rnd.random() * 0.003)                 # skewed arrival
-    cnt = 1 + (it * 37) % 3000
+    cnt = 1 + (it * 137) % 9000                      # both sides of the 32 KiB small/large switch
     x = np.full(cnt, r + it, dtype=np.int64); y = np.empty_like(x)
     w.Allreduce(x, y)
     assert y[0] == n * it + n * (n - 1) // 2 and y[-1] == y[0], (it, y[0])
@@ -26,6 +26,17 @@ for it in range(150):
         buf = np.full(size, (r * 31 + it) % 251, dtype=np.uint8); got = np.empty(size, dtype=np.uint8)
         w.Sendrecv(buf, dest=(r + 1) % n, sendtag=it, recvbuf=got, source=(r - 1) % n, recvtag=it)
         assert got[0] == (((r - 1) % n) * 31 + it) % 251 and got[-1] == got[0]
+    if it % 5 == 0:                                      # other collectives between the two communicators
+        k = sub.Get_size(); sr = sub.Get_rank()
+        a2a = np.empty(k * 3, dtype=np.int64)
+        sub.Alltoall(np.repeat(np.arange(k, dtype=np.int64) + 100 * sr + it, 3), a2a)
+        assert a2a.tolist() == [v for q in range(k) for v in [sr + 100 * q + it] * 3]
+        ag = np.empty(n * 5, dtype=np.float64)
+        w.Allgather(np.full(5, r * 2.0 + it), ag)
+        assert ag.tolist() == [q * 2.0 + it for q in range(n) for _ in range(5)]
+        rs = np.empty(4, dtype=np.int64)
+        w.Reduce_scatter_block(np.arange(4 * n, dtype=np.int64) + r, rs)
+        assert rs.tolist() == [n * (4 * r + j) + n * (n - 1) // 2 for j in range(4)]
     g = w.allgather((r, it))
     assert g == [(q, it) for q in range(n)]
 w.Barrier()
