@@ -204,6 +204,22 @@ int ccmpi_fused_gemm_ag(const ccmpi_dev_comm* comms, int nvr, const void* const*
                         size_t yfull_off, int M, int N, int K, int lda, int ldb, int a_km, int b_kn,
                         int out_dtype, int num_sms, int use_mc, void* stream);
 
+/* EXPERIMENTAL (compiled, not yet run on hardware in round 1): the token-axis ("sequence
+ * parallel") forms of the two kernels above (csrc/fused_gemm_m.cu, csrc/fused_policies_m.cuh).
+ * The reference shards only the feature axis; these cover layouts that shard the activation rows.
+ * M/n must be a multiple of 256. CTA-pair kernels only.
+ *   ag_gemm_m: C[M][N] = [x_0 ; ... ; x_{n-1}] * B, x_r = rank r's [M/n][K] rows at x_off (row
+ *              stride ldx); xfull_off: symmetric [M][K] that the members' rows are pushed into.
+ *   gemm_rs_m: C[M/n][N] = rank-ordered sum over ranks of (A*B)[own rows]; slots_off: symmetric
+ *              [n][M/n][N] staging of the output dtype. */
+int ccmpi_fused_ag_gemm_m(const ccmpi_dev_comm* comms, int nvr, size_t x_off, int ldx, size_t xfull_off,
+                          const void* const* B, void* const* C, int M, int N, int K, int ldb, int ldc,
+                          int b_kn, int out_dtype, int flag_base, unsigned epoch, int num_sms, void* stream);
+int ccmpi_fused_gemm_rs_m(const ccmpi_dev_comm* comms, int nvr, const void* const* A, const void* const* B,
+                          size_t slots_off, void* const* C, int M, int N, int K, int lda, int ldb, int ldc,
+                          int a_km, int b_kn, int out_dtype, int flag_base, unsigned epoch, int num_sms,
+                          void* stream);
+
 /* EXPERIMENTAL (compiled, not yet run on hardware in round 1): fp8 e4m3 GEMM on the CTA-pair
  * kernel, C[M][N] = scale * A[M][K] * B[N][K]^T, both operands K-major (tcgen05.mma.kind::f8f6f4).
  * First step towards the block-scaled fp8 FC layers of BASELINE.md config 3; the reference has no
