@@ -159,6 +159,15 @@ def _declare_device(lib):
         "ccmpi_fused_ag_gemm_m": (i, [P(DevComm), i, sz, i, sz, PV, PV, i, i, i, i, i, i, i, i, u, i, vp]),
         "ccmpi_fused_gemm_rs_m": (i, [P(DevComm), i, PV, PV, sz, PV, i, i, i, i, i, i, i, i, i, i, u, i, vp]),
     }
+    ll = C.c_longlong
+    fused.update({
+        "ccmpi_gate_fwd": (i, [vp, ll, vp, ll, i, i, vp]),
+        "ccmpi_gate_bwd": (i, [vp, ll, vp, ll, vp, ll, i, i, vp]),
+        "ccmpi_gelu_fwd": (i, [vp, vp, ll, vp]),
+        "ccmpi_gelu_bwd": (i, [vp, vp, vp, ll, vp]),
+        "ccmpi_mse_workspace_bytes": (sz, []),
+        "ccmpi_mse_fwd_bwd": (i, [vp, vp, vp, ll, vp, vp, vp]),
+    })
     for name, (res, args) in fused.items():
         fn = getattr(lib, name)
         fn.restype = res

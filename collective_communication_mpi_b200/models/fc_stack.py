@@ -18,6 +18,7 @@ from typing import List
 import torch
 from torch import nn
 
+from ..ops import elementwise as EW
 from ..parallel.dp import GradSink, sgd_step
 from ..parallel.tp_layers import ColumnParallelLinear, RowParallelLinear
 
@@ -31,11 +32,16 @@ class TransformerFCBlock(nn.Module):
         self.fc_o = RowParallelLinear(mp_comm, tokens, hidden, hidden, seed=seed + 2, num_comm_ctas=num_comm_ctas)
         self.fc1 = ColumnParallelLinear(mp_comm, tokens, hidden, ffn_mult * hidden, seed=seed + 3, num_comm_ctas=num_comm_ctas)
         self.fc2 = RowParallelLinear(mp_comm, tokens, ffn_mult * hidden, hidden, seed=seed + 4, num_comm_ctas=num_comm_ctas)
+        # opt-in (CCMPI_FUSED_ELEMENTWISE=1): one-pass gate / GELU kernels with hand-written backward
+        self.fused_elementwise = EW.enabled()
 
     def tp_layers(self) -> List[nn.Module]:
         return [self.fc_qkv, self.fc_o, self.fc1, self.fc2]
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if self.fused_elementwise:
+            h = x + self.fc_o(EW.gate(self.fc_qkv(x)))
+            return h + self.fc2(EW.gelu(self.fc1(h)))
         q, k, v = self.fc_qkv(x).chunk(3, dim=-1)
         a = v * torch.sigmoid(q * k)            # stand-in for attention: elementwise, keeps sharding
         h = x + self.fc_o(a)
@@ -68,11 +74,16 @@ class TrainStep:
         self.model, self.lr = model, lr
         self.sink = GradSink(dp_comm, model.tp_layers(), bucket_mb=bucket_mb, overlap=overlap)
         self.weights = [l.weight.data for l in model.tp_layers()]
+        self.fused_loss = EW.enabled()
 
     def __call__(self, x: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
         y = self.model(x)
-        loss = torch.nn.functional.mse_loss(y.float(), target.float())
-        loss.backward()
+        if self.fused_loss and y.dtype == torch.bfloat16 and target.dtype == torch.bfloat16:
+            loss, dy = EW.mse_loss_and_grad(y, target)      # loss and its gradient in one pass
+            y.backward(dy)
+        else:
+            loss = torch.nn.functional.mse_loss(y.float(), target.float())
+            loss.backward()
         self.sink.finish()
         sgd_step(self.weights, self.sink.grads(), self.lr)
         return loss.detach()

@@ -220,6 +220,22 @@ int ccmpi_fused_gemm_rs_m(const ccmpi_dev_comm* comms, int nvr, const void* cons
                           int a_km, int b_kn, int out_dtype, int flag_base, unsigned epoch, int num_sms,
                           void* stream);
 
+/* EXPERIMENTAL (compiled, not yet run on hardware in round 1): fused elementwise kernels of the
+ * transformer-FC block (csrc/elementwise.cu), bf16 in / bf16 out, fp32 math, one pass over HBM each.
+ * The reference has no compute; these sit between the GEMMs of models/fc_stack.py.
+ *   gate:  a[T][H] = v * sigmoid(q * k) with qkv[T][3H] = q | k | v; backward writes dq | dk | dv.
+ *   gelu:  tanh approximation, forward and backward, n contiguous elements.
+ *   mse:   loss[0] = mean((y - t)^2) and dy = 2 (y - t) / n in one pass; `workspace` holds
+ *          ccmpi_mse_workspace_bytes() bytes, zeroed once by the caller before the first call. */
+int ccmpi_gate_fwd(const void* qkv, long long ld_qkv, void* a, long long ld_a, int T, int H, void* stream);
+int ccmpi_gate_bwd(const void* da, long long ld_da, const void* qkv, long long ld_qkv, void* dqkv,
+                   long long ld_d, int T, int H, void* stream);
+int ccmpi_gelu_fwd(const void* u, void* y, long long n, void* stream);
+int ccmpi_gelu_bwd(const void* dy, const void* u, void* du, long long n, void* stream);
+size_t ccmpi_mse_workspace_bytes(void);
+int ccmpi_mse_fwd_bwd(const void* y, const void* t, void* dy, long long n, void* workspace, void* loss,
+                      void* stream);
+
 /* EXPERIMENTAL (compiled, not yet run on hardware in round 1): fp8 e4m3 GEMM on the CTA-pair
  * kernel, C[M][N] = scale * A[M][K] * B[N][K]^T, both operands K-major (tcgen05.mma.kind::f8f6f4).
  * First step towards the block-scaled fp8 FC layers of BASELINE.md config 3; the reference has no
