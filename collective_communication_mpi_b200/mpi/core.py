@@ -27,6 +27,7 @@ import numpy as np
 
 from .. import _native as N
 from ..runtime.world import World, wtime
+from . import p2p_device as P2P
 
 UNDEFINED = -32766
 ANY_SOURCE = -1
@@ -467,7 +468,11 @@ class Comm:
     def Isend(self, buf, dest: int, tag: int = 0) -> Request:
         b = _Buf(buf, False)
         w = self._world
-        host = _host_bytes(b)  # CUDA payloads are staged to the host for the mailbox path
+        if b.cuda and P2P.enabled() and w.device_available():
+            # opt-in NVLink route: the payload waits in the symmetric heap, a descriptor travels
+            host = P2P.stage_for_send(w, self._peer(dest), b.flat).view(np.uint8)
+        else:
+            host = _host_bytes(b)  # CUDA payloads are staged to the host for the mailbox path
         rid = w._hostlib.ccmpi_host_isend(w.host, self._peer(dest), self._cid, int(tag), host.ctypes.data, host.nbytes)
         N.check_host(rid, "Isend")
         return Request(w, rid, keep=(host, b))
@@ -477,7 +482,11 @@ class Comm:
             raise NotImplementedError("Irecv from ANY_SOURCE")
         b = _Buf(buf, True)
         w = self._world
-        if b.cuda:
+        if b.cuda and P2P.enabled() and w.device_available():
+            host = np.zeros(max(b.nbytes, P2P.DESC_BYTES), dtype=np.uint8)
+            src_world = self._peer(source)
+            done = lambda: P2P.complete_receive(w, src_world, host, b.flat)  # noqa: E731
+        elif b.cuda:
             host = np.empty(b.nbytes, dtype=np.uint8)
             done = lambda: _from_host_bytes(b, host)  # noqa: E731
         else:

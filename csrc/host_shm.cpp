@@ -51,9 +51,11 @@ struct alignas(64) CommSlot {
 struct alignas(64) RingCtl {
     std::atomic<uint64_t> head;  // bytes produced
     char pad0[56];
-    std::atomic<uint64_t> tail;  // bytes consumed
-    char pad1[56];
+    std::atomic<uint64_t> tail;   // bytes consumed
+    std::atomic<uint64_t> acked;  // out-of-band messages the consumer has finished with (see ccmpi_host_ack_post)
+    char pad1[48];
 };
+static_assert(sizeof(RingCtl) == 128, "ring control block layout");
 
 struct Header {
     std::atomic<uint64_t> magic;
@@ -647,6 +649,24 @@ extern "C" int ccmpi_host_recv(int64_t h, int src, int comm_id, int tag, void* b
     if (r < 0) return (int)r;
     return ccmpi_host_waitall(h, &r, 1);
 }
+// Out-of-band completion counters, one per ordered pair, next to that pair's ring. The device
+// point-to-point path sends a small descriptor through the ring while the payload stays in the
+// sender's symmetric heap; when the receiver has copied the payload out (over NVLink) it posts an
+// ack here and the sender may reuse the staging block. Counters only grow; messages of one pair
+// are consumed in send order, so a count identifies which blocks are free.
+extern "C" int ccmpi_host_ack_post(int64_t h, int src) {
+    Handle* H = get(h);
+    if (!H || src < 0 || src >= H->nranks || src == H->rank) { set_error("ack_post: bad handle or peer %d", src); return -2; }
+    H->ring(src, H->rank).acked.fetch_add(1, std::memory_order_release);
+    return 0;
+}
+
+extern "C" int64_t ccmpi_host_ack_count(int64_t h, int dst) {
+    Handle* H = get(h);
+    if (!H || dst < 0 || dst >= H->nranks || dst == H->rank) { set_error("ack_count: bad handle or peer %d", dst); return -2; }
+    return (int64_t)H->ring(H->rank, dst).acked.load(std::memory_order_acquire);
+}
+
 extern "C" int64_t ccmpi_host_probe(int64_t h, int src) {
     Handle* H = get(h);
     if (!H) { set_error("bad host transport handle"); return -2; }

@@ -54,6 +54,13 @@ int ccmpi_host_waitall(int64_t h, const int64_t* reqs, int n);
 /* size of the next message queued from `src` (blocks until a header is there) */
 int64_t ccmpi_host_probe(int64_t h, int src);
 
+/* Out-of-band completion counters, one per ordered pair of ranks (device point-to-point path: a
+ * descriptor travels through the ring, the payload stays in the sender's symmetric heap until the
+ * receiver has copied it over NVLink). ack_post: "I am done with one more message from `src`";
+ * ack_count: how many of this rank's messages to `dst` the receiver is done with. */
+int ccmpi_host_ack_post(int64_t h, int src);
+int64_t ccmpi_host_ack_count(int64_t h, int dst);
+
 #ifdef __cplusplus
 }
 #endif

@@ -17,13 +17,14 @@ run() {   # run <label> <timeout> <command...>
     echo "[$label] rc=$rc  $(tail -1 "$log")" | tee -a "$OUT"
 }
 run regular_suite 900 python -m pytest tests -x -q -m gpu --deselect tests/test_gpu_unverified_fp8.py \
-    --deselect tests/test_gpu_unverified_seq.py --deselect tests/test_gpu_unverified_elementwise.py
+    --deselect tests/test_gpu_unverified_seq.py --deselect tests/test_gpu_unverified_elementwise.py --deselect tests/test_gpu_unverified_p2p.py
 run utils        120 python -m pytest tests/test_gpu_utils.py -x -q
 run elementwise  300 python -m pytest tests/test_gpu_unverified_elementwise.py -q
 run fp8          300 python -m pytest tests/test_gpu_unverified_fp8.py -q
 run seq_emulated 600 python -m pytest tests/test_gpu_unverified_seq.py -q -k "not across_processes"
 if [ "$NG" -ge 2 ]; then
     run seq_multiproc 300 python -m pytest tests/test_gpu_unverified_seq.py -q -k across_processes
+    run p2p_device    300 python -m pytest tests/test_gpu_unverified_p2p.py -q
     run put_signal    300 python -m collective_communication_mpi_b200.launch -n "$NG" --transport device python tests/workers/w_collectives.py --cuda
 fi
 # the switch that would become the default once the elementwise kernels are verified
