@@ -158,6 +158,7 @@ def _declare_device(lib):
         "ccmpi_fused_gemm_ag": (i, [P(DevComm), i, PV, PV, sz, i, i, i, i, i, i, i, i, i, i, vp]),
         "ccmpi_fused_ag_gemm_m": (i, [P(DevComm), i, sz, i, sz, PV, PV, i, i, i, i, i, i, i, i, u, i, vp]),
         "ccmpi_fused_gemm_rs_m": (i, [P(DevComm), i, PV, PV, sz, PV, i, i, i, i, i, i, i, i, i, i, u, i, vp]),
+        "ccmpi_fused_ag_gemm_ag": (i, [P(DevComm), i, sz, i, sz, PV, sz, i, i, i, i, i, i, i, u, i, vp]),
     }
     ll = C.c_longlong
     fused.update({

@@ -113,3 +113,49 @@ class GemmReduceScatterM:
         gemm_rs_m_raw(self.ctx.dev.comms, [a], [b], self.slots[self.epoch & 1][0], [out], self.M, self.N, K, a_km=a_km,
                       b_kn=b_kn, flag_base=self.flag_base, epoch=self.epoch, num_sms=num_sms, stream=stream)
         return out
+
+
+# -------------------------------------------------------------------------------------------------
+# gather -> GEMM -> gather (feature axis): the reference's complete forward step in one kernel
+# -------------------------------------------------------------------------------------------------
+def ag_gemm_ag_raw(comms, x_off: int, ldx: int, xfull_off: int, B: List[torch.Tensor], yfull_off: int, M: int, Nn: int,
+                   K: int, *, b_kn: bool, out_dtype=torch.bfloat16, flag_base: int, epoch: int, num_sms: int = 0,
+                   stream=None):
+    a, n = _arr(comms)
+    rc = N.device_lib().ccmpi_fused_ag_gemm_ag(a, n, x_off, ldx, xfull_off, _ptrs(B), yfull_off, M, Nn, K,
+                                               B[0].stride(0), int(b_kn), _OUT[out_dtype], flag_base, epoch, num_sms,
+                                               _sp(stream))
+    N.check(rc, "ccmpi_fused_ag_gemm_ag")
+    N.count_launch()
+
+
+class AllGatherGemmAllGather:
+    """``gather_last_axis(gather_last_axis(x) @ w)``: ``naive_collect_forward_input``, the FC GEMM
+    and ``naive_collect_forward_output`` (func_impl.py:76-109) as ONE kernel. ``x``: ``[M, K/n]``
+    bf16 per rank; ``w``: this rank's ``[K, N]`` (``b_kn``) or ``[N, K]`` shard; result ``[M, N*n]``
+    in symmetric memory (valid until the call after next)."""
+
+    def __init__(self, comm, M: int, K: int, Nlocal: int, *, dtype=torch.bfloat16):
+        self.ctx = _ctx(comm)
+        h, n = self.ctx.heap, self.ctx.n
+        if K % n or (K // n) % 64:
+            raise ValueError(f"K/n = {K}/{n} must be a multiple of 64")
+        self.M, self.K, self.N, self.chunk, self.dtype = M, K, Nlocal, K // n, dtype
+        self.x_off, self.x = h.empty((M, self.chunk), torch.bfloat16)
+        self.xfull = [h.empty((M, K), torch.bfloat16) for _ in range(2)]
+        self.outs = [h.empty((M, Nlocal * n), dtype) for _ in range(2)]
+        self.flag_base = self.ctx.new_slot(n * ((M + 127) // 128))
+        self.epoch = 0
+
+    def gathered_input(self) -> torch.Tensor:
+        return self.xfull[self.epoch & 1][1]
+
+    def __call__(self, x: torch.Tensor, w: torch.Tensor, *, b_kn: bool = True, num_sms: int = 0, stream=None) -> torch.Tensor:
+        if x.data_ptr() != self.x.data_ptr():
+            self.x.copy_(x.reshape(self.M, self.chunk))
+        self.epoch += 1
+        off, out = self.outs[self.epoch & 1]
+        ag_gemm_ag_raw(self.ctx.dev.comms, self.x_off, self.chunk, self.xfull[self.epoch & 1][0], [w], off, self.M,
+                       self.N, self.K, b_kn=b_kn, out_dtype=self.dtype, flag_base=self.flag_base, epoch=self.epoch,
+                       num_sms=num_sms, stream=stream)
+        return out

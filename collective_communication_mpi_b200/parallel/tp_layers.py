@@ -26,6 +26,7 @@ convention).
 from __future__ import annotations
 
 import math
+import os
 from typing import Optional
 
 import torch
@@ -102,7 +103,13 @@ class ColumnParallelLinear(nn.Module):
         # a 1-member group needs no staging buffers or flags: plain GEMMs
         self.ag = F.AllGatherGemm(mp_comm, tokens, in_features, num_comm_ctas=num_comm_ctas) if self.mp > 1 else None
         self.rs = F.GemmReduceScatter(mp_comm, tokens, in_features) if self.mp > 1 else None
-        self.out_ag = F.GemmAllGather(mp_comm, tokens, self.N) if gather_output and self.mp > 1 else None
+        # gather_output: by default the fused all-gather->GEMM is followed by the strided all-gather
+        # kernel on its output; CCMPI_FUSED_GATHER_OUTPUT=1 selects the single gather->GEMM->gather
+        # kernel (ops/fused_seq.py), which has not run on hardware yet
+        self.out_ag = None
+        if gather_output and self.mp > 1 and os.environ.get("CCMPI_FUSED_GATHER_OUTPUT") == "1":
+            from ..ops.fused_seq import AllGatherGemmAllGather
+            self.out_ag = AllGatherGemmAllGather(mp_comm, tokens, in_features, self.N)
         self.num_sms = 0
 
     def input_buffer(self) -> torch.Tensor:
@@ -117,15 +124,18 @@ class ColumnParallelLinear(nn.Module):
         if self.mp == 1:
             y = gemm(x, w, b_kn=True, num_sms=self.num_sms)
             return y, x
+        if self.out_ag is not None:
+            y = self.out_ag(x, w, b_kn=True, num_sms=self.num_sms)
+            return y, self.out_ag.gathered_input()
         y = self.ag(x, w, b_kn=True, num_sms=self.num_sms)
         x_full = self.ag.xfull[self.ag.epoch & 1][1]
-        if self.out_ag is not None:
+        if self.gather_output:
             # reference semantics (func_impl.py:94-109): also gather the output
-            y = self.out_ag(x_full, w, b_kn=True)
+            y = self.comm.gather_last_axis(y)
         return y, x_full
 
     def _bwd(self, dy, x_full, w):
-        if self.out_ag is not None:
+        if self.gather_output and self.mp > 1:
             r = self.comm.Get_rank()
             dy = dy[:, r * self.N:(r + 1) * self.N].contiguous()     # func_impl.py:111-147
         dw = _weight_grad(self, x_full, dy)

@@ -125,3 +125,61 @@ extern "C" int ccmpi_fused_gemm_rs_m(const ccmpi_dev_comm* comms, int nvr, const
     }
     return dispatch2<RsMPolicy>(lp, BN, a_km != 0, b_kn != 0, out_dtype, per_rank * nvr, (cudaStream_t)stream, nvr > 1);
 }
+
+// all-gather -> GEMM -> all-gather: y_full[M][N*n] (symmetric) = [x_0 | ... | x_{n-1}] * B_r in column block r,
+// on every member; x_r = rank r's [M][K/n] shard (K-gather as in ccmpi_fused_ag_gemm).
+extern "C" int ccmpi_fused_ag_gemm_ag(const ccmpi_dev_comm* comms, int nvr, size_t x_off, int ldx, size_t xfull_off,
+                                      const void* const* B, size_t yfull_off, int M, int N, int K, int ldb, int b_kn,
+                                      int out_dtype, int flag_base, unsigned epoch, int num_sms, void* stream) {
+    int rc = check_shapes(M, N, K, ldx, ldb, N, out_dtype);
+    if (rc) return rc;
+    CCMPI_REQUIRE(comms && nvr >= 1 && nvr <= CCMPI_MAX_VRANKS, "nvr=%d out of range", nvr);
+    const int n = comms[0].size;
+    CCMPI_REQUIRE(nvr == 1 || nvr == n, "emulation needs exactly one virtual rank per member (nvr=%d, size=%d)", nvr, n);
+    CCMPI_REQUIRE(use_2cta(), "the gather-GEMM-gather kernel exists for the CTA-pair GEMM only (unset CCMPI_GEMM_1CTA)");
+    const int m_blocks = (M + BM - 1) / BM;
+    CCMPI_REQUIRE(flag_base >= 0 && flag_base + n * m_blocks <= CCMPI_PAD_USER_WORDS,
+                  "fused op needs %d flag words at base %d, the pad has %d", n * m_blocks, flag_base, CCMPI_PAD_USER_WORDS);
+    CCMPI_REQUIRE(K % n == 0 && (K / n) % BK == 0, "K/n = %d must be a multiple of %d", K / n, BK);
+    CCMPI_REQUIRE((x_off | xfull_off | yfull_off) % 16 == 0, "symmetric offsets must be 16-byte aligned");
+    const int chunk = K / n;
+    const int sms = (num_sms > 0 ? num_sms : ccmpi::device_sm_count());
+    const int budget = (sms / nvr) & ~1;
+    CCMPI_REQUIRE(budget >= 2, "not enough SMs for %d emulated ranks", nvr);
+    const int BN = pick_bn(M, N, budget);
+    const int tiles = 2 * (((m_blocks + 1) / 2) * ((N + BN - 1) / BN));
+    const int ctas = budget < tiles ? budget : tiles;
+    CCMPI_REQUIRE(ctas <= CCMPI_MAX_BLOCKS, "grid of %d CTAs exceeds the %d barrier slots", ctas, CCMPI_MAX_BLOCKS);
+    Launch lp;
+    memset(&lp, 0, sizeof(lp));
+    lp.nvr = nvr;
+    for (int v = 0; v < nvr; ++v) {
+        RankParams& rp = lp.r[v];
+        const ccmpi_dev_comm& c = comms[v];
+        rc = fill_tmaps(rp, c.heap[c.rank] + xfull_off, c.heap[c.rank] + x_off, B[v], M, N, K, K, ldx, ldb, false,
+                        b_kn != 0, BN / 2, M, chunk);
+        if (rc) return rc;
+        rp.M = M; rp.N = N; rp.K = K;
+        rp.comm = c;
+        rp.off0 = x_off; rp.off1 = xfull_off; rp.off2 = yfull_off;
+        rp.chunk = chunk;
+        rp.flag_base = flag_base;
+        rp.epoch = epoch;
+        rp.aux0 = ldx;
+        rp.aux1 = 0;         // bulk-copy push: the staging rows exist in this kernel
+        rp.aux2 = ctas;
+    }
+#define CCMPI_AGAG_CASE(bn, bmn)                                                                                  \
+    if (BN == bn && (b_kn != 0) == bmn) {                                                                         \
+        if (out_dtype == CCMPI_BF16)                                                                              \
+            return launch2<bn, false, bmn, __nv_bfloat16, AgKAgOutPolicy>(lp, ctas * nvr, (cudaStream_t)stream, nvr > 1); \
+        return launch2<bn, false, bmn, float, AgKAgOutPolicy>(lp, ctas * nvr, (cudaStream_t)stream, nvr > 1);     \
+    }
+    CCMPI_AGAG_CASE(256, false)
+    CCMPI_AGAG_CASE(256, true)
+    CCMPI_AGAG_CASE(128, false)
+    CCMPI_AGAG_CASE(128, true)
+#undef CCMPI_AGAG_CASE
+    ccmpi::set_error("no CTA-pair GEMM instantiation for BN=%d", BN);
+    return CCMPI_ERR_UNSUPPORTED;
+}

@@ -264,3 +264,44 @@ struct RsMPolicy : PlainPolicy {
 };
 
 }  // namespace gemm
+
+namespace gemm {
+
+// ================================================================================================
+// all-gather -> GEMM -> all-gather of the output: the reference's whole "naive" forward step
+// (func_impl.py:76-109: gather the input, multiply, gather the output) in ONE kernel. The K-gather
+// is AgKPolicy's background push; the epilogue is AgOutPolicy's: every finished tile is stored to
+// column block `rank` of every member's y_full.
+//   off0 / off1 / chunk / aux0 / aux2 : as in AgKPolicy (x_local, x_full, K/n, ldx, CTAs per rank)
+//   off2 : symmetric offset of y_full [M][N * size] (OutT)
+// The staging row of an epilogue lane serves both its pushes and its output rows; each use starts
+// by waiting until the previous bulk copy has finished reading the row.
+// EXPERIMENTAL in round 1 (compiled, not yet run on hardware). CTA-pair kernel only.
+// ================================================================================================
+struct AgKAgOutPolicy : AgKPolicy {
+    static constexpr bool kStagedStore = true;
+
+    template <typename OutT>
+    __device__ static void bulk_row(const RankParams& p, const TileCoord& tc, int row, int col0, uint32_t smem_row, int bytes) {
+        const ccmpi_dev_comm& c = p.comm;
+        const size_t full_ld = (size_t)p.N * c.size;
+        const size_t d = p.off2 + ((size_t)row * full_ld + (size_t)c.rank * p.N + col0) * sizeof(OutT);
+#pragma unroll
+        for (int s = 0; s < CCMPI_MAX_RANKS; ++s)
+            if (s < c.size) ptx::bulk_s2g(c.heap[(c.rank + s) % c.size] + d, smem_row, bytes);
+    }
+
+    // peers store into our y_full: they must not start before we are done with its previous contents
+    __device__ static void prologue(const RankParams& p, int cta, int nctas, int epi_tid) {
+        cta_rank_barrier(p.comm, cta, epi_tid, [] { epi_bar_sync(); });
+    }
+
+    template <typename OutT>
+    __device__ static void tail(const RankParams& p, State& st, int cta, int nctas, int epi_tid, volatile uint32_t* bcast) {
+        AgKPolicy::tail<OutT>(p, st, cta, nctas, epi_tid, bcast);     // whatever has not been pushed yet
+        if (epi_tid == 0) ptx::fence_acq_rel_sys();
+        cta_rank_barrier(p.comm, cta, epi_tid, [] { epi_bar_sync(); });   // every tile has landed everywhere
+    }
+};
+
+}  // namespace gemm

@@ -220,6 +220,14 @@ int ccmpi_fused_gemm_rs_m(const ccmpi_dev_comm* comms, int nvr, const void* cons
                           int a_km, int b_kn, int out_dtype, int flag_base, unsigned epoch, int num_sms,
                           void* stream);
 
+/* EXPERIMENTAL (compiled, not yet run on hardware in round 1): the reference's whole forward step
+ * -- gather the input, multiply, gather the output (func_impl.py:76-109) -- in one kernel:
+ * ccmpi_fused_ag_gemm's K-gather plus ccmpi_fused_gemm_ag's epilogue. yfull_off: symmetric
+ * [M][N*n]; x_off / xfull_off as in ccmpi_fused_ag_gemm. */
+int ccmpi_fused_ag_gemm_ag(const ccmpi_dev_comm* comms, int nvr, size_t x_off, int ldx, size_t xfull_off,
+                           const void* const* B, size_t yfull_off, int M, int N, int K, int ldb, int b_kn,
+                           int out_dtype, int flag_base, unsigned epoch, int num_sms, void* stream);
+
 /* EXPERIMENTAL (compiled, not yet run on hardware in round 1): fused elementwise kernels of the
  * transformer-FC block (csrc/elementwise.cu), bf16 in / bf16 out, fp32 math, one pass over HBM each.
  * The reference has no compute; these sit between the GEMMs of models/fc_stack.py.

@@ -76,6 +76,33 @@ def test_gemm_reduce_scatter_row_scatter(emu, rows, N, K, b_kn, dt):
         assert torch.equal(results[0][r], results[2][r])
 
 
+@pytest.mark.parametrize("M,N,K,b_kn,dt", [(256, 256, 512, True, BF), (640, 384, 1024, False, BF), (200, 128, 512, True, torch.float32)])
+def test_gather_gemm_gather_in_one_kernel(emu, M, N, K, b_kn, dt):
+    from collective_communication_mpi_b200.ops import fused_seq as S
+    nr, heap, comms = emu
+    chunk = K // nr
+    es = 2 if dt == BF else 4
+    x_off = heap.alloc(M * chunk * 2)
+    xf = [heap.alloc(M * K * 2) for _ in range(2)]
+    yf = [heap.alloc(M * N * nr * es) for _ in range(2)]
+    xs = [_rand(M, chunk, seed=50 + r) for r in range(nr)]
+    ws = [_rand(K, N, seed=60 + r) for r in range(nr)]
+    B = [w if b_kn else w.t().contiguous() for w in ws]
+    for epoch in (1, 2, 3):
+        for r in range(nr):
+            heap.view(x_off, (M, chunk), BF, rank=r).copy_(xs[r] * epoch)
+        x_full = torch.cat([heap.view(x_off, (M, chunk), BF, rank=r) for r in range(nr)], dim=1).float()
+        ref = torch.cat([x_full @ w.float() for w in ws], dim=1)
+        S.ag_gemm_ag_raw(comms, x_off, chunk, xf[epoch & 1], B, yf[epoch & 1], M, N, K, b_kn=b_kn, out_dtype=dt,
+                         flag_base=8192, epoch=epoch)
+        torch.cuda.synchronize()
+        for r in range(nr):
+            got = heap.view(yf[epoch & 1], (M, N * nr), dt, rank=r).float()
+            tol = 0.15 if dt == BF else 2e-2
+            assert (got - ref).abs().max().item() < tol * max(1.0, ref.abs().max().item() / 10)
+            assert torch.equal(heap.view(xf[epoch & 1], (M, K), BF, rank=r).float(), x_full)
+
+
 def test_row_constraints_are_reported(emu):
     from collective_communication_mpi_b200 import _native as Nat
     from collective_communication_mpi_b200.ops import fused_seq as S
@@ -95,3 +122,15 @@ def test_sequence_parallel_ops_across_processes():
     proc = run_ranks(n, ["tests/workers/w_seq.py"], transport="device")
     assert proc.returncode == 0, f"rc={proc.returncode}\n{proc.stdout[-3000:]}\n{proc.stderr[-3000:]}"
     assert f"SEQ OK ranks={n}" in proc.stdout
+
+
+@pytest.mark.parametrize("fused", ["0", "1"])
+def test_column_parallel_layer_with_gathered_output(fused):
+    from conftest import gpu_count, run_ranks
+    n = min(gpu_count(), 4)
+    if n < 2:
+        pytest.skip("needs at least 2 GPUs")
+    n = 1 << (n.bit_length() - 1)
+    proc = run_ranks(n, ["tests/workers/w_gather_output.py"], transport="device", env={"CCMPI_FUSED_GATHER_OUTPUT": fused})
+    assert proc.returncode == 0, f"rc={proc.returncode}\n{proc.stdout[-3000:]}\n{proc.stderr[-3000:]}"
+    assert f"GATHER OUTPUT OK ranks={n} fused={fused}" in proc.stdout
