@@ -21,7 +21,6 @@ import atexit
 import ctypes as C
 import os
 import pickle
-import struct
 import time
 import uuid
 from typing import List, Optional

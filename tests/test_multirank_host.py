@@ -3,12 +3,9 @@
 Each test starts N ranks with the launcher (the ``mpirun -n N`` replacement) and lets the worker
 scripts in tests/workers/ assert on every rank; the launcher exits non-zero if any rank fails.
 """
-import os
-import sys
-
 import pytest
 
-from conftest import REPO, run_ranks
+from conftest import run_ranks
 
 
 def _ok(proc, token):
