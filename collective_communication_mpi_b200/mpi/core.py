@@ -595,6 +595,11 @@ class Comm:
         if self._on_device(s, r):
             _dev_allgather_rows(self._dev, s, r, n, rows, pcols * s.itemsize)
             return out
+        if is_t:    # CPU tensor on the shared-memory plane
+            flat = torch.empty((n, rows, pcols), dtype=x.dtype)
+            self.Allgather(src_t, flat)
+            out.view(rows, n, pcols).copy_(flat.permute(1, 0, 2))
+            return out
         flat = np.empty((n, rows, pcols), dtype=src_t.dtype)
         self.Allgather(src_t, flat)
         np.copyto(out.reshape(rows, n, pcols), flat.transpose(1, 0, 2))
@@ -626,7 +631,10 @@ class Comm:
         if self._on_device(s, r):
             _dev_reduce_scatter_rows(self._dev, s, r, n, rows, pcols, op.code)
             return out
-        blocks = np.ascontiguousarray(src_t.reshape(rows, n, pcols).transpose(1, 0, 2))
+        if is_t:    # CPU tensor on the shared-memory plane
+            blocks = src_t.reshape(rows, n, pcols).permute(1, 0, 2).contiguous()
+        else:
+            blocks = np.ascontiguousarray(src_t.reshape(rows, n, pcols).transpose(1, 0, 2))
         self.Reduce_scatter_block(blocks, out, op)
         return out
 

@@ -147,6 +147,11 @@ class AllGatherGemm:
         zero-copy."""
         return self.x
 
+    def gathered(self) -> torch.Tensor:
+        """The ``[M, K]`` activation the last call assembled on this rank (valid until the call
+        after next: the staging is double-buffered)."""
+        return self.xfull[self.epoch & 1][1]
+
     def __call__(self, x: torch.Tensor, w: torch.Tensor, *, b_kn: bool = True, out: Optional[torch.Tensor] = None,
                  out_dtype=torch.bfloat16, num_sms: int = 0, stream=None) -> torch.Tensor:
         if x.data_ptr() != self.x.data_ptr():

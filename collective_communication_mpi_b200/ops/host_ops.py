@@ -1,0 +1,90 @@
+"""CPU statement of the GEMM and fused GEMM+collective ops: the same classes and call signatures as
+``ops/gemm.py`` and ``ops/fused.py``, written as the unfused math -- library collective, then a
+matmul in fp32 -- on CPU tensors over the shared-memory transport.
+
+Two uses. (1) It is the reference's own dataflow (func_impl.py:76-187: gather, multiply, gather /
+slice, multiply, reduce-scatter) in executable form, i.e. the oracle the CUDA kernels are compared
+with. (2) The tensor-parallel layers, the models and the data-parallel gradient path pick these
+implementations when the process has no GPU, so their Python logic -- autograd wiring, shard
+bookkeeping, bucket scheduling -- is exercised by the CPU test-suite on real multi-process groups.
+
+This is not a fallback for GPU boxes: with CUDA available the layers always use the kernels.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, *, a_km: bool = False, b_kn: bool = False, out: Optional[torch.Tensor] = None,
+         out_dtype: torch.dtype = torch.bfloat16, accumulate: bool = False, num_sms: int = 0, stream=None) -> torch.Tensor:
+    """Same contract as ``ops.gemm.gemm``: ``a`` is ``[M,K]`` (``[K,M]`` with ``a_km``), ``b`` is
+    ``[N,K]`` (``[K,N]`` with ``b_kn``); fp32 accumulation, result cast to ``out_dtype``."""
+    A = a.float().t() if a_km else a.float()
+    B = b.float() if b_kn else b.float().t()
+    c = A @ B
+    if out is None:
+        return c.to(out_dtype)
+    if accumulate:
+        out.add_(c.to(out.dtype))
+    else:
+        out.copy_(c.to(out.dtype))
+    return out
+
+
+def matmul_tn(x: torch.Tensor, dy: torch.Tensor, **kw) -> torch.Tensor:
+    return gemm(x, dy, a_km=True, b_kn=True, **kw)
+
+
+class AllGatherGemm:
+    """``gather_last_axis(x) @ w`` (func_impl.py:76-91 + the FC GEMM)."""
+
+    def __init__(self, comm, M: int, K: int, *, num_comm_ctas: int = 0, use_mc: bool = True):
+        self.comm, self.M, self.K = comm, M, K
+        self._gathered = None
+
+    def gathered(self) -> torch.Tensor:
+        return self._gathered
+
+    def __call__(self, x, w, *, b_kn: bool = True, out=None, out_dtype=torch.bfloat16, num_sms: int = 0, stream=None):
+        self._gathered = self.comm.gather_last_axis(x.reshape(self.M, -1).contiguous())
+        return gemm(self._gathered, w, b_kn=b_kn, out=out, out_dtype=out_dtype)
+
+
+class GemmReduceScatter:
+    """``reduce_scatter_last_axis(a @ b)`` (the dx GEMM + func_impl.py:150-187)."""
+
+    def __init__(self, comm, M: int, Nfull: int, *, dtype=torch.bfloat16):
+        self.comm, self.M, self.N, self.dtype = comm, M, Nfull, dtype
+
+    def __call__(self, a, b, *, a_km: bool = False, b_kn: bool = False, out=None, num_sms: int = 0, stream=None):
+        part = gemm(a, b, a_km=a_km, b_kn=b_kn, out_dtype=torch.float32)
+        red = self.comm.reduce_scatter_last_axis(part).to(self.dtype)
+        if out is not None:
+            out.copy_(red)
+            return out
+        return red
+
+
+class GemmAllReduce:
+    """``all_reduce(a @ b)``."""
+
+    def __init__(self, comm, M: int, Nfull: int, *, dtype=torch.bfloat16, use_mc: bool = True):
+        self.comm, self.dtype = comm, dtype
+
+    def __call__(self, a, b, *, a_km: bool = False, b_kn: bool = False, num_sms: int = 0, stream=None):
+        part = gemm(a, b, a_km=a_km, b_kn=b_kn, out_dtype=torch.float32).contiguous()
+        out = torch.empty_like(part)
+        self.comm.Allreduce(part, out)
+        return out.to(self.dtype)
+
+
+class GemmAllGather:
+    """``gather_last_axis(a @ b)`` (the FC GEMM + func_impl.py:94-109)."""
+
+    def __init__(self, comm, M: int, Nlocal: int, *, dtype=torch.bfloat16, use_mc: bool = True):
+        self.comm, self.dtype = comm, dtype
+
+    def __call__(self, a, b, *, a_km: bool = False, b_kn: bool = True, num_sms: int = 0, stream=None):
+        return self.comm.gather_last_axis(gemm(a, b, a_km=a_km, b_kn=b_kn, out_dtype=self.dtype))

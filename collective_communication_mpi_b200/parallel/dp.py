@@ -32,11 +32,18 @@ class GradSink:
         params = [l.weight for l in self.layers]
         self.total = sum(p.numel() for p in params)
         pad = lambda n: (n + 127) // 128 * 128  # noqa: E731  keep every view 256-byte aligned
-        self.flat = dp_comm.symm_empty(sum(pad(p.numel()) for p in params), torch.bfloat16)
-        self.dev = dp_comm.device_comm()
-        self.flat_off = self.dev.heap.offset_of(self.flat)
-        self.use_nvls = self.dev.has_mc and self.dp > 2      # measured: the P2P two-shot wins between two GPUs
-        self.tmp = dp_comm.symm_empty(self.flat.numel(), torch.bfloat16) if self.dp > 1 and not self.use_nvls else None
+        self.on_gpu = params[0].is_cuda
+        if self.on_gpu:
+            self.flat = dp_comm.symm_empty(sum(pad(p.numel()) for p in params), torch.bfloat16)
+            self.dev = dp_comm.device_comm()
+            self.flat_off = self.dev.heap.offset_of(self.flat)
+            self.use_nvls = self.dev.has_mc and self.dp > 2      # measured: the P2P two-shot wins between two GPUs
+            self.tmp = dp_comm.symm_empty(self.flat.numel(), torch.bfloat16) if self.dp > 1 and not self.use_nvls else None
+        else:
+            # no GPU in this process (CPU test-suite): same buckets, reduced by the library
+            # all-reduce of the shared-memory transport when they complete
+            self.flat = torch.zeros(sum(pad(p.numel()) for p in params), dtype=torch.bfloat16)
+            self.dev, self.flat_off, self.use_nvls, self.tmp = None, 0, False, None
         self._views: Dict[int, torch.Tensor] = {}
         self._bucket_of: Dict[int, int] = {}
         self.buckets: List[dict] = []
@@ -55,7 +62,7 @@ class GradSink:
             cur["want"] += 1
             off += n
             layer.grad_sink = self
-        self.overlap = overlap and self.dp > 1
+        self.overlap = overlap and self.dp > 1 and self.on_gpu
         self.stream = torch.cuda.Stream() if self.overlap else None
         self.max_blocks = max_blocks
         self.algo = N.AR_NVLS if self.use_nvls else N.AR_TWOSHOT
@@ -81,6 +88,13 @@ class GradSink:
         # it every SM; earlier buckets share the GPU with the remaining backward GEMMs
         last = b is self.buckets[-1]
         count = b["hi"] - b["lo"]
+        if not self.on_gpu:
+            view = self.flat[b["lo"]:b["hi"]]
+            total = torch.empty_like(view)
+            self.comm.Allreduce(view, total)
+            view.copy_(total.float() * (1.0 / self.dp))
+            self.launches += 1
+            return
         off = self.flat_off + b["lo"] * 2
         tmp_off = self.dev.heap.offset_of(self.tmp) + b["lo"] * 2 if self.tmp is not None else 0
         cur = torch.cuda.current_stream()

@@ -32,7 +32,17 @@ import torch
 from torch import nn
 
 from ..ops import fused as F
-from ..ops.gemm import gemm, matmul_tn
+from ..ops import host_ops as H
+from ..ops.gemm import gemm as _cuda_gemm, matmul_tn as _cuda_matmul_tn
+
+
+def _backend():
+    """``(device, op classes, gemm, matmul_tn)``: the kernels whenever the process has a GPU, the
+    CPU statement of the same ops (ops/host_ops.py) otherwise -- which is how the CPU test-suite
+    runs these layers on real multi-process groups."""
+    if torch.cuda.is_available():
+        return torch.device("cuda", torch.cuda.current_device()), F, _cuda_gemm, _cuda_matmul_tn
+    return torch.device("cpu"), H, H.gemm, H.matmul_tn
 
 
 class _ColumnFn(torch.autograd.Function):
@@ -75,8 +85,8 @@ def _weight_grad(layer, x, dy):
     ready; autograd then gets ``None`` for the weight."""
     sink = getattr(layer, "grad_sink", None)
     if sink is None:
-        return matmul_tn(x, dy, out_dtype=layer.grad_dtype, num_sms=layer.num_sms)
-    matmul_tn(x, dy, out=sink.view_for(layer.weight), num_sms=layer.num_sms)
+        return layer._matmul_tn(x, dy, out_dtype=layer.grad_dtype, num_sms=layer.num_sms)
+    layer._matmul_tn(x, dy, out=sink.view_for(layer.weight), num_sms=layer.num_sms)
     sink.ready(layer.weight)
     return None
 
@@ -97,16 +107,16 @@ class ColumnParallelLinear(nn.Module):
         self.M, self.K, self.N = tokens, in_features, out_features // self.mp
         self.gather_output = gather_output
         self.grad_dtype = grad_dtype
-        dev = torch.device("cuda", torch.cuda.current_device())
+        dev, ops, self._gemm, self._matmul_tn = _backend()
         self.weight = _init_weight(in_features, self.N, in_features, dev, seed * 1000 + mp_comm.Get_rank())
         # a 1-member group needs no staging buffers or flags: plain GEMMs
-        self.ag = F.AllGatherGemm(mp_comm, tokens, in_features, num_comm_ctas=num_comm_ctas) if self.mp > 1 else None
-        self.rs = F.GemmReduceScatter(mp_comm, tokens, in_features) if self.mp > 1 else None
+        self.ag = ops.AllGatherGemm(mp_comm, tokens, in_features, num_comm_ctas=num_comm_ctas) if self.mp > 1 else None
+        self.rs = ops.GemmReduceScatter(mp_comm, tokens, in_features) if self.mp > 1 else None
         # gather_output: by default the fused all-gather->GEMM is followed by the strided all-gather
         # kernel on its output; CCMPI_FUSED_GATHER_OUTPUT=1 selects the single gather->GEMM->gather
         # kernel (ops/fused_seq.py), which has not run on hardware yet
         self.out_ag = None
-        if gather_output and self.mp > 1 and os.environ.get("CCMPI_FUSED_GATHER_OUTPUT") == "1":
+        if gather_output and self.mp > 1 and dev.type == "cuda" and os.environ.get("CCMPI_FUSED_GATHER_OUTPUT") == "1":
             from ..ops.fused_seq import AllGatherGemmAllGather
             self.out_ag = AllGatherGemmAllGather(mp_comm, tokens, in_features, self.N)
         self.num_sms = 0
@@ -121,13 +131,13 @@ class ColumnParallelLinear(nn.Module):
     # -- kernels ---------------------------------------------------------------------------
     def _fwd(self, x, w):
         if self.mp == 1:
-            y = gemm(x, w, b_kn=True, num_sms=self.num_sms)
+            y = self._gemm(x, w, b_kn=True, num_sms=self.num_sms)
             return y, x
         if self.out_ag is not None:
             y = self.out_ag(x, w, b_kn=True, num_sms=self.num_sms)
             return y, self.out_ag.gathered_input()
         y = self.ag(x, w, b_kn=True, num_sms=self.num_sms)
-        x_full = self.ag.xfull[self.ag.epoch & 1][1]
+        x_full = self.ag.gathered()
         if self.gather_output:
             # reference semantics (func_impl.py:94-109): also gather the output
             y = self.comm.gather_last_axis(y)
@@ -139,7 +149,7 @@ class ColumnParallelLinear(nn.Module):
             dy = dy[:, r * self.N:(r + 1) * self.N].contiguous()     # func_impl.py:111-147
         dw = _weight_grad(self, x_full, dy)
         if self.mp == 1:
-            dx = gemm(dy, w, num_sms=self.num_sms)
+            dx = self._gemm(dy, w, num_sms=self.num_sms)
         else:
             dx = self.rs(dy, w, b_kn=False, num_sms=self.num_sms)
         return dx, dw
@@ -154,10 +164,10 @@ class RowParallelLinear(nn.Module):
         self.comm, self.mp = mp_comm, mp_comm.Get_size()
         self.M, self.K, self.N = tokens, in_features // self.mp, out_features
         self.grad_dtype = grad_dtype
-        dev = torch.device("cuda", torch.cuda.current_device())
+        dev, ops, self._gemm, self._matmul_tn = _backend()
         self.weight = _init_weight(self.K, out_features, in_features, dev, seed * 1000 + mp_comm.Get_rank())
-        self.rs = F.GemmReduceScatter(mp_comm, tokens, out_features) if self.mp > 1 else None
-        self.ag = F.AllGatherGemm(mp_comm, tokens, out_features, num_comm_ctas=num_comm_ctas) if self.mp > 1 else None
+        self.rs = ops.GemmReduceScatter(mp_comm, tokens, out_features) if self.mp > 1 else None
+        self.ag = ops.AllGatherGemm(mp_comm, tokens, out_features, num_comm_ctas=num_comm_ctas) if self.mp > 1 else None
         self.num_sms = 0
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
@@ -165,15 +175,15 @@ class RowParallelLinear(nn.Module):
 
     def _fwd(self, x, w):
         if self.mp == 1:
-            return gemm(x, w, b_kn=True, num_sms=self.num_sms)
+            return self._gemm(x, w, b_kn=True, num_sms=self.num_sms)
         return self.rs(x, w, b_kn=True, num_sms=self.num_sms)
 
     def _bwd(self, dy, x, w):
         if self.mp == 1:
-            dx = gemm(dy, w, num_sms=self.num_sms)
+            dx = self._gemm(dy, w, num_sms=self.num_sms)
             dy_full = dy
         else:
             dx = self.ag(dy, w, b_kn=False, num_sms=self.num_sms)
-            dy_full = self.ag.xfull[self.ag.epoch & 1][1]
+            dy_full = self.ag.gathered()
         dw = _weight_grad(self, x, dy_full)
         return dx, dw

@@ -56,3 +56,46 @@ def test_pytest_itself_runs_under_the_launcher_with_the_mpi_flag(tmp_path):
     p = run_ranks(1, ["-m", "pytest", "-q", "-rs", "-p", "collective_communication_mpi_b200.pytest_plugin",
                       "--rootdir", str(tmp_path), str(t)])
     assert "1 skipped" in p.stdout, p.stdout
+
+
+# ---- tensor-parallel layers, model and training step on CPU tensors ----------------------------
+# Without a GPU the layers use the CPU statement of the fused ops (ops/host_ops.py) over the
+# shared-memory transport, so the same worker that checks them on B200s checks their Python logic
+# -- autograd wiring, shard bookkeeping, gradient buckets, SGD -- here, against a dense model.
+@pytest.mark.parametrize("mp,dp", [(1, 1), (2, 1), (1, 2), (2, 2), (4, 2)])
+def test_tp_layers_and_train_step_match_dense_model_on_cpu(mp, dp):
+    _ok(run_ranks(mp * dp, ["tests/workers/w_layers.py", str(mp), str(dp)], timeout=240), f"LAYERS OK mp={mp} dp={dp}")
+
+
+def test_train_step_with_the_fused_elementwise_ops_on_cpu():
+    _ok(run_ranks(4, ["tests/workers/w_layers.py", "2", "2"], timeout=240, env={"CCMPI_FUSED_ELEMENTWISE": "1"}),
+        "LAYERS OK mp=2 dp=2")
+
+
+@pytest.mark.parametrize("nranks", [2, 4])
+def test_column_parallel_layer_with_gathered_output_on_cpu(nranks):
+    _ok(run_ranks(nranks, ["tests/workers/w_gather_output.py"], timeout=240), f"GATHER OUTPUT OK ranks={nranks}")
+
+
+TORCH_CPU_CODE = r'''
+import torch
+from mpi4py import MPI
+w = MPI.COMM_WORLD
+r, n = w.Get_rank(), w.Get_size()
+for dt in (torch.float32, torch.bfloat16, torch.int64):
+    x = (torch.arange(2 * 3 * 4).reshape(2, 3, 4) + 100 * r).to(dt)
+    g = w.gather_last_axis(x)                                        # func_impl.py:76-91 on CPU tensors
+    assert g.dtype == dt and g.shape == (2, 3, 4 * n)
+    want = torch.cat([(torch.arange(24).reshape(2, 3, 4) + 100 * q).to(dt) for q in range(n)], dim=-1)
+    assert torch.equal(g, want)
+    p = (torch.arange(2 * 3 * 2 * n).reshape(2, 3, 2 * n) + r).to(dt)
+    s = w.reduce_scatter_last_axis(p)                                # func_impl.py:150-187
+    total = sum((torch.arange(2 * 3 * 2 * n).reshape(2, 3, 2 * n) + q).float() for q in range(n))
+    assert s.dtype == dt and torch.equal(s.float(), total[..., 2 * r:2 * r + 2].to(dt).float())
+w.Barrier()
+if r == 0: print("TORCH CPU OK", n)
+'''
+
+
+def test_last_axis_collectives_accept_cpu_torch_tensors():
+    _ok(run_ranks(4, ["-c", TORCH_CPU_CODE], timeout=120), "TORCH CPU OK 4")

@@ -13,7 +13,17 @@ mp, dp = int(sys.argv[1]), int(sys.argv[2])
 world = MPI.COMM_WORLD
 rank, n = world.Get_rank(), world.Get_size()
 assert n == mp * dp
-torch.cuda.set_device(rank)
+CUDA = torch.cuda.is_available()
+DEV = torch.device("cuda", rank) if CUDA else torch.device("cpu")
+if CUDA:
+    torch.cuda.set_device(rank)
+
+
+def sync():
+    if CUDA:
+        torch.cuda.synchronize()
+
+
 mp_idx, dp_idx, mp_comm, dp_comm, _, _ = get_info(comm=world, rank=rank, mp_size=mp, dp_size=dp, fc_layer="fc_q",
                                                   in_dim=1024, out_dim=1024)
 H, TOK = (512 if mp <= 4 else 1024), 256     # every scattered chunk must be >= 128 wide
@@ -25,13 +35,13 @@ X = torch.randn(dp * TOK, H, generator=g) * 0.5
 T = torch.randn(dp * TOK, H, generator=g) * 0.5
 xs, ts = split_data(X, T, mp_size=mp, dp_size=dp, rank=rank)
 sh = H // mp
-x_loc = xs[:, mp_idx * sh:(mp_idx + 1) * sh].contiguous().cuda().bfloat16()
-t_loc = ts[:, mp_idx * sh:(mp_idx + 1) * sh].contiguous().cuda().bfloat16()
+x_loc = xs[:, mp_idx * sh:(mp_idx + 1) * sh].contiguous().to(DEV).bfloat16()
+t_loc = ts[:, mp_idx * sh:(mp_idx + 1) * sh].contiguous().to(DEV).bfloat16()
 
 
 def full_weight(layer, axis):
     parts = mp_comm.allgather(layer.weight.detach().float().cpu())
-    return torch.cat(list(parts), dim=axis).cuda()
+    return torch.cat(list(parts), dim=axis).to(DEV)
 
 
 Wqkv_parts = mp_comm.allgather(model.fc_qkv.weight.detach().float().cpu())   # each [H, 3H/mp] = q|k|v shards
@@ -42,7 +52,7 @@ def dense_forward(x_full):
     """Same math on unsharded fp32 tensors; q/k/v columns are interleaved per rank like the shards."""
     outs = []
     for r in range(mp):
-        q, k, v = (x_full @ Wqkv_parts[r].cuda()).chunk(3, dim=-1)
+        q, k, v = (x_full @ Wqkv_parts[r].to(DEV)).chunk(3, dim=-1)
         outs.append(v * torch.sigmoid(q * k))
     a = torch.cat(outs, dim=-1)
     h = x_full + a @ Wo
@@ -50,10 +60,10 @@ def dense_forward(x_full):
     return h + u @ W2
 
 
-x_full = xs.cuda().float().bfloat16().float()
+x_full = xs.to(DEV).float().bfloat16().float()
 ref = dense_forward(x_full)
 y = model(x_loc)
-torch.cuda.synchronize()
+sync()
 got = y.float()
 want = ref[:, mp_idx * sh:(mp_idx + 1) * sh]
 err = (got - want).abs().max().item()
@@ -63,9 +73,9 @@ assert err < 0.06 * max(1.0, want.abs().max().item()), f"forward mismatch {err}"
 before = [l.weight.detach().clone() for l in model.tp_layers()]
 step = TrainStep(model, dp_comm, lr=0.5, bucket_mb=1)
 loss = step(x_loc, t_loc)
-torch.cuda.synchronize()
+sync()
 
-params = [p.clone().requires_grad_(True) for p in [*[w.cuda() for w in Wqkv_parts], Wo, W1, W2]]
+params = [p.clone().requires_grad_(True) for p in [*[w.to(DEV) for w in Wqkv_parts], Wo, W1, W2]]
 
 
 def dense_loss(x_full, t_full):
@@ -84,8 +94,8 @@ def dense_loss(x_full, t_full):
 
 total = 0.0
 for d in range(dp):
-    xd = X[d * TOK:(d + 1) * TOK].cuda().bfloat16().float()
-    td = T[d * TOK:(d + 1) * TOK].cuda().bfloat16().float()
+    xd = X[d * TOK:(d + 1) * TOK].to(DEV).bfloat16().float()
+    td = T[d * TOK:(d + 1) * TOK].to(DEV).bfloat16().float()
     total = total + dense_loss(xd, td) / dp
 total.backward()
 g_qkv = params[mp_idx].grad
