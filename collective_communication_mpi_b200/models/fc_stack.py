@@ -13,6 +13,7 @@ parameters at 16 x 8192^2).
 """
 from __future__ import annotations
 
+import os
 from typing import List
 
 import torch
@@ -72,7 +73,15 @@ class TrainStep:
 
     def __init__(self, model, dp_comm, *, lr: float = 1e-3, bucket_mb: int = 64, overlap: bool = True):
         self.model, self.lr = model, lr
-        self.sink = GradSink(dp_comm, model.tp_layers(), bucket_mb=bucket_mb, overlap=overlap)
+        # opt-in (CCMPI_FUSED_SGD=1), only without data parallelism: every dW GEMM applies its own
+        # SGD step in the epilogue, so there is no gradient buffer, no reduction and no optimizer pass
+        self.fused_sgd = dp_comm.Get_size() == 1 and os.environ.get("CCMPI_FUSED_SGD") == "1"
+        if self.fused_sgd:
+            for layer in model.tp_layers():
+                layer.sgd_lr = lr
+            self.sink = None
+        else:
+            self.sink = GradSink(dp_comm, model.tp_layers(), bucket_mb=bucket_mb, overlap=overlap)
         self.weights = [l.weight.data for l in model.tp_layers()]
         self.fused_loss = EW.enabled()
 
@@ -84,6 +93,7 @@ class TrainStep:
         else:
             loss = torch.nn.functional.mse_loss(y.float(), target.float())
             loss.backward()
-        self.sink.finish()
-        sgd_step(self.weights, self.sink.grads(), self.lr)
+        if not self.fused_sgd:
+            self.sink.finish()
+            sgd_step(self.weights, self.sink.grads(), self.lr)
         return loss.detach()

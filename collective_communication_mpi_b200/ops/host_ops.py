@@ -37,6 +37,13 @@ def matmul_tn(x: torch.Tensor, dy: torch.Tensor, **kw) -> torch.Tensor:
     return gemm(x, dy, a_km=True, b_kn=True, **kw)
 
 
+def gemm_sgd_(w: torch.Tensor, a: torch.Tensor, b: torch.Tensor, lr: float, *, a_km: bool = False, b_kn: bool = False,
+              num_sms: int = 0, stream=None) -> torch.Tensor:
+    """``w -= lr * (a @ b)`` with the product kept in fp32 (what csrc/gemm_sgd.cu does in its epilogue)."""
+    w.copy_((w.float() - lr * gemm(a, b, a_km=a_km, b_kn=b_kn, out_dtype=torch.float32)).to(w.dtype))
+    return w
+
+
 class AllGatherGemm:
     """``gather_last_axis(x) @ w`` (func_impl.py:76-91 + the FC GEMM)."""
 

@@ -33,7 +33,7 @@ from torch import nn
 
 from ..ops import fused as F
 from ..ops import host_ops as H
-from ..ops.gemm import gemm as _cuda_gemm, matmul_tn as _cuda_matmul_tn
+from ..ops.gemm import gemm as _cuda_gemm, gemm_sgd_ as _cuda_gemm_sgd, matmul_tn as _cuda_matmul_tn
 
 
 def _backend():
@@ -41,8 +41,8 @@ def _backend():
     CPU statement of the same ops (ops/host_ops.py) otherwise -- which is how the CPU test-suite
     runs these layers on real multi-process groups."""
     if torch.cuda.is_available():
-        return torch.device("cuda", torch.cuda.current_device()), F, _cuda_gemm, _cuda_matmul_tn
-    return torch.device("cpu"), H, H.gemm, H.matmul_tn
+        return torch.device("cuda", torch.cuda.current_device()), F, _cuda_gemm, _cuda_matmul_tn, _cuda_gemm_sgd
+    return torch.device("cpu"), H, H.gemm, H.matmul_tn, H.gemm_sgd_
 
 
 class _ColumnFn(torch.autograd.Function):
@@ -83,6 +83,11 @@ def _weight_grad(layer, x, dy):
     """dW = x^T dy. With a gradient sink attached (``parallel/dp.py``) the GEMM writes straight
     into the data-parallel bucket in symmetric memory and the reducer is told the bucket entry is
     ready; autograd then gets ``None`` for the weight."""
+    if layer.sgd_lr is not None:
+        # no data-parallel reduction needed: the dW kernel applies the step itself (W -= lr * x^T dy)
+        with torch.no_grad():
+            layer._gemm_sgd(layer.weight.data, x, dy, layer.sgd_lr, a_km=True, b_kn=True, num_sms=layer.num_sms)
+        return None
     sink = getattr(layer, "grad_sink", None)
     if sink is None:
         return layer._matmul_tn(x, dy, out_dtype=layer.grad_dtype, num_sms=layer.num_sms)
@@ -107,7 +112,8 @@ class ColumnParallelLinear(nn.Module):
         self.M, self.K, self.N = tokens, in_features, out_features // self.mp
         self.gather_output = gather_output
         self.grad_dtype = grad_dtype
-        dev, ops, self._gemm, self._matmul_tn = _backend()
+        dev, ops, self._gemm, self._matmul_tn, self._gemm_sgd = _backend()
+        self.sgd_lr = None      # set by TrainStep when the optimizer step is fused into the dW GEMM
         self.weight = _init_weight(in_features, self.N, in_features, dev, seed * 1000 + mp_comm.Get_rank())
         # a 1-member group needs no staging buffers or flags: plain GEMMs
         self.ag = ops.AllGatherGemm(mp_comm, tokens, in_features, num_comm_ctas=num_comm_ctas) if self.mp > 1 else None
@@ -147,11 +153,15 @@ class ColumnParallelLinear(nn.Module):
         if self.gather_output and self.mp > 1:
             r = self.comm.Get_rank()
             dy = dy[:, r * self.N:(r + 1) * self.N].contiguous()     # func_impl.py:111-147
-        dw = _weight_grad(self, x_full, dy)
+        # dW first: its data-parallel bucket can start reducing while dx is computed -- unless the
+        # dW kernel itself rewrites W (fused SGD), in which case dx must read W before that
+        dw = _weight_grad(self, x_full, dy) if self.sgd_lr is None else None
         if self.mp == 1:
             dx = self._gemm(dy, w, num_sms=self.num_sms)
         else:
             dx = self.rs(dy, w, b_kn=False, num_sms=self.num_sms)
+        if self.sgd_lr is not None:
+            dw = _weight_grad(self, x_full, dy)
         return dx, dw
 
 
@@ -164,7 +174,8 @@ class RowParallelLinear(nn.Module):
         self.comm, self.mp = mp_comm, mp_comm.Get_size()
         self.M, self.K, self.N = tokens, in_features // self.mp, out_features
         self.grad_dtype = grad_dtype
-        dev, ops, self._gemm, self._matmul_tn = _backend()
+        dev, ops, self._gemm, self._matmul_tn, self._gemm_sgd = _backend()
+        self.sgd_lr = None
         self.weight = _init_weight(self.K, out_features, in_features, dev, seed * 1000 + mp_comm.Get_rank())
         self.rs = ops.GemmReduceScatter(mp_comm, tokens, out_features) if self.mp > 1 else None
         self.ag = ops.AllGatherGemm(mp_comm, tokens, out_features, num_comm_ctas=num_comm_ctas) if self.mp > 1 else None
@@ -185,5 +196,5 @@ class RowParallelLinear(nn.Module):
         else:
             dx = self.ag(dy, w, b_kn=False, num_sms=self.num_sms)
             dy_full = self.ag.gathered()
-        dw = _weight_grad(self, x, dy_full)
+        dw = _weight_grad(self, x, dy_full)     # after dx: with fused SGD this kernel rewrites W
         return dx, dw

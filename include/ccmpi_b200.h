@@ -244,6 +244,13 @@ size_t ccmpi_mse_workspace_bytes(void);
 int ccmpi_mse_fwd_bwd(const void* y, const void* t, void* dy, long long n, void* workspace, void* loss,
                       void* stream);
 
+/* EXPERIMENTAL (compiled, not yet run on hardware in round 1): weight-gradient GEMM with the SGD
+ * update in its epilogue, W[M][N] -= lr * (A * B), bf16 W updated in place from the fp32
+ * accumulator (csrc/gemm_sgd.cu). For layers whose gradient needs no data-parallel reduction.
+ * Operand layout flags as in ccmpi_gemm_bf16. */
+int ccmpi_gemm_sgd_bf16(const void* A, const void* B, void* W, int M, int N, int K, int lda, int ldb, int ldw,
+                        int a_mn_major, int b_mn_major, float lr, int num_sms, void* stream);
+
 /* EXPERIMENTAL (compiled, not yet run on hardware in round 1): fp8 e4m3 GEMM on the CTA-pair
  * kernel, C[M][N] = scale * A[M][K] * B[N][K]^T, both operands K-major (tcgen05.mma.kind::f8f6f4).
  * First step towards the block-scaled fp8 FC layers of BASELINE.md config 3; the reference has no

@@ -17,9 +17,10 @@ run() {   # run <label> <timeout> <command...>
     echo "[$label] rc=$rc  $(tail -1 "$log")" | tee -a "$OUT"
 }
 run regular_suite 900 python -m pytest tests -x -q -m gpu --deselect tests/test_gpu_unverified_fp8.py \
-    --deselect tests/test_gpu_unverified_seq.py --deselect tests/test_gpu_unverified_elementwise.py --deselect tests/test_gpu_unverified_p2p.py
+    --deselect tests/test_gpu_unverified_seq.py --deselect tests/test_gpu_unverified_elementwise.py --deselect tests/test_gpu_unverified_p2p.py --deselect tests/test_gpu_unverified_sgd.py
 run utils        120 python -m pytest tests/test_gpu_utils.py -x -q
 run elementwise  300 python -m pytest tests/test_gpu_unverified_elementwise.py -q
+run sgd          300 python -m pytest tests/test_gpu_unverified_sgd.py -q
 run fp8          300 python -m pytest tests/test_gpu_unverified_fp8.py -q
 run seq_emulated 600 python -m pytest tests/test_gpu_unverified_seq.py -q -k "not across_processes"
 if [ "$NG" -ge 2 ]; then
@@ -30,4 +31,5 @@ fi
 # the switch that would become the default once the elementwise kernels are verified
 CCMPI_FUSED_ELEMENTWISE=0 run bench_eager 300 python bench.py --steps 10 --warmup 3
 CCMPI_FUSED_ELEMENTWISE=1 run bench_fused 300 python bench.py --steps 10 --warmup 3
+CCMPI_FUSED_ELEMENTWISE=1 CCMPI_FUSED_SGD=1 run bench_fused_sgd 300 python bench.py --steps 10 --warmup 3
 cat "$OUT"

@@ -67,6 +67,18 @@ def test_tp_layers_and_train_step_match_dense_model_on_cpu(mp, dp):
     _ok(run_ranks(mp * dp, ["tests/workers/w_layers.py", str(mp), str(dp)], timeout=240), f"LAYERS OK mp={mp} dp={dp}")
 
 
+@pytest.mark.parametrize("mp", [1, 2])
+def test_train_step_with_sgd_fused_into_the_weight_gradient_on_cpu(mp):
+    """dp = 1: every dW GEMM applies its own SGD step; dx must have read W before that."""
+    _ok(run_ranks(mp, ["tests/workers/w_layers.py", str(mp), "1"], timeout=240, env={"CCMPI_FUSED_SGD": "1"}),
+        f"LAYERS OK mp={mp} dp=1")
+    # with data parallelism the switch is ignored (the gradient has to be reduced first)
+    if mp == 1:
+        p = run_ranks(2, ["tests/workers/w_layers.py", "1", "2"], timeout=240, env={"CCMPI_FUSED_SGD": "1"})
+        _ok(p, "LAYERS OK mp=1 dp=2")
+        assert "fused_sgd=0" in p.stdout
+
+
 def test_train_step_with_the_fused_elementwise_ops_on_cpu():
     _ok(run_ranks(4, ["tests/workers/w_layers.py", "2", "2"], timeout=240, env={"CCMPI_FUSED_ELEMENTWISE": "1"}),
         "LAYERS OK mp=2 dp=2")

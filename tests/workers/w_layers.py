@@ -109,4 +109,4 @@ for name, layer, w0, gref in zip(("qkv", "o", "fc1", "fc2"), model.tp_layers(), 
     assert e < 0.08 * scale + 2e-3, f"{name}: grad mismatch {e} (scale {scale})"
 world.Barrier()
 if rank == 0:
-    print(f"LAYERS OK mp={mp} dp={dp} loss={loss.item():.4f} ar_launches={step.sink.launches}")
+    print(f"LAYERS OK mp={mp} dp={dp} loss={loss.item():.4f} ar_launches={step.sink.launches if step.sink else 0} fused_sgd={int(step.fused_sgd)}")
