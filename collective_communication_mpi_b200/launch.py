@@ -49,6 +49,10 @@ def launch(nprocs: int, cmd, *, tag_output: bool = False, env_extra=None, timeou
             "PYTHONUNBUFFERED": "1",
         })
         env["PYTHONPATH"] = repo_root + (os.pathsep + env["PYTHONPATH"] if env.get("PYTHONPATH") else "")
+        if nprocs > 1:
+            # like torchrun: N ranks that each start one compute thread per core thrash the node;
+            # give every rank its share unless the user has said otherwise
+            env.setdefault("OMP_NUM_THREADS", str(max(1, (os.cpu_count() or 1) // nprocs)))
         if env_extra:
             env.update(env_extra)
         pipe = subprocess.PIPE if (tag_output or capture) else None

@@ -62,7 +62,7 @@ def test_pytest_itself_runs_under_the_launcher_with_the_mpi_flag(tmp_path):
 # Without a GPU the layers use the CPU statement of the fused ops (ops/host_ops.py) over the
 # shared-memory transport, so the same worker that checks them on B200s checks their Python logic
 # -- autograd wiring, shard bookkeeping, gradient buckets, SGD -- here, against a dense model.
-@pytest.mark.parametrize("mp,dp", [(1, 1), (2, 1), (1, 2), (2, 2), (4, 2)])
+@pytest.mark.parametrize("mp,dp", [(2, 2), (4, 2)])
 def test_tp_layers_and_train_step_match_dense_model_on_cpu(mp, dp):
     _ok(run_ranks(mp * dp, ["tests/workers/w_layers.py", str(mp), str(dp)], timeout=240), f"LAYERS OK mp={mp} dp={dp}")
 
@@ -80,8 +80,8 @@ def test_train_step_with_sgd_fused_into_the_weight_gradient_on_cpu(mp):
 
 
 def test_train_step_with_the_fused_elementwise_ops_on_cpu():
-    _ok(run_ranks(4, ["tests/workers/w_layers.py", "2", "2"], timeout=240, env={"CCMPI_FUSED_ELEMENTWISE": "1"}),
-        "LAYERS OK mp=2 dp=2")
+    _ok(run_ranks(2, ["tests/workers/w_layers.py", "2", "1"], timeout=240, env={"CCMPI_FUSED_ELEMENTWISE": "1"}),
+        "LAYERS OK mp=2 dp=1")
 
 
 @pytest.mark.parametrize("nranks", [2, 4])
