@@ -18,6 +18,10 @@ def test_collectives_p2p_split_and_accounting(nranks):
     _ok(run_ranks(nranks, ["tests/workers/w_collectives.py"]), f"COLLECTIVES OK ranks={nranks}")
 
 
+def test_collectives_p2p_split_and_accounting_with_cpu_torch_tensors():
+    _ok(run_ranks(4, ["tests/workers/w_collectives.py", "--torch-cpu"]), "COLLECTIVES OK ranks=4 cuda=False torch-cpu")
+
+
 @pytest.mark.parametrize("nranks", [4, 8])
 def test_grid_and_tp_communication_steps(nranks):
     _ok(run_ranks(nranks, ["tests/workers/w_tp_steps.py"]), f"TP STEPS OK ranks={nranks}")

@@ -10,20 +10,26 @@ from mpi4py import MPI
 from mpi_wrapper import Communicator
 
 CUDA = "--cuda" in sys.argv
+TORCH_CPU = "--torch-cpu" in sys.argv        # CPU tensors instead of NumPy arrays (same memory, other front door)
 world = MPI.COMM_WORLD
 rank, n = world.Get_rank(), world.Get_size()
 
-if CUDA:
+if CUDA or TORCH_CPU:
     import torch
+if CUDA:
     torch.cuda.set_device(rank)
 
 
 def put(a):
-    return torch.from_numpy(np.ascontiguousarray(a)).cuda() if CUDA else a
+    if CUDA:
+        return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    if TORCH_CPU:
+        return torch.from_numpy(np.array(a, copy=True))
+    return a
 
 
 def get(a):
-    return a.cpu().numpy() if CUDA else a
+    return a.cpu().numpy() if (CUDA or TORCH_CPU) else a
 
 
 def empty(shape, dtype):
@@ -156,4 +162,4 @@ assert world.bcast({"k": rank} if rank == 0 else None) == {"k": 0}
 assert world.allreduce(rank, op=MPI.SUM) == n * (n - 1) // 2
 world.Barrier()
 if rank == 0:
-    print(f"COLLECTIVES OK ranks={n} cuda={CUDA}")
+    print(f"COLLECTIVES OK ranks={n} cuda={CUDA}" + (" torch-cpu" if TORCH_CPU else ""))
