@@ -50,3 +50,53 @@ def linear_fp8(x: torch.Tensor, w_nk: torch.Tensor, **kw) -> torch.Tensor:
     xq, sx = quantize_e4m3(x)
     wq, sw = quantize_e4m3(w_nk)
     return gemm_fp8(xq, wq, float(sx * sw), **kw)
+
+
+# -------------------------------------------------------------------------------------------------
+# MX (block-scaled) quantisation: host side of the planned tcgen05 ``kind::mxf8f6f4.block_scale`` GEMM
+# (DESIGN.md section 6). Pure PyTorch, runs on CPU or GPU; the kernel that consumes it is not built yet.
+# -------------------------------------------------------------------------------------------------
+MX_BLOCK = 32          # elements sharing one scale (OCP MXFP8)
+SF_ROWS, SF_COLS = 128, 4   # one 512-byte chunk of the hardware scale layout: 128 rows x 4 scales
+
+
+def quantize_mxfp8(x: torch.Tensor):
+    """``x[R, K]`` -> ``(q, sf)``: ``q`` is ``float8_e4m3fn`` ``[R, K]``, ``sf`` is ``uint8 [R, K/32]`` holding one
+    UE8M0 scale (biased power-of-two exponent) per 1 x 32 block, chosen so the block's largest magnitude fits
+    e4m3's range: ``x ~= q * 2**(sf - 127)``."""
+    if x.dim() != 2 or x.shape[1] % MX_BLOCK:
+        raise ValueError(f"expected [R, K] with K a multiple of {MX_BLOCK}, got {tuple(x.shape)}")
+    R, K = x.shape
+    blocks = x.float().reshape(R, K // MX_BLOCK, MX_BLOCK)
+    amax = blocks.abs().amax(dim=-1).clamp_min(2.0 ** -126)
+    exp = torch.ceil(torch.log2(amax / E4M3_MAX)).clamp(-127, 127)
+    q = (blocks / torch.exp2(exp).unsqueeze(-1)).clamp(-E4M3_MAX, E4M3_MAX).reshape(R, K).to(torch.float8_e4m3fn)
+    return q, (exp + 127).to(torch.uint8)
+
+
+def dequantize_mxfp8(q: torch.Tensor, sf: torch.Tensor) -> torch.Tensor:
+    R, K = q.shape
+    scale = torch.exp2(sf.float() - 127.0).unsqueeze(-1)
+    return (q.float().reshape(R, K // MX_BLOCK, MX_BLOCK) * scale).reshape(R, K)
+
+
+def sf_chunk_offset(r: int, k: int, k_scales: int) -> int:
+    """Byte offset of the scale of row ``r``, scale column ``k`` in the layout the tensor cores read
+    (cutlass/detail/sm100_blockscaled_layout.hpp): 512-byte chunks of 128 rows x 4 scales, K-fastest, and
+    inside a chunk ``(r % 32) * 16 + (r // 32) * 4 + k``."""
+    chunks_k = (k_scales + SF_COLS - 1) // SF_COLS
+    chunk = (r // SF_ROWS) * chunks_k + k // SF_COLS
+    rr, kk = r % SF_ROWS, k % SF_COLS
+    return chunk * SF_ROWS * SF_COLS + (rr % 32) * 16 + (rr // 32) * 4 + kk
+
+
+def swizzle_scales(sf: torch.Tensor) -> torch.Tensor:
+    """Row-major ``[R, K/32]`` scales -> the chunked hardware layout (flat ``uint8``, rows and scale columns
+    padded to whole chunks with the neutral exponent 127)."""
+    R, Ks = sf.shape
+    Rp, Kp = -(-R // SF_ROWS) * SF_ROWS, -(-Ks // SF_COLS) * SF_COLS
+    pad = torch.full((Rp, Kp), 127, dtype=torch.uint8, device=sf.device)
+    pad[:R, :Ks] = sf
+    # [row chunk, 4 x 32 rows, k chunk, 4] -> [row chunk, k chunk, 32, 4 (row quarter), 4 (k)]
+    t = pad.reshape(Rp // SF_ROWS, 4, 32, Kp // SF_COLS, SF_COLS).permute(0, 3, 2, 1, 4)
+    return t.contiguous().reshape(-1)
