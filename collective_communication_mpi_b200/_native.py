@@ -167,6 +167,7 @@ def _declare_device(lib):
         "ccmpi_gelu_fwd": (i, [vp, vp, ll, vp]),
         "ccmpi_gelu_bwd": (i, [vp, vp, vp, ll, vp]),
         "ccmpi_gemm_sgd_bf16": (i, [vp, vp, vp, i, i, i, i, i, i, i, i, f, i, vp]),
+        "ccmpi_gemm_mxfp8": (i, [vp, vp, vp, vp, vp, i, i, i, i, i, i, i, i, vp]),
         "ccmpi_mse_workspace_bytes": (sz, []),
         "ccmpi_mse_fwd_bwd": (i, [vp, vp, vp, ll, vp, vp, vp]),
     })

@@ -100,3 +100,26 @@ def swizzle_scales(sf: torch.Tensor) -> torch.Tensor:
     # [row chunk, 4 x 32 rows, k chunk, 4] -> [row chunk, k chunk, 32, 4 (row quarter), 4 (k)]
     t = pad.reshape(Rp // SF_ROWS, 4, 32, Kp // SF_COLS, SF_COLS).permute(0, 3, 2, 1, 4)
     return t.contiguous().reshape(-1)
+
+
+def gemm_mxfp8(a_q: torch.Tensor, a_sf: torch.Tensor, b_q: torch.Tensor, b_sf: torch.Tensor, *,
+               out_dtype=torch.bfloat16, out=None, num_sms: int = 0, stream=None) -> torch.Tensor:
+    """``out[M,N] = dequant(a) @ dequant(b).T`` on the block-scaled tensor-core path (csrc/gemm_mxfp8.cu).
+    ``a_q [M,K]`` / ``b_q [N,K]``: ``float8_e4m3fn``; ``a_sf [M,K/32]`` / ``b_sf [N,K/32]``: row-major UE8M0
+    scales as returned by ``quantize_mxfp8`` (re-laid out here). Experimental: not yet run on hardware."""
+    if a_q.dtype != torch.float8_e4m3fn or b_q.dtype != torch.float8_e4m3fn:
+        raise TypeError("gemm_mxfp8 takes float8_e4m3fn operands")
+    M, K = a_q.shape
+    Nn = b_q.shape[0]
+    if b_q.shape[1] != K or K % 128 or a_sf.shape != (M, K // MX_BLOCK) or b_sf.shape != (Nn, K // MX_BLOCK):
+        raise ValueError("shapes: a [M,K], b [N,K], K a multiple of 128, scales [rows, K/32]")
+    sa, sb = swizzle_scales(a_sf), swizzle_scales(b_sf)
+    if out is None:
+        out = torch.empty((M, Nn), dtype=out_dtype, device=a_q.device)
+    s = stream if stream is not None else torch.cuda.current_stream()
+    rc = N.device_lib().ccmpi_gemm_mxfp8(a_q.data_ptr(), sa.data_ptr(), b_q.data_ptr(), sb.data_ptr(), out.data_ptr(), M, Nn, K,
+                                         a_q.stride(0), b_q.stride(0), out.stride(0),
+                                         N.BF16 if out.dtype == torch.bfloat16 else N.F32, num_sms, s.cuda_stream)
+    N.check(rc, "ccmpi_gemm_mxfp8")
+    N.count_launch()
+    return out

@@ -258,6 +258,14 @@ int ccmpi_gemm_sgd_bf16(const void* A, const void* B, void* W, int M, int N, int
 int ccmpi_gemm_fp8_e4m3(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb,
                         int ldc, float scale, int out_dtype, int num_sms, void* stream);
 
+/* EXPERIMENTAL DRAFT (compiled, not yet run on hardware in round 1): block-scaled fp8 GEMM (OCP MXFP8:
+ * e4m3 values, one UE8M0 scale per 1 x 32 block), C[M][N] = (A * 2^sfa) (B * 2^sfb)^T with both operands
+ * K-major, on tcgen05.mma.kind::mxf8f6f4.block_scale (csrc/gemm_mxfp8.cu). sfa / sfb are in the tensor
+ * cores' chunked layout: 512-byte chunks of 128 rows x 4 scales, K-fastest, padded to whole chunks
+ * (collective_communication_mpi_b200/ops/gemm_fp8.py::swizzle_scales). K must be a multiple of 128. */
+int ccmpi_gemm_mxfp8(const void* A, const void* sfa, const void* B, const void* sfb, void* C, int M, int N,
+                     int K, int lda, int ldb, int ldc, int out_dtype, int num_sms, void* stream);
+
 /* No counterpart in the reference: it never allocates device memory because it has no device
  * code. This is the GEMM -> reduce-scatter kernel of ccmpi_fused_gemm_rs for a ONE-GPU
  * communicator (C[M][N] = A * B), for callers that must not allocate device memory when they
