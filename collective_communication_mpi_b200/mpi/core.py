@@ -459,6 +459,33 @@ class Comm:
             scratch = np.empty(s.count, dtype=_np_dtype_of(s))
             self.Allreduce(sendbuf, scratch, op)
 
+    def Gather(self, sendbuf, recvbuf, root: int = 0):
+        """``MPI_Gather`` of equal blocks: built on the all-gather (every rank pays for the full
+        result, the root keeps it) -- not on any hot path of the reference, kept for mpi4py users."""
+        s = _Buf(sendbuf, False)
+        n = len(self._members)
+        if self._me == root:
+            self.Allgather(sendbuf, recvbuf)
+        else:
+            scratch = np.empty(s.count * n, dtype=_np_dtype_of(s)) if not s.cuda else _empty_like_flat(s, s.count * n)
+            self.Allgather(sendbuf, scratch)
+
+    def Scatter(self, sendbuf, recvbuf, root: int = 0):
+        """``MPI_Scatter`` of equal blocks: block ``i`` of the root's ``sendbuf`` lands in rank ``i``'s
+        ``recvbuf`` (an all-to-all in which only the root's row carries data)."""
+        r = _Buf(recvbuf, True)
+        n = len(self._members)
+        if self._me == root:
+            s = _Buf(sendbuf, False)
+            if s.nbytes != r.nbytes * n:
+                raise ValueError(f"Scatter: send buffer holds {s.nbytes} B, expected {n} x {r.nbytes} B")
+            src = sendbuf
+        else:
+            src = np.zeros(r.count * n, dtype=_np_dtype_of(r)) if not r.cuda else _empty_like_flat(r, r.count * n)
+        out = np.empty(r.count * n, dtype=_np_dtype_of(r)) if not r.cuda else _empty_like_flat(r, r.count * n)
+        self.Alltoall(src, out)
+        _copy(r, _Buf(out.reshape(n, -1)[root], False))
+
     # ---- point-to-point ------------------------------------------------------------------
     def _peer(self, r: int) -> int:
         if not 0 <= r < len(self._members):
@@ -659,6 +686,16 @@ class Comm:
             acc = acc + v if op == SUM else (min(acc, v) if op == MIN else (max(acc, v) if op == MAX else acc * v))
         return acc
 
+    def sendrecv(self, sendobj, dest: int, sendtag: int = 0, recvbuf=None, source: int = ANY_SOURCE,
+                 recvtag: int = ANY_TAG, status=None):
+        """Object ``sendrecv``: the lengths are exchanged first, so neither side has to probe."""
+        blob = np.frombuffer(pickle.dumps(_to_wire(sendobj), protocol=pickle.HIGHEST_PROTOCOL), dtype=np.uint8)
+        mine, theirs = np.array([blob.size], dtype=np.int64), np.empty(1, dtype=np.int64)
+        self.Sendrecv(mine, dest, sendtag, theirs, source, recvtag)
+        got = np.empty(int(theirs[0]), dtype=np.uint8)
+        self.Sendrecv(blob, dest, sendtag, got, source, recvtag)
+        return pickle.loads(got.tobytes())
+
     def send(self, obj, dest: int, tag: int = 0):
         blob = np.frombuffer(pickle.dumps(obj, protocol=pickle.HIGHEST_PROTOCOL), dtype=np.uint8)
         self.Send(blob, dest, tag)
@@ -690,6 +727,12 @@ def _to_wire(obj):
 
 def _from_wire(obj, device):
     return obj.to(device) if device is not None and _is_torch(obj) else obj
+
+
+def _empty_like_flat(b: _Buf, count: int):
+    """Scratch with ``count`` elements of ``b``'s element type on ``b``'s device (torch buffers)."""
+    import torch
+    return torch.empty(count, dtype=b.flat.dtype, device=b.flat.device)
 
 
 def _np_dtype_of(b: _Buf):

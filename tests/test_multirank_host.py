@@ -115,3 +115,29 @@ if r == 0: print("TORCH CPU OK", n)
 
 def test_last_axis_collectives_accept_cpu_torch_tensors():
     _ok(run_ranks(4, ["-c", TORCH_CPU_CODE], timeout=120), "TORCH CPU OK 4")
+
+
+GATHER_SCATTER_CODE = r'''
+import numpy as np
+from mpi4py import MPI
+w = MPI.COMM_WORLD; r, n = w.Get_rank(), w.Get_size()
+for root in (0, n - 1):
+    out = np.empty(3 * n, dtype=np.float64) if r == root else None
+    w.Gather(np.full(3, r + 0.5), out, root=root)
+    if r == root:
+        assert out.tolist() == [q + 0.5 for q in range(n) for _ in range(3)]
+    src = (np.arange(2 * n, dtype=np.int32) + 100 * root) if r == root else None
+    got = np.empty(2, dtype=np.int32)
+    w.Scatter(src, got, root=root)
+    assert got.tolist() == [2 * r + 100 * root, 2 * r + 1 + 100 * root], (r, got)
+nxt, prv = (r + 1) % n, (r - 1) % n
+got = w.sendrecv({"from": r, "pad": "x" * (r * 1000)}, dest=nxt, source=prv)
+assert got["from"] == prv and len(got["pad"]) == prv * 1000
+w.Barrier()
+if r == 0: print("GS OK", n)
+'''
+
+
+def test_gather_scatter_and_object_sendrecv():
+    """mpi4py members beyond what the reference touches (SURVEY Appendix B), for users switching over."""
+    _ok(run_ranks(4, ["-c", GATHER_SCATTER_CODE], timeout=120), "GS OK 4")
