@@ -141,3 +141,13 @@ if r == 0: print("GS OK", n)
 def test_gather_scatter_and_object_sendrecv():
     """mpi4py members beyond what the reference touches, for users switching over."""
     _ok(run_ranks(4, ["-c", GATHER_SCATTER_CODE], timeout=120), "GS OK 4")
+
+
+def test_training_example_runs_and_learns_on_cpu():
+    import sys
+    from conftest import REPO
+    import subprocess
+    p = subprocess.run([sys.executable, "-m", "collective_communication_mpi_b200.launch", "-n", "2", sys.executable,
+                        "examples/train_block.py", "--mp", "2", "--steps", "6"], cwd=REPO, capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
+    assert "TRAIN OK" in p.stdout, p.stdout[-1000:]
