@@ -1,1 +1,1 @@
-from .fc_stack import MLPStack, TrainStep, TransformerFCBlock  # noqa: F401
+from .fc_stack import MLPStack, TrainStep, TransformerFCBlock, TransformerFCBlockSP  # noqa: F401

@@ -50,6 +50,34 @@ class TransformerFCBlock(nn.Module):
         return h + self.fc2(u)
 
 
+class TransformerFCBlockSP(nn.Module):
+    """The same block in the sequence-parallel layout (``parallel/sp_layers.py``): input and output are
+    this rank's ``tokens/mp`` rows of the full width, so the residual adds touch 1/mp of the data; between
+    the GEMM pairs the activation is feature-sharded as in ``TransformerFCBlock``."""
+
+    def __init__(self, mp_comm, tokens: int, hidden: int, ffn_mult: int = 4, *, seed: int = 0):
+        super().__init__()
+        from ..parallel.sp_layers import SeqColumnParallelLinear, SeqRowParallelLinear
+        self.hidden, self.mp = hidden, mp_comm.Get_size()
+        self.fc_qkv = SeqColumnParallelLinear(mp_comm, tokens, hidden, 3 * hidden, seed=seed + 1)
+        self.fc_o = SeqRowParallelLinear(mp_comm, tokens, hidden, hidden, seed=seed + 2)
+        self.fc1 = SeqColumnParallelLinear(mp_comm, tokens, hidden, ffn_mult * hidden, seed=seed + 3)
+        self.fc2 = SeqRowParallelLinear(mp_comm, tokens, ffn_mult * hidden, hidden, seed=seed + 4)
+        self.fused_elementwise = EW.enabled()
+
+    def tp_layers(self) -> List[nn.Module]:
+        return [self.fc_qkv, self.fc_o, self.fc1, self.fc2]
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if self.fused_elementwise:
+            h = x + self.fc_o(EW.gate(self.fc_qkv(x)))
+            return h + self.fc2(EW.gelu(self.fc1(h)))
+        q, k, v = self.fc_qkv(x).chunk(3, dim=-1)
+        h = x + self.fc_o(v * torch.sigmoid(q * k))
+        u = torch.nn.functional.gelu(self.fc1(h), approximate="tanh")
+        return h + self.fc2(u)
+
+
 class MLPStack(nn.Module):
     def __init__(self, mp_comm, tokens: int, width: int, depth: int, *, seed: int = 0):
         super().__init__()

@@ -95,3 +95,38 @@ class GemmAllGather:
 
     def __call__(self, a, b, *, a_km: bool = False, b_kn: bool = True, num_sms: int = 0, stream=None):
         return self.comm.gather_last_axis(gemm(a, b, a_km=a_km, b_kn=b_kn, out_dtype=self.dtype))
+
+
+# ---- token-axis (sequence-parallel) forms: ops/fused_seq.py -----------------------------------------
+class AllGatherGemmM:
+    """``concat_rows(x_0, ..., x_{n-1}) @ w``; ``x``: this rank's ``[M/n, K]`` rows."""
+
+    def __init__(self, comm, M: int, K: int):
+        self.comm, self.M, self.K = comm, M, K
+        self._gathered = None
+
+    def gathered(self) -> torch.Tensor:
+        return self._gathered
+
+    def __call__(self, x, w, *, b_kn: bool = True, out=None, out_dtype=torch.bfloat16, num_sms: int = 0, stream=None):
+        full = torch.empty((self.M, self.K), dtype=x.dtype)
+        self.comm.Allgather(x.reshape(-1, self.K).contiguous(), full)      # row blocks are contiguous: a flat all-gather
+        self._gathered = full
+        return gemm(full, w, b_kn=b_kn, out=out, out_dtype=out_dtype)
+
+
+class GemmReduceScatterM:
+    """Rows ``[rank*M/n, (rank+1)*M/n)`` of ``sum over ranks of a @ b``."""
+
+    def __init__(self, comm, M: int, Nfull: int, *, dtype=torch.bfloat16):
+        self.comm, self.M, self.N, self.dtype = comm, M, Nfull, dtype
+
+    def __call__(self, a, b, *, a_km: bool = False, b_kn: bool = False, out=None, num_sms: int = 0, stream=None):
+        part = gemm(a, b, a_km=a_km, b_kn=b_kn, out_dtype=torch.float32).contiguous()
+        red = torch.empty((self.M // self.comm.Get_size(), self.N), dtype=torch.float32)
+        self.comm.Reduce_scatter_block(part, red)
+        red = red.to(self.dtype)
+        if out is not None:
+            out.copy_(red)
+            return out
+        return red

@@ -134,3 +134,13 @@ def test_column_parallel_layer_with_gathered_output(fused):
     proc = run_ranks(n, ["tests/workers/w_gather_output.py"], transport="device", env={"CCMPI_FUSED_GATHER_OUTPUT": fused})
     assert proc.returncode == 0, f"rc={proc.returncode}\n{proc.stdout[-3000:]}\n{proc.stderr[-3000:]}"
     assert f"GATHER OUTPUT OK ranks={n} fused={fused}" in proc.stdout
+
+
+@pytest.mark.parametrize("mp,dp", [(2, 1), (2, 2), (4, 2)])
+def test_sequence_parallel_block_matches_dense_model(mp, dp):
+    from conftest import gpu_count, run_ranks
+    if gpu_count() < mp * dp:
+        pytest.skip(f"needs {mp * dp} GPUs")
+    proc = run_ranks(mp * dp, ["tests/workers/w_layers.py", str(mp), str(dp), "--sp"], transport="device")
+    assert proc.returncode == 0, f"rc={proc.returncode}\n{proc.stdout[-3000:]}\n{proc.stderr[-3000:]}"
+    assert f"LAYERS OK mp={mp} dp={dp} sp=1" in proc.stdout

@@ -151,3 +151,10 @@ def test_training_example_runs_and_learns_on_cpu():
                         "examples/train_block.py", "--mp", "2", "--steps", "6"], cwd=REPO, capture_output=True, text=True, timeout=300)
     assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
     assert "TRAIN OK" in p.stdout, p.stdout[-1000:]
+
+
+@pytest.mark.parametrize("mp,dp,env", [(2, 2, None), (4, 1, None), (2, 1, {"CCMPI_FUSED_SGD": "1", "CCMPI_FUSED_ELEMENTWISE": "1"})])
+def test_sequence_parallel_block_matches_dense_model_on_cpu(mp, dp, env):
+    """Megatron-SP layout (parallel/sp_layers.py): token-sharded activations outside the GEMM pairs."""
+    _ok(run_ranks(mp * dp, ["tests/workers/w_layers.py", str(mp), str(dp), "--sp"], timeout=240, env=env),
+        f"LAYERS OK mp={mp} dp={dp} sp=1")

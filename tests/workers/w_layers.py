@@ -1,5 +1,6 @@
 """Rank-side check of the tensor-parallel layers / model / train step against a dense fp32
-PyTorch model assembled from the gathered weight shards. Args: MP DP."""
+PyTorch model assembled from the gathered weight shards. Args: MP DP [--sp].
+``--sp``: the sequence-parallel block (activations sharded by tokens outside the GEMM pairs)."""
 import sys
 
 import torch
@@ -7,9 +8,10 @@ import torch
 from mpi4py import MPI
 from model.func_impl import get_info
 from data.data_parallel_preprocess import split_data
-from collective_communication_mpi_b200.models import TrainStep, TransformerFCBlock
+from collective_communication_mpi_b200.models import TrainStep, TransformerFCBlock, TransformerFCBlockSP
 
 mp, dp = int(sys.argv[1]), int(sys.argv[2])
+SP = "--sp" in sys.argv
 world = MPI.COMM_WORLD
 rank, n = world.Get_rank(), world.Get_size()
 assert n == mp * dp
@@ -27,7 +29,11 @@ def sync():
 mp_idx, dp_idx, mp_comm, dp_comm, _, _ = get_info(comm=world, rank=rank, mp_size=mp, dp_size=dp, fc_layer="fc_q",
                                                   in_dim=1024, out_dim=1024)
 H, TOK = (512 if mp <= 4 else 1024), 256     # every scattered chunk must be >= 128 wide
-model = TransformerFCBlock(mp_comm, TOK, H, ffn_mult=4, seed=7, num_comm_ctas=2)
+if SP:
+    TOK = 256 * mp                            # the kernels want 256 rows per rank
+    model = TransformerFCBlockSP(mp_comm, TOK, H, ffn_mult=4, seed=7)
+else:
+    model = TransformerFCBlock(mp_comm, TOK, H, ffn_mult=4, seed=7, num_comm_ctas=2)
 
 # global batch: dp replicas x TOK tokens, feature-sharded over mp
 g = torch.Generator().manual_seed(123)
@@ -35,8 +41,16 @@ X = torch.randn(dp * TOK, H, generator=g) * 0.5
 T = torch.randn(dp * TOK, H, generator=g) * 0.5
 xs, ts = split_data(X, T, mp_size=mp, dp_size=dp, rank=rank)
 sh = H // mp
-x_loc = xs[:, mp_idx * sh:(mp_idx + 1) * sh].contiguous().to(DEV).bfloat16()
-t_loc = ts[:, mp_idx * sh:(mp_idx + 1) * sh].contiguous().to(DEV).bfloat16()
+rows = TOK // mp
+
+
+def shard(full, r):
+    """Rank r's part of a [TOK, H] activation: a column block, or a row block with --sp."""
+    return full[r * rows:(r + 1) * rows] if SP else full[:, r * sh:(r + 1) * sh]
+
+
+x_loc = shard(xs, mp_idx).contiguous().to(DEV).bfloat16()
+t_loc = shard(ts, mp_idx).contiguous().to(DEV).bfloat16()
 
 
 def full_weight(layer, axis):
@@ -65,7 +79,7 @@ ref = dense_forward(x_full)
 y = model(x_loc)
 sync()
 got = y.float()
-want = ref[:, mp_idx * sh:(mp_idx + 1) * sh]
+want = shard(ref, mp_idx)
 err = (got - want).abs().max().item()
 assert err < 0.06 * max(1.0, want.abs().max().item()), f"forward mismatch {err}"
 
@@ -89,7 +103,7 @@ def dense_loss(x_full, t_full):
     yy = h + u @ params[mp + 2]
     # every rank's loss is the mean over ITS shard; the model-parallel sum of those is mp x the
     # mean over the full width
-    return sum(torch.nn.functional.mse_loss(yy[:, r * sh:(r + 1) * sh], t_full[:, r * sh:(r + 1) * sh]) for r in range(mp))
+    return sum(torch.nn.functional.mse_loss(shard(yy, r), shard(t_full, r)) for r in range(mp))
 
 
 total = 0.0
@@ -109,4 +123,4 @@ for name, layer, w0, gref in zip(("qkv", "o", "fc1", "fc2"), model.tp_layers(), 
     assert e < 0.08 * scale + 2e-3, f"{name}: grad mismatch {e} (scale {scale})"
 world.Barrier()
 if rank == 0:
-    print(f"LAYERS OK mp={mp} dp={dp} loss={loss.item():.4f} ar_launches={step.sink.launches if step.sink else 0} fused_sgd={int(step.fused_sgd)}")
+    print(f"LAYERS OK mp={mp} dp={dp} sp={int(SP)} loss={loss.item():.4f} ar_launches={step.sink.launches if step.sink else 0} fused_sgd={int(step.fused_sgd)}")
