@@ -12,9 +12,12 @@
 //     execute in issue order, and the scale columns are double-buffered by K-block parity.
 // Tile: 256 x 128 per pair (two 128-column accumulators + 16 scale columns of tensor memory).
 //
-// EXPERIMENTAL DRAFT (round 1): compiles for sm_100a; NOT yet run on hardware -- descriptor encodings and the
-// tensor-memory scale addressing are taken from the CUTLASS 4.5 headers, not from an experiment. Nothing
-// uses it; its test is opt-in (CCMPI_TEST_UNVERIFIED=1).
+// EXPERIMENTAL DRAFT (round 1): compiles for sm_100a; NOT yet run on hardware. What could be checked without
+// a GPU was: the instruction descriptor, the shared-memory descriptor of a scale chunk (LBO 16 B, SBO 128 B,
+// no swizzle) and the scale layouts in shared and tensor memory (32 lanes x 4 columns per chunk, scale id =
+// byte of the column, replicated to the four lane quadrants) are bit-for-bit what the CUTLASS 4.5 headers on
+// the image compute for this tile (evaluated in a host program). Nothing uses the kernel; its test is opt-in
+// (CCMPI_TEST_UNVERIFIED=1).
 #include "gemm_host.h"
 
 namespace mx {
@@ -171,8 +174,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1) gemm
                     ptx::mbar_wait(&full[stage], phase, 300 + stage);
                     ptx::tc_fence_after();
                     const uint32_t sf = tmem_base + SF_COL0 + (kb & 1) * 8;     // 4 columns SFA, then 4 columns SFB
-                    utccp_32x128b_2sm(sf, smem_desc_noswizzle(ptx::smem_u32(smem_sfa(stage)), 0, 128));
-                    utccp_32x128b_2sm(sf + 4, smem_desc_noswizzle(ptx::smem_u32(smem_sfb(stage)), 0, 128));
+                    // LBO 16 B / SBO 128 B: the values CUTLASS's get_utccp_smem_desc_tensor produces for this chunk
+                    utccp_32x128b_2sm(sf, smem_desc_noswizzle(ptx::smem_u32(smem_sfa(stage)), 16, 128));
+                    utccp_32x128b_2sm(sf + 4, smem_desc_noswizzle(ptx::smem_u32(smem_sfb(stage)), 16, 128));
                     const uint32_t a_addr = ptx::smem_u32(smem_a(stage));
                     const uint32_t b_addr = ptx::smem_u32(smem_b(stage));
 #pragma unroll
