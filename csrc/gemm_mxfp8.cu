@@ -19,6 +19,7 @@
 // the image compute for this tile (evaluated in a host program). Nothing uses the kernel; its test is opt-in
 // (CCMPI_TEST_UNVERIFIED=1).
 #include "gemm_host.h"
+#include "mx_desc.cuh"
 
 namespace mx {
 
@@ -45,29 +46,9 @@ struct Params {
     int out_bf16;
 };
 
-// Shared-memory matrix descriptor without swizzle: 8-row x 16-byte core matrices `sbo` bytes apart.
-__device__ __forceinline__ uint64_t smem_desc_noswizzle(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-    uint64_t d = 0;
-    d |= static_cast<uint64_t>((smem_addr >> 4) & 0x3fff);
-    d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3fff) << 16;
-    d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3fff) << 32;
-    d |= 1ull << 46;      // descriptor version: Blackwell; layout type 0 = no swizzle
-    return d;
-}
-
 // 32 rows x 16 bytes of shared memory -> 4 columns of tensor memory, replicated to the four lane quadrants
 __device__ __forceinline__ void utccp_32x128b_2sm(uint32_t taddr, uint64_t sdesc) {
     asm volatile("tcgen05.cp.cta_group::2.32x128b.warpx4 [%0], %1;" ::"r"(taddr), "l"(sdesc) : "memory");
-}
-
-// Instruction descriptor of kind::mxf8f6f4.block_scale: e4m3 x e4m3, K-major, E8M0 scales
-__host__ __device__ constexpr uint32_t idesc_mx(uint32_t m, uint32_t n, uint32_t sf_id) {
-    return (sf_id << 4)               // B scale id (byte of the tensor-memory word)
-           | (0u << 7) | (0u << 10)   // A / B format: e4m3
-           | ((n >> 3) << 17)
-           | (1u << 23)               // scale format: E8M0
-           | ((m >> 4) << 24)
-           | (sf_id << 29);           // A scale id
 }
 
 __device__ __forceinline__ void umma_mx_ss_2sm(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
@@ -175,8 +156,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1) gemm
                     ptx::tc_fence_after();
                     const uint32_t sf = tmem_base + SF_COL0 + (kb & 1) * 8;     // 4 columns SFA, then 4 columns SFB
                     // LBO 16 B / SBO 128 B: the values CUTLASS's get_utccp_smem_desc_tensor produces for this chunk
-                    utccp_32x128b_2sm(sf, smem_desc_noswizzle(ptx::smem_u32(smem_sfa(stage)), 16, 128));
-                    utccp_32x128b_2sm(sf + 4, smem_desc_noswizzle(ptx::smem_u32(smem_sfb(stage)), 16, 128));
+                    utccp_32x128b_2sm(sf, smem_desc_noswizzle(ptx::smem_u32(smem_sfa(stage)), SF_CHUNK_LBO, SF_CHUNK_SBO));
+                    utccp_32x128b_2sm(sf + 4, smem_desc_noswizzle(ptx::smem_u32(smem_sfb(stage)), SF_CHUNK_LBO, SF_CHUNK_SBO));
                     const uint32_t a_addr = ptx::smem_u32(smem_a(stage));
                     const uint32_t b_addr = ptx::smem_u32(smem_b(stage));
 #pragma unroll
