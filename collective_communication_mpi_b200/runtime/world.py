@@ -50,6 +50,7 @@ class World:
         self._hostlib = None
         self.heap = None           # SymmetricHeap or None
         self._device_tried = False
+        self._device_ok = {}
         self.device_error: Optional[str] = None
         self.mc_supported = False
         self.stage = None
@@ -114,6 +115,9 @@ class World:
         mode = os.environ.get("CCMPI_TRANSPORT", "auto").lower()
         if mode == "host":
             return False
+        cached = self._device_ok.get(mode)      # asked on every collective call: probe the driver once
+        if cached is not None:
+            return cached
         try:
             import torch
             ok = torch.cuda.is_available() and torch.cuda.device_count() > self.local_rank and \
@@ -122,6 +126,7 @@ class World:
             ok = False
         if mode == "device" and not ok:
             raise RuntimeError("CCMPI_TRANSPORT=device but there is no GPU per rank on this node")
+        self._device_ok[mode] = ok
         return ok
 
     def ensure_heap(self):
