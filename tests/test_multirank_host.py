@@ -71,16 +71,15 @@ def test_tp_layers_and_train_step_match_dense_model_on_cpu(mp, dp):
     _ok(run_ranks(mp * dp, ["tests/workers/w_layers.py", str(mp), str(dp)], timeout=240), f"LAYERS OK mp={mp} dp={dp}")
 
 
-@pytest.mark.parametrize("mp", [1, 2])
-def test_train_step_with_sgd_fused_into_the_weight_gradient_on_cpu(mp):
+def test_train_step_with_sgd_fused_into_the_weight_gradient_on_cpu():
     """dp = 1: every dW GEMM applies its own SGD step; dx must have read W before that."""
-    _ok(run_ranks(mp, ["tests/workers/w_layers.py", str(mp), "1"], timeout=240, env={"CCMPI_FUSED_SGD": "1"}),
-        f"LAYERS OK mp={mp} dp=1")
+    p = run_ranks(2, ["tests/workers/w_layers.py", "2", "1"], timeout=240, env={"CCMPI_FUSED_SGD": "1"})
+    _ok(p, "LAYERS OK mp=2 dp=1")
+    assert "fused_sgd=1" in p.stdout
     # with data parallelism the switch is ignored (the gradient has to be reduced first)
-    if mp == 1:
-        p = run_ranks(2, ["tests/workers/w_layers.py", "1", "2"], timeout=240, env={"CCMPI_FUSED_SGD": "1"})
-        _ok(p, "LAYERS OK mp=1 dp=2")
-        assert "fused_sgd=0" in p.stdout
+    p = run_ranks(2, ["tests/workers/w_layers.py", "1", "2"], timeout=240, env={"CCMPI_FUSED_SGD": "1"})
+    _ok(p, "LAYERS OK mp=1 dp=2")
+    assert "fused_sgd=0" in p.stdout
 
 
 def test_train_step_with_the_fused_elementwise_ops_on_cpu():
@@ -88,7 +87,7 @@ def test_train_step_with_the_fused_elementwise_ops_on_cpu():
         "LAYERS OK mp=2 dp=1")
 
 
-@pytest.mark.parametrize("nranks", [2, 4])
+@pytest.mark.parametrize("nranks", [4])
 def test_column_parallel_layer_with_gathered_output_on_cpu(nranks):
     _ok(run_ranks(nranks, ["tests/workers/w_gather_output.py"], timeout=240), f"GATHER OUTPUT OK ranks={nranks}")
 
@@ -153,7 +152,7 @@ def test_training_example_runs_and_learns_on_cpu():
     assert "TRAIN OK" in p.stdout, p.stdout[-1000:]
 
 
-@pytest.mark.parametrize("mp,dp,env", [(2, 2, None), (4, 1, None), (2, 1, {"CCMPI_FUSED_SGD": "1", "CCMPI_FUSED_ELEMENTWISE": "1"})])
+@pytest.mark.parametrize("mp,dp,env", [(2, 2, None), (2, 1, {"CCMPI_FUSED_SGD": "1", "CCMPI_FUSED_ELEMENTWISE": "1"})])
 def test_sequence_parallel_block_matches_dense_model_on_cpu(mp, dp, env):
     """Megatron-SP layout (parallel/sp_layers.py): token-sharded activations outside the GEMM pairs."""
     _ok(run_ranks(mp * dp, ["tests/workers/w_layers.py", str(mp), str(dp), "--sp"], timeout=240, env=env),
