@@ -510,7 +510,10 @@ class Comm:
         b = _Buf(buf, True)
         w = self._world
         if b.cuda and P2P.enabled() and w.device_available():
-            host = np.zeros(max(b.nbytes, P2P.DESC_BYTES), dtype=np.uint8)
+            # room for a whole payload (a NumPy sender uses the host path), but only the descriptor-sized
+            # head is touched when the sender is on the NVLink route
+            host = np.empty(max(b.nbytes, P2P.DESC_BYTES), dtype=np.uint8)
+            host[:P2P.DESC_BYTES] = 0
             src_world = self._peer(source)
             done = lambda: P2P.complete_receive(w, src_world, host, b.flat)  # noqa: E731
         elif b.cuda:
