@@ -51,6 +51,7 @@ class World:
         self.heap = None           # SymmetricHeap or None
         self._device_tried = False
         self._device_ok = {}
+        self.numa_node: Optional[int] = None
         self.device_error: Optional[str] = None
         self.mc_supported = False
         self.stage = None
@@ -139,6 +140,9 @@ class World:
         lib = N.device_lib()
         dev = self.local_rank
         torch.cuda.set_device(dev)
+        if os.environ.get("CCMPI_NUMA_BIND") == "1":      # opt-in: run next to the GPU (utils/numa.py)
+            from ..utils.numa import bind_to_gpu_node
+            self.numa_node = bind_to_gpu_node(dev)
         torch.zeros(1, device=f"cuda:{dev}")  # primary context
         probe = (C.c_int * 8)()
         N.check(lib.ccmpi_probe(dev, probe), "ccmpi_probe")
