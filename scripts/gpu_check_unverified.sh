@@ -32,4 +32,13 @@ fi
 CCMPI_FUSED_ELEMENTWISE=0 run bench_eager 300 python bench.py --steps 10 --warmup 3
 CCMPI_FUSED_ELEMENTWISE=1 run bench_fused 300 python bench.py --steps 10 --warmup 3
 CCMPI_FUSED_ELEMENTWISE=1 CCMPI_FUSED_SGD=1 run bench_fused_sgd 300 python bench.py --steps 10 --warmup 3
+if [ "$NG" -ge 2 ]; then
+    # end-to-end (H2D-bound at N >= 4 in round 1): does running each rank next to its GPU help?
+    P=29600
+    for bind in 0 1; do
+        P=$((P + 1))
+        CCMPI_NUMA_BIND=$bind run bench_e2e_numa$bind 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node "$NG" \
+            --master-addr 127.0.0.1 --master-port $P bench.py --gpus "$NG" --steps 10 --warmup 3
+    done
+fi
 cat "$OUT"
