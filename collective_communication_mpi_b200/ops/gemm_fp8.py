@@ -106,14 +106,25 @@ def gemm_mxfp8(a_q: torch.Tensor, a_sf: torch.Tensor, b_q: torch.Tensor, b_sf: t
                out_dtype=torch.bfloat16, out=None, num_sms: int = 0, stream=None) -> torch.Tensor:
     """``out[M,N] = dequant(a) @ dequant(b).T`` on the block-scaled tensor-core path (csrc/gemm_mxfp8.cu).
     ``a_q [M,K]`` / ``b_q [N,K]``: ``float8_e4m3fn``; ``a_sf [M,K/32]`` / ``b_sf [N,K/32]``: row-major UE8M0
-    scales as returned by ``quantize_mxfp8`` (re-laid out here). Experimental: not yet run on hardware."""
+    scales as returned by ``quantize_mxfp8`` (re-laid out here), or 1-D tensors already in the hardware
+    layout (``swizzle_scales``; do that once for weights). Experimental: not yet run on hardware."""
     if a_q.dtype != torch.float8_e4m3fn or b_q.dtype != torch.float8_e4m3fn:
         raise TypeError("gemm_mxfp8 takes float8_e4m3fn operands")
     M, K = a_q.shape
     Nn = b_q.shape[0]
-    if b_q.shape[1] != K or K % 128 or a_sf.shape != (M, K // MX_BLOCK) or b_sf.shape != (Nn, K // MX_BLOCK):
-        raise ValueError("shapes: a [M,K], b [N,K], K a multiple of 128, scales [rows, K/32]")
-    sa, sb = swizzle_scales(a_sf), swizzle_scales(b_sf)
+    if b_q.shape[1] != K or K % 128:
+        raise ValueError("shapes: a [M,K], b [N,K], K a multiple of 128")
+
+    def hw_layout(sf, rows):
+        if sf.dim() == 1:
+            if sf.numel() != -(-rows // SF_ROWS) * (K // 128) * SF_ROWS * SF_COLS:
+                raise ValueError("pre-swizzled scales have the wrong size")
+            return sf
+        if sf.shape != (rows, K // MX_BLOCK):
+            raise ValueError("row-major scales must be [rows, K/32]")
+        return swizzle_scales(sf)
+
+    sa, sb = hw_layout(a_sf, M), hw_layout(b_sf, Nn)
     if out is None:
         out = torch.empty((M, Nn), dtype=out_dtype, device=a_q.device)
     s = stream if stream is not None else torch.cuda.current_stream()

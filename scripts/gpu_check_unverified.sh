@@ -28,6 +28,8 @@ if [ "$NG" -ge 2 ]; then
     run p2p_device    300 python -m pytest tests/test_gpu_unverified_p2p.py -q
     run put_signal    300 python -m collective_communication_mpi_b200.launch -n "$NG" --transport device python tests/workers/w_collectives.py --cuda
 fi
+run extras_bench 600 python benchmarks/extras_bench.py
+cp gpurun_out/unverified_extras_bench_${NG}gpu.log gpurun_out/extras_bench_${NG}gpu.jsonl 2>/dev/null
 # the switch that would become the default once the elementwise kernels are verified
 CCMPI_FUSED_ELEMENTWISE=0 run bench_eager 300 python bench.py --steps 10 --warmup 3
 CCMPI_FUSED_ELEMENTWISE=1 run bench_fused 300 python bench.py --steps 10 --warmup 3
