@@ -30,10 +30,15 @@ struct AgMPolicy : PlainPolicy {
     __device__ static int mbpr(const RankParams& p) { return p.chunk / BM; }   // m-blocks per rank
     __device__ static int ready_idx(const RankParams& p, int src, int lm) { return p.flag_base + src * mbpr(p) + lm; }
 
-    // rows owned by this rank first, then rank+1, ...: their tiles need no remote data
+    // Owner-major order: ALL tiles of this rank's own rows first (they need no remote data), then the rows of
+    // rank+1, rank+2, ...; the grouped raster runs inside one owner's block of rows. (Rotating one global raster
+    // is not enough: a raster group of 8 m-pairs spans several owners as soon as a rank has fewer than 8 pairs.)
     __device__ static TileCoord tile(const RankParams& p, int t, int mb, int nb) {
-        TileCoord tc = raster(t, mb, nb);
-        tc.m_blk = (tc.m_blk + p.comm.rank * (mb / p.comm.size)) % mb;
+        const int n = p.comm.size;
+        const int per_owner = (mb / n) * nb;
+        const int o = t / per_owner;
+        TileCoord tc = raster(t - o * per_owner, mb / n, nb);
+        tc.m_blk += ((p.comm.rank + o) % n) * (mb / n);
         return tc;
     }
 
@@ -114,8 +119,10 @@ struct AgMPolicy : PlainPolicy {
         ptx::tma_store_commit();
         const long long next = st.base + stride;
         int done = (int)min((long long)st.m_blocks, next / per_blk);
-        constexpr int GRANULE = 16;
-        done = (done / GRANULE) * GRANULE;
+        // flags go out per group of m-blocks (each costs a system-scope fence); a rank's share is only M/n rows
+        // here, so small shares use a finer grain than the K-gather's 16
+        const int granule = st.m_blocks >= 32 ? 16 : 4;
+        done = (done / granule) * granule;
         if (next >= total) done = st.m_blocks;
         st.base = next;
         if (done <= st.flagged) return true;
