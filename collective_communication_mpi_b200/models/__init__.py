@@ -1,1 +1,2 @@
-from .fc_stack import MLPStack, TrainStep, TransformerFCBlock, TransformerFCBlockSP  # noqa: F401
+from .fc_stack import (MLPStack, TrainStep, TransformerFCBlock, TransformerFCBlockMegatron,  # noqa: F401
+                       TransformerFCBlockSP)

@@ -78,6 +78,34 @@ class TransformerFCBlockSP(nn.Module):
         return h + self.fc2(u)
 
 
+class TransformerFCBlockMegatron(nn.Module):
+    """The same block in the classic Megatron layout (``parallel/megatron_layers.py``): the residual stream
+    ``[tokens, hidden]`` is replicated on every model-parallel rank; each column/row pair ends in a GEMM fused
+    with an all-reduce. Note that with replicated outputs every rank computes the same loss on the same data."""
+
+    def __init__(self, mp_comm, tokens: int, hidden: int, ffn_mult: int = 4, *, seed: int = 0):
+        super().__init__()
+        from ..parallel.megatron_layers import MegatronColumnParallelLinear, MegatronRowParallelLinear
+        self.hidden, self.mp = hidden, mp_comm.Get_size()
+        self.fc_qkv = MegatronColumnParallelLinear(mp_comm, tokens, hidden, 3 * hidden, seed=seed + 1)
+        self.fc_o = MegatronRowParallelLinear(mp_comm, tokens, hidden, hidden, seed=seed + 2)
+        self.fc1 = MegatronColumnParallelLinear(mp_comm, tokens, hidden, ffn_mult * hidden, seed=seed + 3)
+        self.fc2 = MegatronRowParallelLinear(mp_comm, tokens, ffn_mult * hidden, hidden, seed=seed + 4)
+        self.fused_elementwise = EW.enabled()
+
+    def tp_layers(self) -> List[nn.Module]:
+        return [self.fc_qkv, self.fc_o, self.fc1, self.fc2]
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if self.fused_elementwise:
+            h = x + self.fc_o(EW.gate(self.fc_qkv(x)))
+            return h + self.fc2(EW.gelu(self.fc1(h)))
+        q, k, v = self.fc_qkv(x).chunk(3, dim=-1)
+        h = x + self.fc_o(v * torch.sigmoid(q * k))
+        u = torch.nn.functional.gelu(self.fc1(h), approximate="tanh")
+        return h + self.fc2(u)
+
+
 class MLPStack(nn.Module):
     def __init__(self, mp_comm, tokens: int, width: int, depth: int, *, seed: int = 0):
         super().__init__()

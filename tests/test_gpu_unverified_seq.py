@@ -144,3 +144,14 @@ def test_sequence_parallel_block_matches_dense_model(mp, dp):
     proc = run_ranks(mp * dp, ["tests/workers/w_layers.py", str(mp), str(dp), "--sp"], transport="device")
     assert proc.returncode == 0, f"rc={proc.returncode}\n{proc.stdout[-3000:]}\n{proc.stderr[-3000:]}"
     assert f"LAYERS OK mp={mp} dp={dp} sp=1" in proc.stdout
+
+
+@pytest.mark.parametrize("mp,dp", [(2, 1), (2, 2), (8, 1)])
+def test_megatron_layout_block_matches_dense_model(mp, dp):
+    """Layers built from hardware-verified ops (plain GEMM, GEMM -> all-reduce) but not yet run themselves."""
+    from conftest import gpu_count, run_ranks
+    if gpu_count() < mp * dp:
+        pytest.skip(f"needs {mp * dp} GPUs")
+    proc = run_ranks(mp * dp, ["tests/workers/w_layers.py", str(mp), str(dp), "--megatron"], transport="device")
+    assert proc.returncode == 0, f"rc={proc.returncode}\n{proc.stdout[-3000:]}\n{proc.stderr[-3000:]}"
+    assert f"LAYERS OK mp={mp} dp={dp} sp=0 megatron=1" in proc.stdout

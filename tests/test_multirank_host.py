@@ -157,3 +157,10 @@ def test_sequence_parallel_block_matches_dense_model_on_cpu(mp, dp, env):
     """Megatron-SP layout (parallel/sp_layers.py): token-sharded activations outside the GEMM pairs."""
     _ok(run_ranks(mp * dp, ["tests/workers/w_layers.py", str(mp), str(dp), "--sp"], timeout=240, env=env),
         f"LAYERS OK mp={mp} dp={dp} sp=1")
+
+
+@pytest.mark.parametrize("mp,dp", [(2, 2), (4, 1)])
+def test_megatron_layout_block_matches_dense_model_on_cpu(mp, dp):
+    """Classic Megatron layout (parallel/megatron_layers.py): replicated activations, GEMM -> all-reduce."""
+    _ok(run_ranks(mp * dp, ["tests/workers/w_layers.py", str(mp), str(dp), "--megatron"], timeout=240),
+        f"LAYERS OK mp={mp} dp={dp} sp=0 megatron=1")
