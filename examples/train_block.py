@@ -18,7 +18,8 @@ import torch  # noqa: E402
 from mpi4py import MPI  # noqa: E402
 from data.data_parallel_preprocess import split_data  # noqa: E402
 from model.func_impl import get_info  # noqa: E402
-from collective_communication_mpi_b200.models import TrainStep, TransformerFCBlock, TransformerFCBlockSP  # noqa: E402
+from collective_communication_mpi_b200.models import (TrainStep, TransformerFCBlock, TransformerFCBlockMegatron,  # noqa: E402
+                                                      TransformerFCBlockSP)
 
 
 def main():
@@ -28,6 +29,7 @@ def main():
     ap.add_argument("--tokens", type=int, default=256, help="tokens per replica and step")
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--sp", action="store_true", help="sequence-parallel layout: each rank holds tokens/mp rows of the full width")
+    ap.add_argument("--megatron", action="store_true", help="classic Megatron layout: activations replicated across the mp group")
     ap.add_argument("--lr", type=float, default=10.0, help="plain SGD on a mean-squared error: gradients are tiny")
     args = ap.parse_args()
 
@@ -43,7 +45,7 @@ def main():
 
     mp_idx, dp_idx, mp_comm, dp_comm, _, _ = get_info(comm=comm, rank=rank, mp_size=args.mp, dp_size=dp, fc_layer="fc_q",
                                                       in_dim=args.hidden, out_dim=args.hidden)
-    block = TransformerFCBlockSP if args.sp else TransformerFCBlock
+    block = TransformerFCBlockSP if args.sp else TransformerFCBlockMegatron if args.megatron else TransformerFCBlock
     model = block(mp_comm, args.tokens, args.hidden, ffn_mult=4, seed=1)
     step = TrainStep(model, dp_comm, lr=args.lr)
 
@@ -53,7 +55,9 @@ def main():
     X = torch.randn(dp * args.tokens, args.hidden, generator=g) * 0.5
     Y = torch.tanh(X.roll(1, dims=1)) * 0.5
     xs, ys = split_data(X, Y, mp_size=args.mp, dp_size=dp, rank=rank)
-    if args.sp:       # this rank's block of rows, all features
+    if args.megatron:  # every rank of the replica holds the whole batch
+        x, y = xs.contiguous().to(dev).bfloat16(), ys.contiguous().to(dev).bfloat16()
+    elif args.sp:     # this rank's block of rows, all features
         rows = args.tokens // args.mp
         x = xs[mp_idx * rows:(mp_idx + 1) * rows].contiguous().to(dev).bfloat16()
         y = ys[mp_idx * rows:(mp_idx + 1) * rows].contiguous().to(dev).bfloat16()
@@ -67,7 +71,7 @@ def main():
         local = float(step(x, y))
         losses.append(comm.allreduce(local, op=MPI.SUM) / world)      # mean over shards and replicas
     if rank == 0:
-        print(f"grid mp{args.mp} x dp{dp}{' (sequence-parallel)' if args.sp else ''} on {'GPU' if cuda else 'CPU'}: loss " + " -> ".join(f"{v:.4f}" for v in losses))
+        print(f"grid mp{args.mp} x dp{dp}{' (sequence-parallel)' if args.sp else ' (Megatron layout)' if args.megatron else ''} on {'GPU' if cuda else 'CPU'}: loss " + " -> ".join(f"{v:.4f}" for v in losses))
         print("TRAIN OK" if losses[-1] < losses[0] else "TRAIN DID NOT IMPROVE")
     comm.Barrier()
 
