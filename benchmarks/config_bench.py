@@ -25,6 +25,11 @@ CONFIGS = {
     "tp8": dict(model="block", hidden=8192, ffn=4, tokens=8192, mp="all"),
     "tp24": dict(model="block", hidden=4096, ffn=4, tokens=8192, mp=2),
     "dp8": dict(model="mlp", hidden=8192, depth=16, tokens=4096, mp=1),
+    # the same block in the other two activation layouts (ours only; kernels / layers not yet run on hardware)
+    "tp8sp": dict(model="block_sp", hidden=8192, ffn=4, tokens=8192, mp="all"),
+    "tp8meg": dict(model="block_megatron", hidden=8192, ffn=4, tokens=8192, mp="all"),
+    "tp24sp": dict(model="block_sp", hidden=4096, ffn=4, tokens=8192, mp=2),
+    "tp24meg": dict(model="block_megatron", hidden=4096, ffn=4, tokens=8192, mp=2),
 }
 
 
@@ -86,23 +91,27 @@ def main():
     mp_idx, dp_idx, mp_comm, dp_comm, _, _ = get_info(comm=comm, rank=rank, mp_size=mp, dp_size=dp, fc_layer="fc_q",
                                                       in_dim=H, out_dim=H)
     if args.impl == "ours":
-        from collective_communication_mpi_b200.models import MLPStack, TrainStep, TransformerFCBlock
-        model = TransformerFCBlock(mp_comm, tokens, H, cfg["ffn"], seed=1) if cfg["model"] == "block" else \
-            MLPStack(mp_comm, tokens, H, cfg["depth"], seed=1)
-        step = TrainStep(model, dp_comm, lr=1e-4)
+        from collective_communication_mpi_b200 import models as Mo
+        blocks = {"block": Mo.TransformerFCBlock, "block_sp": Mo.TransformerFCBlockSP, "block_megatron": Mo.TransformerFCBlockMegatron}
+        model = blocks[cfg["model"]](mp_comm, tokens, H, cfg["ffn"], seed=1) if cfg["model"] in blocks else \
+            Mo.MLPStack(mp_comm, tokens, H, cfg["depth"], seed=1)
+        step = Mo.TrainStep(model, dp_comm, lr=1e-4)
     else:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("MASTER_PORT", "29541")
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", torch.cuda.current_device()))
+        if cfg["model"] != "mlp" and cfg["model"] != "block":
+            raise SystemExit(f"config {args.config} has no NCCL arm: compare with tp8 / tp24 --impl nccl")
         if cfg["model"] == "block":
             from nccl_baseline import NcclTrainStep
             step = NcclTrainStep(rank, world, mp, dp, tokens, H, cfg["ffn"], lr=1e-4)
         else:
             step = NcclMLPStep(rank, world, H, cfg["depth"], 1e-4)
-    shard = H // mp
-    xs = [(torch.randn(tokens, shard, device="cuda") * 0.5).bfloat16() for _ in range(2)]
-    ts = [(torch.randn(tokens, shard, device="cuda") * 0.5).bfloat16() for _ in range(2)]
+    # input shard per rank: features (reference layout), rows (sequence parallel) or everything (Megatron)
+    shape = {"block_sp": (tokens // mp, H), "block_megatron": (tokens, H)}.get(cfg["model"], (tokens, H // mp))
+    xs = [(torch.randn(*shape, device="cuda") * 0.5).bfloat16() for _ in range(2)]
+    ts = [(torch.randn(*shape, device="cuda") * 0.5).bfloat16() for _ in range(2)]
     for i in range(max(3, args.warmup)):
         step(xs[i & 1], ts[i & 1])
     torch.cuda.synchronize(); comm.Barrier(); torch.cuda.synchronize()
@@ -114,7 +123,7 @@ def main():
     e1.record()
     torch.cuda.synchronize(); comm.Barrier()
     ms = max(comm.allgather(e0.elapsed_time(e1))) / args.steps
-    if cfg["model"] == "block":
+    if cfg["model"].startswith("block"):
         flops = 3 * 2 * tokens * (H * 3 * H + H * H + 2 * H * cfg["ffn"] * H) * dp
         params = (H * 3 * H + H * H + 2 * H * cfg["ffn"] * H)
     else:
