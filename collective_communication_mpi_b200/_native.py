@@ -166,6 +166,8 @@ def _declare_device(lib):
         "ccmpi_gate_bwd": (i, [vp, ll, vp, ll, vp, ll, i, i, vp]),
         "ccmpi_gelu_fwd": (i, [vp, vp, ll, vp]),
         "ccmpi_gelu_bwd": (i, [vp, vp, vp, ll, vp]),
+        "ccmpi_reduce_scatter_tight": (i, [P(DevComm), i, i, i, sz, sz, sz, sz, sz, sz, i, vp]),
+        "ccmpi_allreduce_twoshot_tight": (i, [P(DevComm), i, i, i, sz, sz, sz, sz, f, i, vp]),
         "ccmpi_gemm_sgd_bf16": (i, [vp, vp, vp, i, i, i, i, i, i, i, i, f, i, vp]),
         "ccmpi_gemm_mxfp8": (i, [vp, vp, vp, vp, vp, i, i, i, i, i, i, i, i, vp]),
         "ccmpi_mse_workspace_bytes": (sz, []),

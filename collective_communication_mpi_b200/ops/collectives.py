@@ -11,6 +11,7 @@ Reference call sites these replace: comm.py:16 (Barrier), :22 (Allreduce), :29 (
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Sequence
 
 import torch
@@ -60,9 +61,22 @@ def barrier(comms, stream=None):
     N.count_launch()
 
 
+def _tight(flag) -> bool:
+    """Group-size-specialised reduction kernels (csrc/collectives_tight.cu): opt-in, not yet measured."""
+    return os.environ.get("CCMPI_COLL_TIGHT") == "1" if flag is None else bool(flag)
+
+
 def allreduce(comms, dtype: int, op: int, src_off: int, dst_off: int, count: int, *, tmp_off: int = 0,
-              algo: int = N.AR_AUTO, scale: float = 1.0, out_dtype: int = -1, max_blocks: int = 0, stream=None):
+              algo: int = N.AR_AUTO, scale: float = 1.0, out_dtype: int = -1, max_blocks: int = 0, stream=None,
+              tight=None):
     a, n = _arr(comms)
+    if algo == N.AR_TWOSHOT and out_dtype in (-1, dtype) and _tight(tight):
+        rc = N.device_lib().ccmpi_allreduce_twoshot_tight(a, n, dtype, op, src_off, dst_off, tmp_off, count,
+                                                          C.c_float(scale), max_blocks, _sp(stream))
+        if rc != N.ERR_UNSUPPORTED:
+            N.check(rc, "ccmpi_allreduce_twoshot_tight")
+            N.count_launch()
+            return
     N.check(N.device_lib().ccmpi_allreduce(a, n, algo, dtype, op, src_off, dst_off, tmp_off, count,
                                            C.c_float(scale), out_dtype, max_blocks, _sp(stream)), "ccmpi_allreduce")
     N.count_launch()
@@ -78,8 +92,15 @@ def allgather(comms, src_off: int, dst_off: int, rows: int, row_bytes: int, src_
 
 def reduce_scatter(comms, dtype: int, op: int, src_off: int, dst_off: int, rows: int, row_elems: int,
                    src_row_stride: int, dst_row_stride: int, *, use_mc: bool = True, max_blocks: int = 0,
-                   stream=None):
+                   stream=None, tight=None):
     a, n = _arr(comms)
+    if _tight(tight) and (not use_mc or comms[0].size <= 2 or tight):
+        rc = N.device_lib().ccmpi_reduce_scatter_tight(a, n, dtype, op, src_off, dst_off, rows, row_elems, src_row_stride,
+                                                       dst_row_stride, max_blocks, _sp(stream))
+        if rc != N.ERR_UNSUPPORTED:
+            N.check(rc, "ccmpi_reduce_scatter_tight")
+            N.count_launch()
+            return
     N.check(N.device_lib().ccmpi_reduce_scatter(a, n, dtype, op, src_off, dst_off, rows, row_elems,
                                                 src_row_stride, dst_row_stride, int(use_mc), max_blocks,
                                                 _sp(stream)), "ccmpi_reduce_scatter")

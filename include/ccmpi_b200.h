@@ -244,6 +244,16 @@ size_t ccmpi_mse_workspace_bytes(void);
 int ccmpi_mse_fwd_bwd(const void* y, const void* t, void* dy, long long n, void* workspace, void* loss,
                       void* stream);
 
+/* EXPERIMENTAL (compiled, not yet run or measured in round 1): the pull-style reduce-scatter and the two-shot
+ * all-reduce with their in-flight buffers sized by the communicator (2 / 4 / 8 members) instead of for 8
+ * (csrc/collectives_tight.cu). fp32 / bf16, SUM / MIN / MAX, 16-byte aligned operands; anything else returns
+ * CCMPI_ERR_UNSUPPORTED. Results are bit-identical to ccmpi_reduce_scatter / ccmpi_allreduce(CCMPI_AR_TWOSHOT). */
+int ccmpi_reduce_scatter_tight(const ccmpi_dev_comm* comms, int nvr, int dtype, int op, size_t src_off, size_t dst_off,
+                               size_t rows, size_t row_elems, size_t src_row_stride, size_t dst_row_stride,
+                               int max_blocks, void* stream);
+int ccmpi_allreduce_twoshot_tight(const ccmpi_dev_comm* comms, int nvr, int dtype, int op, size_t src_off, size_t dst_off,
+                                  size_t tmp_off, size_t count, float scale, int max_blocks, void* stream);
+
 /* EXPERIMENTAL (compiled, not yet run on hardware in round 1): weight-gradient GEMM with the SGD
  * update in its epilogue, W[M][N] -= lr * (A * B), bf16 W updated in place from the fp32
  * accumulator (csrc/gemm_sgd.cu). For layers whose gradient needs no data-parallel reduction.

@@ -17,9 +17,10 @@ run() {   # run <label> <timeout> <command...>
     echo "[$label] rc=$rc  $(tail -1 "$log")" | tee -a "$OUT"
 }
 run regular_suite 900 python -m pytest tests -x -q -m gpu --deselect tests/test_gpu_unverified_fp8.py \
-    --deselect tests/test_gpu_unverified_seq.py --deselect tests/test_gpu_unverified_elementwise.py --deselect tests/test_gpu_unverified_p2p.py --deselect tests/test_gpu_unverified_sgd.py --deselect tests/test_gpu_unverified_graphs.py
+    --deselect tests/test_gpu_unverified_seq.py --deselect tests/test_gpu_unverified_elementwise.py --deselect tests/test_gpu_unverified_p2p.py --deselect tests/test_gpu_unverified_sgd.py --deselect tests/test_gpu_unverified_graphs.py --deselect tests/test_gpu_unverified_tight.py
 run utils        120 python -m pytest tests/test_gpu_utils.py -x -q
 run elementwise  300 python -m pytest tests/test_gpu_unverified_elementwise.py -q
+run tight        300 python -m pytest tests/test_gpu_unverified_tight.py -q
 run graphs       120 python -m pytest tests/test_gpu_unverified_graphs.py -q
 run sgd          300 python -m pytest tests/test_gpu_unverified_sgd.py -q
 run fp8          300 python -m pytest tests/test_gpu_unverified_fp8.py -q
