@@ -37,6 +37,8 @@ CCMPI_FUSED_ELEMENTWISE=0 run bench_eager 300 python bench.py --steps 10 --warmu
 CCMPI_FUSED_ELEMENTWISE=1 run bench_fused 300 python bench.py --steps 10 --warmup 3
 CCMPI_FUSED_ELEMENTWISE=1 CCMPI_FUSED_SGD=1 run bench_fused_sgd 300 python bench.py --steps 10 --warmup 3
 if [ "$NG" -ge 2 ]; then
+    run sweep_tight 600 python -m collective_communication_mpi_b200.launch -n "$NG" --transport device python benchmarks/sweep.py --tight --no-nccl --min-kb 1024 --max-mb 256
+    run seq_bench 600 python -m collective_communication_mpi_b200.launch -n "$NG" --transport device python benchmarks/seq_bench.py
     # end-to-end (H2D-bound at N >= 4 in round 1): does running each rank next to its GPU help?
     P=29600
     for bind in 0 1; do
