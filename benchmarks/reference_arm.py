@@ -12,9 +12,17 @@ or engine is on the path -- with one unavoidable exception that is reported in t
 ``from mpi4py import MPI`` inside the reference resolves to this repository's shared-memory
 stand-in (host transport; CCMPI_TRANSPORT=host is forced so no GPU kernel runs).
 
-If no reference install is present, or one step would make the run exceed the wall budget
-(CCMPI_REF_BUDGET_S, default 1500 s), a single ``{"impl": "reference", "unavailable": ...}`` line is
-printed and the exit code is 0, as the task statement prescribes.
+``baseline/_ref`` is tracked in git (the box that runs this arm has no ``/root/reference``); if it is
+missing anyway and ``/root/reference`` exists, ``scripts/install_reference.sh`` is run first. If there
+is no reference at all, a single ``{"impl": "reference", "unavailable": ...}`` line is printed and the
+exit code is 0, as the task statement prescribes.
+
+Wall budget: one CPU step of this configuration takes tens of seconds (54 s on 8 cores, measured), so
+the requested ``--warmup W --steps K`` may not fit the caller's time limit. The first step is timed;
+when ``(W + K)`` steps would exceed ``CCMPI_REF_BUDGET_S`` (default 780 s) the arm runs as many as
+fit (never fewer than 1 warm-up + 1 timed step), reports the counts it really ran in ``steps`` /
+``warmup`` and says so in ``note``. Per-step time on the CPU is stable to a few per cent, so the
+tokens/s of a shortened run is the same measurement with a wider error bar, not a different one.
 """
 from __future__ import annotations
 
@@ -26,12 +34,23 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def run_reference(args, emit, grid_for, cfg):
+    t_start = time.perf_counter()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     ref_root = os.path.join(ROOT, "baseline", "_ref")
     if not os.path.isfile(os.path.join(ref_root, "model", "func_impl.py")):
+        # not expected (the tree is tracked); a checkout that lost it can still rebuild it from /root/reference
+        import subprocess
+        if rank == 0 and os.path.isdir("/root/reference"):
+            subprocess.run(["bash", os.path.join(ROOT, "scripts", "install_reference.sh")], stdout=subprocess.DEVNULL,
+                           stderr=subprocess.DEVNULL, check=False)
+        for _ in range(120):        # other ranks wait for rank 0's install (no communicator exists yet)
+            if os.path.isfile(os.path.join(ref_root, "mpi-test.py")) or not os.path.isdir("/root/reference"):
+                break
+            time.sleep(0.5)
+    if not os.path.isfile(os.path.join(ref_root, "model", "func_impl.py")):
         if rank == 0:
-            emit({"impl": "reference", "unavailable": "baseline/_ref is missing (run scripts/install_reference.sh)"})
+            emit({"impl": "reference", "unavailable": "baseline/_ref is missing and /root/reference does not exist here"})
         return
     if world != args.gpus:
         if rank == 0:
@@ -132,32 +151,37 @@ def run_reference(args, emit, grid_for, cfg):
     comm.Barrier()
     first = time.perf_counter() - t0
     first = max(comm.allgather(first))
-    budget = float(os.environ.get("CCMPI_REF_BUDGET_S", "1500"))
-    warm = max(3, args.warmup)
-    if first * (warm + args.steps) > budget:
-        if rank == 0:
-            emit({"impl": "reference", "unavailable": f"one CPU step takes {first:.1f} s on {threads} threads/rank; "
-                  f"{warm}+{args.steps} steps would exceed the {budget:.0f} s budget (CCMPI_REF_BUDGET_S)",
-                  "metric": cfg["metric"], "n_gpus": world, "seconds_per_step_measured_once": round(first, 2),
-                  "tokens_per_s_from_one_step": round(tokens * dp / first, 1)})
-        return
+    budget = float(os.environ.get("CCMPI_REF_BUDGET_S", "780"))
+    warm, steps, note = max(3, args.warmup), args.steps, None
+    fit = int((budget - (time.perf_counter() - t_start)) / (first * 1.05))     # steps that still fit, first one excluded
+    if (warm - 1) + steps > fit:
+        warm = max(1, min(warm, 1 + (fit - 1) // 4))        # keep about a fifth of the run as warm-up
+        steps = max(1, min(steps, fit - (warm - 1)))
+        note = (f"one CPU step takes {first:.1f} s on {threads} threads/rank: the requested {max(3, args.warmup)}+{args.steps} "
+                f"steps do not fit the {budget:.0f} s wall budget (CCMPI_REF_BUDGET_S); ran {warm}+{steps}")
     for _ in range(warm - 1):
         step()
     comm.Barrier()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
+    for _ in range(steps):
         step()
     comm.Barrier()
     el = max(comm.allgather(time.perf_counter() - t0))
     if rank == 0:
-        val = tokens * dp * args.steps / el
+        val = tokens * dp * steps / el
+        ms = round(el / steps * 1e3, 2)
         emit({"impl": "reference", "metric": cfg["metric"], "value": round(val, 1), "unit": "tokens/s", "n_gpus": world,
-              "steps": args.steps, "warmup": warm, "ms_per_step": round(el / args.steps * 1e3, 2), "higher_is_better": True,
+              "steps": steps, "warmup": warm, "ms_per_step": ms, "higher_is_better": True, **({"note": note} if note else {}),
               "scaling": "weak", "vs_baseline": None, "dtype": "fp32 (NumPy on CPU; the reference has no GPU or bf16 path)",
               "data": "synthetic",
-              "config": {"model": "transformer FC layers fc_q/k/v/o + fc1/fc2, hidden 4096, ffn 4x (random init)",
+              "config": {"model": f"transformer FC layers fc_q/k/v/o + fc1/fc2, hidden {H}, ffn {cfg['ffn_mult']}x (random init)",
                          "global_batch": cfg["seqs"] * dp, "seq_len": cfg["seq"], "parallelism": f"mp{mp}xdp{dp}",
                          "threads_per_rank": threads},
               "mpi_runtime": "in-repo shared-memory stand-in for mpi4py (no MPI on the image); reference code unmodified",
-              "e2e": {"value": round(val, 1), "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+              # the reference never leaves the host: its end-to-end step IS its step (inputs are NumPy arrays in
+              # host memory, the loss is a Python float), so no copies are declared
+              "e2e": {"value": round(val, 1), "unit": "tokens/s", "ms_per_step": ms, "h2d_bytes_per_step": 0,
+                      "d2h_bytes_per_step": 0, "note": "CPU-resident: no host<->device copies exist on this arm"},
+              "native_libs_mapped": sorted({os.path.basename(l.split()[-1]) for l in open("/proc/self/maps")
+                                            if "libccmpi" in l}),
               "gpu_launches": 0})

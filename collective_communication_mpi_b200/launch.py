@@ -40,6 +40,7 @@ def launch(nprocs: int, cmd, *, tag_output: bool = False, env_extra=None, timeou
     procs = []
     outputs = [[] for _ in range(nprocs)]
     threads = []
+    out_lock = threading.Lock()
     repo_root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     for r in range(nprocs):
         env = dict(os.environ)
@@ -55,18 +56,23 @@ def launch(nprocs: int, cmd, *, tag_output: bool = False, env_extra=None, timeou
             env.setdefault("OMP_NUM_THREADS", str(max(1, (os.cpu_count() or 1) // nprocs)))
         if env_extra:
             env.update(env_extra)
-        pipe = subprocess.PIPE if (tag_output or capture) else None
-        p = subprocess.Popen(cmd, env=env, stdout=pipe, stderr=subprocess.STDOUT if pipe else None, text=True,
-                             start_new_session=True)
+        # every rank's stdout / stderr comes through a pipe and is forwarded one whole line at a time
+        # under a lock (what mpirun's I/O forwarding does): ranks that print at the same moment cannot
+        # splice their lines into each other, which they do when N children share the terminal directly
+        p = subprocess.Popen(cmd, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True,
+                             start_new_session=True, errors="replace")
         procs.append(p)
-        if pipe:
-            def pump(proc=p, rank=r):
-                for line in proc.stdout:
+
+        def pump(src, dst, rank=r, keep=True):
+            for line in src:
+                if keep:
                     outputs[rank].append(line)
-                    if not capture or tag_output:
-                        sys.stdout.write(f"[{rank}] {line}" if tag_output else line)
-                        sys.stdout.flush()
-            t = threading.Thread(target=pump, daemon=True)
+                if not capture or tag_output:
+                    with out_lock:
+                        dst.write(f"[{rank}] {line}" if tag_output else line)
+                        dst.flush()
+        for src, dst, keep in ((p.stdout, sys.stdout, True), (p.stderr, sys.stderr, capture)):
+            t = threading.Thread(target=pump, args=(src, dst), kwargs={"keep": keep}, daemon=True)
             t.start()
             threads.append(t)
 

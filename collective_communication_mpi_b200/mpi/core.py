@@ -210,6 +210,43 @@ class _DeviceSide:
         self.comm = make_dev_comm(heap, heap_members, me if not heap.emulated else 0, cid, mc)
         self.has_mc = bool(mc)
         self.comms = [self.comm]
+        self._members, self._me, self._cid = list(members), me, cid
+        self._members_c = (C.c_int * len(members))(*members)
+        self._route_send = np.zeros(2, dtype=np.int64)
+        self._route_recv = np.zeros(2 * len(members), dtype=np.int64)
+        self.alias = (False, False)
+
+    def agree(self, s: "_Buf", r: "_Buf"):
+        """Host-plane rendezvous in front of every front-end device collective. It does two jobs.
+
+        (1) Zero-copy routing. A kernel applies ONE heap offset to every member
+        (``heap[p] + off``), so an operand may be used in place only when every member passed a
+        tensor at the SAME offset of the symmetric heap. Each member reports the offset of its
+        send / receive tensor (-1: not in the heap, or misaligned) and the in-place route is taken
+        only if all reports are equal; otherwise everybody stages through the arena. A
+        rank-dependent slice of a symmetric tensor, or a symmetric tensor on one rank and an
+        ordinary one on another, therefore costs a copy instead of corrupting a peer's heap.
+
+        (2) Skew. MPI lets ranks reach a collective arbitrarily far apart; the device kernels'
+        watchdog is for GPU-side faults. Meeting on the host first (the host plane waits
+        ``CCMPI_TIMEOUT`` seconds, like any MPI) leaves the device wait only GPU-side skew."""
+        n = len(self._members)
+        if n == 1 or self.heap.emulated:
+            self.alias = (False, False)
+            return
+
+        def base(b):
+            if not b.cuda:
+                return -1
+            off = self.heap.offset_of(b.flat)
+            return off if off is not None and off % 16 == 0 else -1
+        self._route_send[0], self._route_send[1] = base(s), base(r)
+        w = self.world
+        N.check_host(w._hostlib.ccmpi_host_allgather(w.host, self._cid, self._members_c, n, self._me,
+                                                     self._route_send.ctypes.data, self._route_recv.ctypes.data, 16),
+                     "device-collective rendezvous")
+        got = self._route_recv.reshape(n, 2)
+        self.alias = tuple(bool(got[0, k] >= 0 and (got[:, k] == got[0, k]).all()) for k in (0, 1))
 
 
 class Comm:
@@ -347,18 +384,22 @@ class Comm:
         w = self._world
         if color is None:
             color = UNDEFINED
-        info = w.host_allgather_obj(self._cid, self._members, self._me, (int(color), int(key), w.next_comm_id)) \
-            if len(self._members) > 1 else [(int(color), int(key), w.next_comm_id)]
-        ck = tuple((c, k) for c, k, _ in info)
+        multi = len(self._members) > 1
+        info = w.host_allgather_obj(self._cid, self._members, self._me, (int(color), int(key))) if multi \
+            else [(int(color), int(key))]
+        ck = tuple(info)
         hit = self._split_cache.get(ck)
         if hit is not None or ck in self._split_cache:
             return hit
-        colors = sorted({c for c, _, _ in info if c != UNDEFINED})
-        base = w.reserve_comm_ids([nx for _, _, nx in info], len(colors))
+        colors = sorted({c for c, _ in info if c != UNDEFINED})
+        # group rank 0 draws the ids from the job-wide counter and tells the rest (second small exchange)
+        base = w.reserve_comm_ids(len(colors)) if self._me == 0 else None
+        if multi:
+            base = w.host_allgather_obj(self._cid, self._members, self._me, base)[0]
         if color == UNDEFINED:
             self._split_cache[ck] = None
             return None
-        order = sorted((k, pr) for pr, (c, k, _) in enumerate(info) if c == color)
+        order = sorted((k, pr) for pr, (c, k) in enumerate(info) if c == color)
         members = [self._members[pr] for _, pr in order]
         me = [pr for _, pr in order].index(self._me)
         cid = base + colors.index(color)
@@ -778,9 +819,8 @@ def _stage_in(dev: _DeviceSide, b: _Buf, off: int, byte_lo: int, nbytes: int):
     import torch
     heap = dev.heap
     if b.cuda:
-        base = heap.offset_of(b.flat)
-        if base is not None and (base + byte_lo) % 16 == 0:
-            return base + byte_lo  # already symmetric: zero-copy
+        if dev.alias[0] and byte_lo % 16 == 0:
+            return heap.offset_of(b.flat) + byte_lo  # symmetric at the same offset on every member: zero-copy
         heap.view(off, (nbytes,), torch.uint8).copy_(b.flat.view(torch.uint8)[byte_lo:byte_lo + nbytes], non_blocking=True)
         return off
     src = torch.from_numpy(b.flat.view(np.uint8)[byte_lo:byte_lo + nbytes])
@@ -792,8 +832,7 @@ def _stage_out(dev: _DeviceSide, b: _Buf, off: int, byte_lo: int, nbytes: int):
     import torch
     heap = dev.heap
     if b.cuda:
-        base = heap.offset_of(b.flat)
-        if base is not None and base + byte_lo == off:
+        if dev.alias[1] and heap.offset_of(b.flat) + byte_lo == off:
             return
         b.flat.view(torch.uint8)[byte_lo:byte_lo + nbytes].copy_(heap.view(off, (nbytes,), torch.uint8), non_blocking=True)
         return
@@ -803,10 +842,8 @@ def _stage_out(dev: _DeviceSide, b: _Buf, off: int, byte_lo: int, nbytes: int):
 
 def _out_offset(dev: _DeviceSide, b: _Buf, fallback: int, byte_lo: int) -> int:
     """Kernels write results straight into the user's tensor when it lives in the heap."""
-    if b.cuda:
-        base = dev.heap.offset_of(b.flat)
-        if base is not None and (base + byte_lo) % 16 == 0:
-            return base + byte_lo
+    if b.cuda and dev.alias[1] and byte_lo % 16 == 0:
+        return dev.heap.offset_of(b.flat) + byte_lo
     return fallback
 
 
@@ -817,6 +854,7 @@ def _finish(r: _Buf):
 
 
 def _dev_allreduce(dev: _DeviceSide, s: _Buf, r: _Buf, op: int):
+    dev.agree(s, r)
     from ..ops import collectives as CO
     sin, sout, stmp, cap = _DeviceSide.STAGE
     es = s.itemsize
@@ -831,6 +869,7 @@ def _dev_allreduce(dev: _DeviceSide, s: _Buf, r: _Buf, op: int):
 
 
 def _dev_allgather(dev: _DeviceSide, s: _Buf, r: _Buf, n: int):
+    dev.agree(s, r)
     from ..ops import collectives as CO
     sin, sout, _, cap = _DeviceSide.STAGE
     step = max(16, (cap // n) // 16 * 16)
@@ -849,6 +888,7 @@ def _dev_allgather(dev: _DeviceSide, s: _Buf, r: _Buf, n: int):
 
 
 def _dev_reduce_scatter(dev: _DeviceSide, s: _Buf, r: _Buf, n: int, op: int):
+    dev.agree(s, r)
     from ..ops import collectives as CO
     sin, sout, _, cap = _DeviceSide.STAGE
     es = s.itemsize
@@ -872,9 +912,13 @@ def _dev_reduce_scatter(dev: _DeviceSide, s: _Buf, r: _Buf, n: int, op: int):
 
 def _dev_allgather_rows(dev: _DeviceSide, s: _Buf, r: _Buf, n: int, rows: int, row_bytes: int):
     """Strided (last-axis) all-gather; row-chunked when it exceeds the staging arena."""
+    dev.agree(s, r)
     from ..ops import collectives as CO
     sin, sout, _, cap = _DeviceSide.STAGE
-    rows_per = max(1, cap // (row_bytes * n))
+    if row_bytes * n > cap:
+        raise ValueError(f"last-axis all-gather: one gathered row is {row_bytes * n} B, the staging arena holds {cap} B "
+                         "(raise CCMPI_STAGE_MB or gather symmetric tensors)")
+    rows_per = cap // (row_bytes * n)
     for r0 in range(0, rows, rows_per):
         nr = min(rows_per, rows - r0)
         src = _stage_in(dev, s, sin, r0 * row_bytes, nr * row_bytes)
@@ -885,11 +929,15 @@ def _dev_allgather_rows(dev: _DeviceSide, s: _Buf, r: _Buf, n: int, rows: int, r
 
 
 def _dev_reduce_scatter_rows(dev: _DeviceSide, s: _Buf, r: _Buf, n: int, rows: int, pcols: int, op: int):
+    dev.agree(s, r)
     from ..ops import collectives as CO
     sin, sout, _, cap = _DeviceSide.STAGE
     es = s.itemsize
     in_row = pcols * n * es
-    rows_per = max(1, cap // in_row)
+    if in_row > cap:
+        raise ValueError(f"last-axis reduce-scatter: one input row is {in_row} B, the staging arena holds {cap} B "
+                         "(raise CCMPI_STAGE_MB or pass symmetric tensors)")
+    rows_per = cap // in_row
     for r0 in range(0, rows, rows_per):
         nr = min(rows_per, rows - r0)
         src = _stage_in(dev, s, sin, r0 * in_row, nr * in_row)
@@ -907,6 +955,7 @@ def _stage_in_at(dev: _DeviceSide, b: _Buf, off: int, byte_lo: int, nbytes: int)
 
 
 def _dev_alltoall(dev: _DeviceSide, s: _Buf, r: _Buf, n: int, staggered: bool = False):
+    dev.agree(s, r)
     from ..ops import collectives as CO
     sin, sout, _, cap = _DeviceSide.STAGE
     seg = s.nbytes // n

@@ -199,15 +199,18 @@ class World:
         return int(lib.ccmpi_mc_ptr(self.heap.handle, g) or 0)
 
     # ---- communicator ids ---------------------------------------------------------------
-    def reserve_comm_ids(self, peers_next: List[int], ncolors: int) -> int:
-        """Given every parent member's next free id, pick the base id all of them will use."""
-        base = max(peers_next)
-        self._next_comm_id = base + ncolors
+    def reserve_comm_ids(self, count: int) -> int:
+        """``count`` fresh communicator ids from the job-wide counter in the shared segment (a
+        process-local counter when the job is a single process). Called by ONE member of the
+        parent communicator, which then tells the others: ids derived from the members' own
+        state would collide between groups that have no rank in common."""
+        if self.host is None:
+            base = self._next_comm_id
+            self._next_comm_id += count
+            return base
+        base = self._hostlib.ccmpi_host_reserve_comm_ids(self.host, count)
+        N.check_host(min(base, 0), "reserve_comm_ids")
         return base
-
-    @property
-    def next_comm_id(self) -> int:
-        return self._next_comm_id
 
     # ---- teardown -----------------------------------------------------------------------
     def close(self):

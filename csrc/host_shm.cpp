@@ -60,7 +60,7 @@ static_assert(sizeof(RingCtl) == 128, "ring control block layout");
 struct Header {
     std::atomic<uint64_t> magic;
     uint32_t nranks;
-    uint32_t reserved;
+    std::atomic<uint32_t> comm_ids;  // communicator ids handed out so far, job-wide (ccmpi_host_reserve_comm_ids)
     uint64_t stage_bytes;
     uint64_t ring_bytes;
     std::atomic<uint32_t> attached;
@@ -654,6 +654,22 @@ extern "C" int ccmpi_host_recv(int64_t h, int src, int comm_id, int tag, void* b
 // sender's symmetric heap; when the receiver has copied the payload out (over NVLink) it posts an
 // ack here and the sender may reuse the staging block. Counters only grow; messages of one pair
 // are consumed in send order, so a count identifies which blocks are free.
+// Communicator ids come from ONE job-wide counter: two groups that share no rank (the two halves of a
+// split, say) still split again at the same time, and ids picked from their own members' state alone
+// would collide -- and with them the barrier slot and the signal pad both index by id.
+extern "C" int ccmpi_host_reserve_comm_ids(int64_t h, int count) {
+    Handle* H = get(h);
+    if (!H) { set_error("bad handle"); return -1; }
+    if (count < 0) { set_error("reserve_comm_ids: count %d", count); return -2; }
+    // id 0 is the world; the counter stores ids in use beyond it
+    uint32_t base = 1 + H->hdr->comm_ids.fetch_add((uint32_t)count, std::memory_order_relaxed);
+    if (base + (uint32_t)count > CCMPI_HOST_MAX_COMMS) {
+        set_error("out of communicator ids (%d): reuse communicators instead of re-splitting", CCMPI_HOST_MAX_COMMS);
+        return -3;
+    }
+    return (int)base;
+}
+
 extern "C" int ccmpi_host_ack_post(int64_t h, int src) {
     Handle* H = get(h);
     if (!H || src < 0 || src >= H->nranks || src == H->rank) { set_error("ack_post: bad handle or peer %d", src); return -2; }

@@ -54,6 +54,10 @@ int ccmpi_host_waitall(int64_t h, const int64_t* reqs, int n);
 /* size of the next message queued from `src` (blocks until a header is there) */
 int64_t ccmpi_host_probe(int64_t h, int src);
 
+/* Reserve `count` consecutive communicator ids from the job-wide counter in the segment; returns the
+ * first one (>= 1; 0 is the world) or <0. One member of the parent calls this and tells the others. */
+int ccmpi_host_reserve_comm_ids(int64_t h, int count);
+
 /* Out-of-band completion counters, one per ordered pair of ranks (device point-to-point path: a
  * descriptor travels through the ring, the payload stays in the sender's symmetric heap until the
  * receiver has copied it over NVLink). ack_post: "I am done with one more message from `src`";

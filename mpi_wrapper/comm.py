@@ -171,6 +171,7 @@ def _my_allreduce_device(comm, s, r, op_code: int, algo: int):
     sin, sout, stmp, cap = dev.STAGE
     if algo == _N.AR_NVLS and not dev.has_mc:
         raise RuntimeError("algo='nvls' needs NVLS multicast, which this communicator does not have")
+    dev.agree(s, r)     # host rendezvous + "same heap offset on every member?" (zero-copy only then)
     es = s.itemsize
     step = cap // es * es
     for lo in range(0, s.nbytes, step):

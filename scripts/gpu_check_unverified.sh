@@ -48,3 +48,6 @@ if [ "$NG" -ge 2 ]; then
     done
 fi
 cat "$OUT"
+# how long one reference-arm CPU step takes on this box (sets the default wall budget of the arm)
+CCMPI_REF_BUDGET_S=${REF_PROBE_BUDGET_S:-70} run reference_arm 400 python bench.py --impl reference --gpus 1 --steps 2 --warmup 3
+nproc >> "$OUT"; cat "$OUT"

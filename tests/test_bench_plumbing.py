@@ -34,13 +34,15 @@ def test_reference_arm_emits_one_json_line(nproc):
     assert "shared-memory stand-in" in d["mpi_runtime"]
 
 
-def test_reference_arm_reports_unavailable_when_over_budget():
+def test_reference_arm_shortens_the_run_to_its_wall_budget_and_says_so():
     if not HAVE_REF:
         pytest.skip("baseline/_ref not installed")
-    p = _bench(["--impl", "reference", "--steps", "1000000", "--warmup", "1"], {"CCMPI_REF_BUDGET_S": "1"})
+    p = _bench(["--impl", "reference", "--steps", "1000000", "--warmup", "5"], {"CCMPI_REF_BUDGET_S": "1"})
     assert p.returncode == 0
     d = json.loads([l for l in p.stdout.splitlines() if l.startswith("{")][-1])
-    assert d["impl"] == "reference" and "unavailable" in d
+    assert d["impl"] == "reference" and "unavailable" not in d
+    assert 1 <= d["steps"] < 1000000 and d["warmup"] >= 1 and "wall budget" in d["note"]
+    assert d["value"] > 0 and d["e2e"]["ms_per_step"] == d["ms_per_step"]
 
 
 def test_launcher_exports_torchrun_style_environment():

@@ -164,3 +164,8 @@ def test_megatron_layout_block_matches_dense_model_on_cpu(mp, dp):
     """Classic Megatron layout (parallel/megatron_layers.py): replicated activations, GEMM -> all-reduce."""
     _ok(run_ranks(mp * dp, ["tests/workers/w_layers.py", str(mp), str(dp), "--megatron"], timeout=240),
         f"LAYERS OK mp={mp} dp={dp} sp=0 megatron=1")
+
+
+def test_sibling_groups_that_split_again_get_distinct_ids_and_do_not_disturb_each_other():
+    """Two halves of the world split at the same time: ids come from one job-wide counter."""
+    _ok(run_ranks(8, ["tests/workers/w_nested_split.py"], timeout=120), "NESTED SPLIT OK")
