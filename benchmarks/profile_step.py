@@ -47,7 +47,7 @@ if rank == 0:
     os.makedirs("gpurun_out", exist_ok=True)
     with open(f"gpurun_out/profile_{impl}_{world}gpu.txt", "w") as f:
         f.write(f"# {impl} {world} GPU: device time per step {tot/1000:.3f} ms (sum over kernels, profiler)\n")
-        for k, us, c in rows[:40]:
+        for k, us, c in rows[:60]:
             f.write(f"{us:10.1f} us  x{c:3d}  {k[:110]}\n")
     print(open(f"gpurun_out/profile_{impl}_{world}gpu.txt").read())
 if impl == "nccl":

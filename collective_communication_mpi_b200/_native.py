@@ -103,6 +103,25 @@ def host_lib():
         return lib
 
 
+_timeout_done = set()
+
+
+def apply_device_timeout(device: int, seconds: float = None) -> float:
+    """Set the watchdog budget of the device-side waits on ``device`` (once per device and process
+    unless ``seconds`` is given): ``CCMPI_DEVICE_TIMEOUT_S``, default 120 s -- the same default as the
+    host plane's ``CCMPI_TIMEOUT``. A rank may reach a collective long after its peers (data loading,
+    first-call module load, a debugger); the peers' kernels wait that long before they trap."""
+    if seconds is None:
+        if device in _timeout_done:
+            return -1.0
+        seconds = float(os.environ.get("CCMPI_DEVICE_TIMEOUT_S", "120"))
+    import torch
+    with torch.cuda.device(device):
+        check(device_lib().ccmpi_set_spin_timeout_ns(int(seconds * 1e9)), "ccmpi_set_spin_timeout_ns")
+    _timeout_done.add(device)
+    return seconds
+
+
 def check(rc: int, what: str = "") -> int:
     """Raise on a negative native status, with the library's own message."""
     if rc is not None and rc < 0:
@@ -124,6 +143,7 @@ def _declare_device(lib):
     sigs = {
         "ccmpi_last_error": (C.c_char_p, []),
         "ccmpi_version": (i, []),
+        "ccmpi_set_spin_timeout_ns": (i, [C.c_ulonglong]),
         "ccmpi_probe": (i, [i, P(C.c_int)]),
         "ccmpi_heap_create": (i64, [i, sz]),
         "ccmpi_heap_create_emulated": (i64, [i, sz, i]),

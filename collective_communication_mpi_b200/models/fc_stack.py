@@ -33,7 +33,7 @@ class TransformerFCBlock(nn.Module):
         self.fc_o = RowParallelLinear(mp_comm, tokens, hidden, hidden, seed=seed + 2, num_comm_ctas=num_comm_ctas)
         self.fc1 = ColumnParallelLinear(mp_comm, tokens, hidden, ffn_mult * hidden, seed=seed + 3, num_comm_ctas=num_comm_ctas)
         self.fc2 = RowParallelLinear(mp_comm, tokens, ffn_mult * hidden, hidden, seed=seed + 4, num_comm_ctas=num_comm_ctas)
-        # opt-in (CCMPI_FUSED_ELEMENTWISE=1): one-pass gate / GELU kernels with hand-written backward
+        # one-pass gate / GELU kernels with hand-written backward (CCMPI_FUSED_ELEMENTWISE=0: eager op chains)
         self.fused_elementwise = EW.enabled()
 
     def tp_layers(self) -> List[nn.Module]:
@@ -129,9 +129,9 @@ class TrainStep:
 
     def __init__(self, model, dp_comm, *, lr: float = 1e-3, bucket_mb: int = 64, overlap: bool = True):
         self.model, self.lr = model, lr
-        # opt-in (CCMPI_FUSED_SGD=1), only without data parallelism: every dW GEMM applies its own
-        # SGD step in the epilogue, so there is no gradient buffer, no reduction and no optimizer pass
-        self.fused_sgd = dp_comm.Get_size() == 1 and os.environ.get("CCMPI_FUSED_SGD") == "1"
+        # without data parallelism every dW GEMM applies its own SGD step in the epilogue: no gradient
+        # buffer, no reduction, no optimizer pass (CCMPI_FUSED_SGD=0 keeps them separate)
+        self.fused_sgd = dp_comm.Get_size() == 1 and os.environ.get("CCMPI_FUSED_SGD", "1") != "0"
         if self.fused_sgd:
             for layer in model.tp_layers():
                 layer.sgd_lr = lr

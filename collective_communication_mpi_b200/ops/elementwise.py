@@ -8,8 +8,9 @@ of the tests.
 CUDA tensors always go to the kernels (a missing library is an error, not a fallback). CPU tensors
 -- the CPU test-suite, documentation examples -- run the reference formulas.
 
-EXPERIMENTAL in round 1: compiled, not yet run on hardware; models use these ops only when
-``CCMPI_FUSED_ELEMENTWISE=1``.
+The models use these ops by default (``CCMPI_FUSED_ELEMENTWISE=0`` switches back to eager PyTorch op
+chains, which is what the NCCL + cuBLAS baseline arm runs). Measured on a B200
+(profiles/r2_extras_bench_1gpu.jsonl): gate fwd+bwd 4.5x, MSE loss+grad 7.7x the eager chains.
 """
 from __future__ import annotations
 
@@ -26,7 +27,7 @@ _A = 0.044715
 
 
 def enabled() -> bool:
-    return os.environ.get("CCMPI_FUSED_ELEMENTWISE", "0") == "1"
+    return os.environ.get("CCMPI_FUSED_ELEMENTWISE", "1") != "0"
 
 
 def _stream(stream=None) -> int:

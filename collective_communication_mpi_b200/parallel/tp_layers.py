@@ -60,7 +60,9 @@ class _ColumnFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy):
         (weight,) = ctx.saved_tensors
-        dx, dw = ctx.layer._bwd(dy.contiguous(), ctx.x_full, weight)
+        # the first layer of a model gets data, not activations: nobody wants d loss / d input, so the
+        # dx GEMM (and its reduce-scatter) is not run at all
+        dx, dw = ctx.layer._bwd(dy.contiguous(), ctx.x_full, weight, need_dx=ctx.needs_input_grad[0])
         ctx.x_full = None
         return dx, dw, None
 
@@ -75,7 +77,7 @@ class _RowFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy):
         x, weight = ctx.saved_tensors
-        dx, dw = ctx.layer._bwd(dy.contiguous(), x, weight)
+        dx, dw = ctx.layer._bwd(dy.contiguous(), x, weight, need_dx=ctx.needs_input_grad[0])
         return dx, dw, None
 
 
@@ -149,14 +151,16 @@ class ColumnParallelLinear(nn.Module):
             y = self.comm.gather_last_axis(y)
         return y, x_full
 
-    def _bwd(self, dy, x_full, w):
+    def _bwd(self, dy, x_full, w, need_dx: bool = True):
         if self.gather_output and self.mp > 1:
             r = self.comm.Get_rank()
             dy = dy[:, r * self.N:(r + 1) * self.N].contiguous()     # func_impl.py:111-147
         # dW first: its data-parallel bucket can start reducing while dx is computed -- unless the
         # dW kernel itself rewrites W (fused SGD), in which case dx must read W before that
         dw = _weight_grad(self, x_full, dy) if self.sgd_lr is None else None
-        if self.mp == 1:
+        if not need_dx:
+            dx = None
+        elif self.mp == 1:
             dx = self._gemm(dy, w, num_sms=self.num_sms)
         else:
             dx = self.rs(dy, w, b_kn=False, num_sms=self.num_sms)
@@ -189,9 +193,11 @@ class RowParallelLinear(nn.Module):
             return self._gemm(x, w, b_kn=True, num_sms=self.num_sms)
         return self.rs(x, w, b_kn=True, num_sms=self.num_sms)
 
-    def _bwd(self, dy, x, w):
+    def _bwd(self, dy, x, w, need_dx: bool = True):
+        # (a row-parallel layer's dx kernel is also what gathers dy for the dW GEMM, so with mp > 1 it
+        # runs whether or not dx is wanted)
         if self.mp == 1:
-            dx = self._gemm(dy, w, num_sms=self.num_sms)
+            dx = self._gemm(dy, w, num_sms=self.num_sms) if need_dx else None
             dy_full = dy
         else:
             dx = self.ag(dy, w, b_kn=False, num_sms=self.num_sms)

@@ -60,6 +60,7 @@ class SymmetricHeap:
             if not p:
                 raise N.NativeError(f"heap segment of rank {r} is not mapped")
             self.ptrs.append(int(p))
+        N.apply_device_timeout(device)      # watchdog budget of the kernels' waits (CCMPI_DEVICE_TIMEOUT_S)
         self._free: List[Tuple[int, int]] = [(PAD_REGION, self.bytes - PAD_REGION)]  # (offset, size)
         self._live: Dict[int, int] = {}
         self._bytes_views: Dict[int, object] = {}

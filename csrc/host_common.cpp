@@ -1,5 +1,7 @@
 #include "host_common.h"
 
+#include <vector>
+
 #include <mutex>
 #include <unordered_map>
 
@@ -109,7 +111,29 @@ int device_sm_count() {
     return sms[dev];
 }
 
+namespace {
+std::vector<int (*)(unsigned long long)>& spin_timeout_setters() {
+    static std::vector<int (*)(unsigned long long)> v;     // function-local: safe during static initialisation
+    return v;
+}
+}  // namespace
+void register_spin_timeout_setter(int (*fn)(unsigned long long)) { spin_timeout_setters().push_back(fn); }
+
 }  // namespace ccmpi
+
+// Watchdog budget of every device-side wait, on the CURRENT device (call once per device after
+// selecting it; kernels launched afterwards see the new value).
+extern "C" int ccmpi_set_spin_timeout_ns(unsigned long long ns) {
+    CCMPI_REQUIRE(ns >= 1000000ull, "spin timeout of %llu ns is below 1 ms", ns);
+    for (auto fn : ccmpi::spin_timeout_setters()) {
+        int e = fn(ns);
+        if (e != 0) {
+            ccmpi::set_error("cudaMemcpyToSymbol(spin timeout) failed: %s", cudaGetErrorString((cudaError_t)e));
+            return CCMPI_ERR_CUDA;
+        }
+    }
+    return CCMPI_OK;
+}
 
 extern "C" const char* ccmpi_last_error(void) { return ccmpi::g_err.c_str(); }
 extern "C" int ccmpi_version(void) { return 100; }

@@ -46,10 +46,18 @@ __device__ __forceinline__ bool elect_one() {
 
 // Watchdog budget for every spin in this library (mbarrier waits and cross-GPU flag waits).
 // A wrong descriptor or a peer that never arrives must end in a trap with a message, not in a
-// hung GPU.
+// hung GPU. The budget is a run-time value (ccmpi_set_spin_timeout_ns, CCMPI_DEVICE_TIMEOUT_S from
+// Python): MPI semantics allow any skew between ranks, so what is "too long" is the job's call.
+// The variable exists once per translation unit (no relocatable device code in this build); every
+// unit registers a setter at load time and the public entry point updates all copies on the
+// current device.
 #ifndef CCMPI_SPIN_TIMEOUT_NS
-#define CCMPI_SPIN_TIMEOUT_NS 8000000000ull
+#define CCMPI_SPIN_TIMEOUT_NS 120000000000ull
 #endif
+static __device__ unsigned long long g_spin_timeout_ns = CCMPI_SPIN_TIMEOUT_NS;
+__device__ __forceinline__ unsigned long long spin_timeout_ns() {
+    return *(volatile unsigned long long*)&g_spin_timeout_ns;
+}
 
 // ---------------------------------------------------------------------------------------------
 // mbarrier
@@ -101,7 +109,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int ta
     const uint64_t t0 = globaltimer_ns();
     uint32_t spins = 0;
     while (!mbar_try_wait(bar, parity)) {
-        if ((++spins & 0x3ff) == 0 && globaltimer_ns() - t0 > CCMPI_SPIN_TIMEOUT_NS)
+        if ((++spins & 0x3ff) == 0 && globaltimer_ns() - t0 > spin_timeout_ns())
             spin_timeout_trap("mbarrier wait", tag, (int)parity);
     }
 }
@@ -383,7 +391,7 @@ __device__ __forceinline__ void wait_flag_ge_sys(const uint32_t* p, uint32_t tar
     const uint64_t t0 = globaltimer_ns();
     uint32_t spins = 0;
     while ((int32_t)(ld_acquire_sys(p) - target) < 0) {
-        if ((++spins & 0xff) == 0 && globaltimer_ns() - t0 > CCMPI_SPIN_TIMEOUT_NS)
+        if ((++spins & 0xff) == 0 && globaltimer_ns() - t0 > spin_timeout_ns())
             spin_timeout_trap("peer flag wait", tag, (int)target);
     }
 }
@@ -392,7 +400,7 @@ __device__ __forceinline__ void wait_flag_ge_gpu(const uint32_t* p, uint32_t tar
     const uint64_t t0 = globaltimer_ns();
     uint32_t spins = 0;
     while ((int32_t)(ld_acquire_gpu(p) - target) < 0) {
-        if ((++spins & 0xff) == 0 && globaltimer_ns() - t0 > CCMPI_SPIN_TIMEOUT_NS)
+        if ((++spins & 0xff) == 0 && globaltimer_ns() - t0 > spin_timeout_ns())
             spin_timeout_trap("local flag wait", tag, (int)target);
     }
 }
@@ -475,3 +483,17 @@ __device__ __forceinline__ void multimem_st_v4(void* p, const uint4& v) {
 }
 
 }  // namespace ptx
+
+// ---- host side: this translation unit's copy of the watchdog budget --------------------------
+namespace ccmpi {
+void register_spin_timeout_setter(int (*fn)(unsigned long long));   // host_common.cpp
+}
+namespace {
+inline int ccmpi_tu_set_spin_timeout(unsigned long long ns) {
+    return (int)cudaMemcpyToSymbol(ptx::g_spin_timeout_ns, &ns, sizeof(ns));
+}
+struct CcmpiSpinTimeoutRegistrar {
+    CcmpiSpinTimeoutRegistrar() { ccmpi::register_spin_timeout_setter(&ccmpi_tu_set_spin_timeout); }
+};
+static CcmpiSpinTimeoutRegistrar ccmpi_spin_timeout_registrar;
+}  // namespace

@@ -75,6 +75,12 @@ typedef struct ccmpi_dev_comm {
 } ccmpi_dev_comm;
 
 const char* ccmpi_last_error(void);
+
+/* Every device-side wait (flag spins across GPUs, mbarrier waits) gives up with a printed message and a
+ * trap after this long; default 120 s. Applies to the current device, to kernels launched afterwards.
+ * (The reference's MPI calls wait forever, mpi_wrapper/comm.py:15-16; a GPU kernel that does so cannot be
+ * stopped, hence a generous, adjustable limit instead.) */
+int ccmpi_set_spin_timeout_ns(unsigned long long ns);
 int ccmpi_version(void);
 
 /* ------------------------------------------------------------------------------------------

@@ -54,8 +54,8 @@ def test_autograd_wrappers_on_cpu_tensors():
     torch.testing.assert_close(qkv.grad, ref_in.grad, rtol=1e-4, atol=1e-5)
 
 
-def test_switch_defaults_to_off(monkeypatch):
+def test_switch_defaults_to_on_and_zero_turns_it_off(monkeypatch):
     monkeypatch.delenv("CCMPI_FUSED_ELEMENTWISE", raising=False)
-    assert EW.enabled() is False
-    monkeypatch.setenv("CCMPI_FUSED_ELEMENTWISE", "1")
     assert EW.enabled() is True
+    monkeypatch.setenv("CCMPI_FUSED_ELEMENTWISE", "0")
+    assert EW.enabled() is False

@@ -1,12 +1,10 @@
-"""CUDA-graph replay of stand-alone collectives (device-side epochs) with emulated ranks on one GPU.
-Opt-in with CCMPI_TEST_UNVERIFIED=1: written after round 1's GPU budget was spent."""
+"""CUDA-graph replay of stand-alone collectives (device-side epochs) with emulated ranks on one GPU."""
 import os
 
 import pytest
 
 torch = pytest.importorskip("torch")
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("CCMPI_TEST_UNVERIFIED") != "1", reason="path not yet verified on hardware")]
+pytestmark = pytest.mark.gpu
 
 
 def test_a_captured_chain_of_small_allreduces_replays_correctly():

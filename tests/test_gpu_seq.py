@@ -1,13 +1,12 @@
-"""Token-axis (sequence-parallel) fused kernels with emulated ranks on one GPU. Written after round
-1's GPU budget was spent, not yet run on hardware: opt-in with CCMPI_TEST_UNVERIFIED=1. Oracle: the
-unfused math in fp32 PyTorch (concatenate rows / matmul / rank-ordered sum / row slice)."""
+"""Token-axis (sequence-parallel) fused kernels with emulated ranks on one GPU (first run on a B200 in
+round 2, profiles/r2_unverified_1gpu.txt). Oracle: the unfused math in fp32 PyTorch (concatenate rows /
+matmul / rank-ordered sum / row slice)."""
 import os
 
 import pytest
 
 torch = pytest.importorskip("torch")
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("CCMPI_TEST_UNVERIFIED") != "1", reason="kernel not yet verified on hardware")]
+pytestmark = pytest.mark.gpu
 
 BF = torch.bfloat16
 

@@ -1,13 +1,12 @@
 """Weight-gradient GEMM with the SGD step in its epilogue (csrc/gemm_sgd.cu) vs fp32 PyTorch.
-Written after round 1's GPU budget was spent: opt-in with CCMPI_TEST_UNVERIFIED=1. The layer-level
-logic (dx before the in-place weight update) is covered on the CPU by tests/test_multirank_host.py."""
+First run on a B200 in round 2 (profiles/r2_unverified_1gpu.txt). The layer-level logic (dx before the
+in-place weight update) is also covered on the CPU by tests/test_multirank_host.py."""
 import os
 
 import pytest
 
 torch = pytest.importorskip("torch")
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("CCMPI_TEST_UNVERIFIED") != "1", reason="kernel not yet verified on hardware")]
+pytestmark = pytest.mark.gpu
 
 BF = torch.bfloat16
 

@@ -1,13 +1,11 @@
 """Group-size-specialised reduce-scatter / two-shot all-reduce (csrc/collectives_tight.cu) against the regular
-kernels, emulated ranks on one GPU: results must be bit-identical (same rank-ordered reduction). Opt-in with
-CCMPI_TEST_UNVERIFIED=1: written after round 1's GPU budget was spent."""
+kernels, emulated ranks on one GPU: results must be bit-identical (same rank-ordered reduction)."""
 import os
 
 import pytest
 
 torch = pytest.importorskip("torch")
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("CCMPI_TEST_UNVERIFIED") != "1", reason="kernel not yet verified on hardware")]
+pytestmark = pytest.mark.gpu
 
 
 @pytest.fixture(params=[2, 4])
