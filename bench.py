@@ -118,6 +118,18 @@ def run_gpu(args, impl: str):
                                                       in_dim=HIDDEN, out_dim=HIDDEN)
     tokens = SEQ * SEQS_PER_REPLICA
     shard = HIDDEN // mp
+    check = None
+    if impl == "ours":
+        # correctness witness before anything is timed (at N >= 2 the only one a timing line can carry)
+        sys.path.insert(0, os.path.join(ROOT, "benchmarks"))
+        from selfcheck import run_selfcheck
+        check = run_selfcheck(comm, mp_comm, dp_comm)
+        if not check["ok"]:
+            if rank == 0:
+                emit({"metric": METRIC, "impl": impl, "n_gpus": world, "selfcheck": check,
+                      "error": "fused kernels disagree with the unfused oracle; nothing was timed"})
+            comm.Barrier()
+            raise SystemExit(3)
     if impl == "ours":
         from collective_communication_mpi_b200.models import TrainStep, TransformerFCBlock
         model = TransformerFCBlock(mp_comm, tokens, HIDDEN, FFN_MULT, seed=1)
@@ -209,6 +221,7 @@ def run_gpu(args, impl: str):
             "e2e": {"value": round(e2e, 1), "unit": "tokens/s", "h2d_bytes_per_step": int(2 * tokens * shard * 2),
                     "d2h_bytes_per_step": 4, "ms_per_step": round(ms_e2e / args.steps, 4)},
             "gpu_launches": int(launches) if impl == "ours" else 0,
+            **({"selfcheck": check} if check is not None else {}),
             "gemm_tflops_per_gpu": round(tflops_per_gpu, 1),
         })
     comm.Barrier()

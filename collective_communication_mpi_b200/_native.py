@@ -16,6 +16,7 @@ from . import build as _build
 MAX_RANKS = 8
 MAX_VRANKS = 4
 MAX_BLOCKS = 160
+BLOCKS_PAIRED = 0x10000     # OR into max_blocks: even grid launched as 2-CTA clusters (whole SM pairs)
 PAD_WORDS = 16384
 PAD_BYTES = PAD_WORDS * 4
 PAD_USER = 2048
@@ -172,13 +173,14 @@ def _declare_device(lib):
     PV = P(vp)
     u = C.c_uint
     fused = {
-        "ccmpi_fused_ag_gemm": (i, [P(DevComm), i, sz, i, sz, PV, PV, i, i, i, i, i, i, i, i, u, i, i, i, vp]),
+        "ccmpi_fused_ag_gemm": (i, [P(DevComm), i, sz, i, sz, PV, PV, i, i, i, i, i, i, i, i, u, u, i, i, i, vp]),
+        "ccmpi_fused_ag_ctas": (i, [i, i, i, i, i]),
         "ccmpi_fused_gemm_rs": (i, [P(DevComm), i, PV, PV, sz, PV, i, i, i, i, i, i, i, i, i, i, u, i, vp]),
         "ccmpi_fused_gemm_ar": (i, [P(DevComm), i, PV, PV, sz, sz, i, i, i, i, i, i, i, i, i, u, i, i, vp]),
         "ccmpi_fused_gemm_ag": (i, [P(DevComm), i, PV, PV, sz, i, i, i, i, i, i, i, i, i, i, vp]),
-        "ccmpi_fused_ag_gemm_m": (i, [P(DevComm), i, sz, i, sz, PV, PV, i, i, i, i, i, i, i, i, u, i, vp]),
+        "ccmpi_fused_ag_gemm_m": (i, [P(DevComm), i, sz, i, sz, PV, PV, i, i, i, i, i, i, i, i, u, u, i, vp]),
         "ccmpi_fused_gemm_rs_m": (i, [P(DevComm), i, PV, PV, sz, PV, i, i, i, i, i, i, i, i, i, i, u, i, vp]),
-        "ccmpi_fused_ag_gemm_ag": (i, [P(DevComm), i, sz, i, sz, PV, sz, i, i, i, i, i, i, i, u, i, vp]),
+        "ccmpi_fused_ag_gemm_ag": (i, [P(DevComm), i, sz, i, sz, PV, sz, i, i, i, i, i, i, i, u, u, i, vp]),
     }
     ll = C.c_longlong
     fused.update({

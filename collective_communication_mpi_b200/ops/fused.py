@@ -40,14 +40,24 @@ def _ptrs(tensors: Sequence[Optional[torch.Tensor]]):
 # raw entry points
 # -------------------------------------------------------------------------------------------------
 def ag_gemm_raw(comms, x_off: int, ldx: int, xfull_off: int, B: List[torch.Tensor], Cout: List[torch.Tensor],
-                M: int, Nn: int, K: int, *, b_kn: bool, flag_base: int, epoch: int, num_comm_ctas: int = 0,
-                num_sms: int = 0, use_mc: bool = True, stream=None):
+                M: int, Nn: int, K: int, *, b_kn: bool, flag_base: int, epoch: int, flag_target: int = 0,
+                num_comm_ctas: int = 0, num_sms: int = 0, use_mc: bool = True, stream=None):
+    """``flag_target``: value the ready flags must reach for this launch (running sum of ``ag_ctas``
+    over the launches on these flags); 0 = ``epoch`` times this launch's CTA count, which is right only
+    when every launch on the flags has the same shape and SM budget (the tests' case)."""
     a, n = _arr(comms)
     rc = N.device_lib().ccmpi_fused_ag_gemm(a, n, x_off, ldx, xfull_off, _ptrs(B), _ptrs(Cout), M, Nn, K,
                                             B[0].stride(0), Cout[0].stride(0), int(b_kn), _OUT[Cout[0].dtype],
-                                            flag_base, epoch, num_comm_ctas, num_sms, int(use_mc), _sp(stream))
+                                            flag_base, epoch, flag_target & 0xFFFFFFFF, num_comm_ctas, num_sms,
+                                            int(use_mc), _sp(stream))
     N.check(rc, "ccmpi_fused_ag_gemm")
     N.count_launch()
+
+
+def ag_ctas(kind: int, M: int, Nn: int, nvr: int, num_sms: int) -> int:
+    """CTAs per rank of an all-gather->GEMM launch = contributions each of its ready flags gets from one
+    source rank (kind 0: K-gather kernels, 1: M-gather)."""
+    return N.check(N.device_lib().ccmpi_fused_ag_ctas(kind, M, Nn, nvr, num_sms), "ccmpi_fused_ag_ctas")
 
 
 def gemm_rs_raw(comms, A: List[torch.Tensor], B: List[torch.Tensor], slots_off: int, Cout: List[torch.Tensor],
@@ -140,6 +150,7 @@ class AllGatherGemm:
         self.xfull = [h.empty((M, K), torch.bfloat16) for _ in range(2)] if n > 1 else [h.empty((8, 8), torch.bfloat16)] * 2
         self.flag_base = self.ctx.new_slot(_ag_flag_words(M, n))
         self.epoch = 0
+        self.flag_total = 0     # running sum of CTA counts: what the ready flags have reached after the last launch
         self.num_comm_ctas, self.use_mc = num_comm_ctas, use_mc and self.ctx.dev.has_mc
 
     def input_buffer(self) -> torch.Tensor:
@@ -160,10 +171,13 @@ class AllGatherGemm:
         if out is None:
             out = torch.empty((self.M, Nn), dtype=out_dtype, device=w.device)
         self.epoch += 1
+        # every member launches the same shape with the same SM budget, so this rank's CTA count is
+        # also the number of contributions its flags receive from each peer
+        self.flag_total += ag_ctas(0, self.M, Nn, 1, num_sms)
         xf_off = self.xfull[self.epoch & 1][0]
         ag_gemm_raw(self.ctx.dev.comms, self.x_off, self.chunk, xf_off, [w], [out], self.M, Nn, self.K, b_kn=b_kn,
-                    flag_base=self.flag_base, epoch=self.epoch, num_comm_ctas=self.num_comm_ctas, num_sms=num_sms,
-                    use_mc=self.use_mc, stream=stream)
+                    flag_base=self.flag_base, epoch=self.epoch, flag_target=self.flag_total,
+                    num_comm_ctas=self.num_comm_ctas, num_sms=num_sms, use_mc=self.use_mc, stream=stream)
         return out
 
 

@@ -21,15 +21,16 @@ import torch
 
 from .. import _native as N
 from .collectives import _arr, _sp
-from .fused import _OUT, _ctx, _ptrs
+from .fused import _OUT, _ctx, _ptrs, ag_ctas
 
 
 def ag_gemm_m_raw(comms, x_off: int, ldx: int, xfull_off: int, B: List[torch.Tensor], Cout: List[torch.Tensor],
-                  M: int, Nn: int, K: int, *, b_kn: bool, flag_base: int, epoch: int, num_sms: int = 0, stream=None):
+                  M: int, Nn: int, K: int, *, b_kn: bool, flag_base: int, epoch: int, flag_target: int = 0,
+                  num_sms: int = 0, stream=None):
     a, n = _arr(comms)
     rc = N.device_lib().ccmpi_fused_ag_gemm_m(a, n, x_off, ldx, xfull_off, _ptrs(B), _ptrs(Cout), M, Nn, K,
                                               B[0].stride(0), Cout[0].stride(0), int(b_kn), _OUT[Cout[0].dtype],
-                                              flag_base, epoch, num_sms, _sp(stream))
+                                              flag_base, epoch, flag_target & 0xFFFFFFFF, num_sms, _sp(stream))
     N.check(rc, "ccmpi_fused_ag_gemm_m")
     N.count_launch()
 
@@ -87,8 +88,10 @@ class AllGatherGemmM:
         if out is None:
             out = torch.empty((self.M, Nn), dtype=out_dtype, device=w.device)
         self.epoch += 1
+        self.flag_total = getattr(self, "flag_total", 0) + ag_ctas(1, self.M, Nn, 1, num_sms)
         ag_gemm_m_raw(self.ctx.dev.comms, self.x_off, self.K, self.xfull[self.epoch & 1][0], [w], [out], self.M, Nn,
-                      self.K, b_kn=b_kn, flag_base=self.flag_base, epoch=self.epoch, num_sms=num_sms, stream=stream)
+                      self.K, b_kn=b_kn, flag_base=self.flag_base, epoch=self.epoch, flag_target=self.flag_total,
+                      num_sms=num_sms, stream=stream)
         return out
 
 
@@ -119,12 +122,12 @@ class GemmReduceScatterM:
 # gather -> GEMM -> gather (feature axis): the reference's complete forward step in one kernel
 # -------------------------------------------------------------------------------------------------
 def ag_gemm_ag_raw(comms, x_off: int, ldx: int, xfull_off: int, B: List[torch.Tensor], yfull_off: int, M: int, Nn: int,
-                   K: int, *, b_kn: bool, out_dtype=torch.bfloat16, flag_base: int, epoch: int, num_sms: int = 0,
-                   stream=None):
+                   K: int, *, b_kn: bool, out_dtype=torch.bfloat16, flag_base: int, epoch: int, flag_target: int = 0,
+                   num_sms: int = 0, stream=None):
     a, n = _arr(comms)
     rc = N.device_lib().ccmpi_fused_ag_gemm_ag(a, n, x_off, ldx, xfull_off, _ptrs(B), yfull_off, M, Nn, K,
-                                               B[0].stride(0), int(b_kn), _OUT[out_dtype], flag_base, epoch, num_sms,
-                                               _sp(stream))
+                                               B[0].stride(0), int(b_kn), _OUT[out_dtype], flag_base, epoch,
+                                               flag_target & 0xFFFFFFFF, num_sms, _sp(stream))
     N.check(rc, "ccmpi_fused_ag_gemm_ag")
     N.count_launch()
 
@@ -154,8 +157,9 @@ class AllGatherGemmAllGather:
         if x.data_ptr() != self.x.data_ptr():
             self.x.copy_(x.reshape(self.M, self.chunk))
         self.epoch += 1
+        self.flag_total = getattr(self, "flag_total", 0) + ag_ctas(0, self.M, self.N, 1, num_sms)
         off, out = self.outs[self.epoch & 1]
         ag_gemm_ag_raw(self.ctx.dev.comms, self.x_off, self.chunk, self.xfull[self.epoch & 1][0], [w], off, self.M,
                        self.N, self.K, b_kn=b_kn, out_dtype=self.dtype, flag_base=self.flag_base, epoch=self.epoch,
-                       num_sms=num_sms, stream=stream)
+                       flag_target=self.flag_total, num_sms=num_sms, stream=stream)
         return out

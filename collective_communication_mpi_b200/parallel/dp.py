@@ -11,8 +11,19 @@ is implied. Here it is a first-class path:
   of csrc/collectives.cu (NVLS ``multimem.ld_reduce``/``multimem.st`` with fp32 accumulation when
   the switch supports it, two-shot P2P otherwise), in place, with ``scale = 1/dp`` applied in the
   same pass;
-* the kernel runs on its own stream: 512-thread blocks without shared memory co-reside with the
-  persistent GEMM CTAs, so the reduction hides behind the remaining backward GEMMs.
+* the kernel runs on its own stream next to the remaining backward GEMMs, on SMs of its own.
+
+SM partition (why ``max_blocks`` and ``layer.bwd_num_sms`` exist). A reduction block (512 threads
+x 82-128 registers) fills an SM's register file, so it never shares an SM with a GEMM CTA. The
+fused GEMM+collective kernels of a model-parallel group assign tiles and push work statically to
+their CTAs, which wait on peers: every CTA must be resident. If a rank's reduction took SMs the
+next fused GEMM needed while its data-parallel partner had them the other way round, the two
+kernels of the two groups would wait on each other for ever. Therefore, whenever buckets overlap a
+model-parallel backward (mp > 1 and dp > 1): the reduction gets at most ``max_blocks`` blocks,
+launched as 2-CTA clusters so that it takes whole SM pairs (the GEMM's CTA pairs need both SMs of a
+pair), and the layers' backward fused kernels are sized to the remaining SMs. Together they always
+fit, whatever order the hardware starts them in. The last bucket has nothing to hide behind: it is
+launched on the main stream, after the kernels before it, and may use every SM.
 """
 from __future__ import annotations
 
@@ -25,7 +36,7 @@ from ..ops import collectives as CO
 
 
 class GradSink:
-    def __init__(self, dp_comm, layers, *, bucket_mb: int = 64, overlap: bool = True, max_blocks: int = 32):
+    def __init__(self, dp_comm, layers, *, bucket_mb: int = 64, overlap: bool = True, max_blocks: int = 16):
         self.comm = dp_comm
         self.dp = dp_comm.Get_size()
         self.layers = list(layers)
@@ -64,9 +75,18 @@ class GradSink:
             layer.grad_sink = self
         self.overlap = overlap and self.dp > 1 and self.on_gpu
         self.stream = torch.cuda.Stream() if self.overlap else None
-        self.max_blocks = max_blocks
+        self.max_blocks = max_blocks & ~1
         self.algo = N.AR_NVLS if self.use_nvls else N.AR_TWOSHOT
         self.launches = 0
+        # reserve the reduction's SMs in the backward fused kernels of a model-parallel group
+        self.partitioned = self.overlap and any(getattr(l, "mp", 1) > 1 for l in self.layers)
+        if self.partitioned:
+            sms = self.comm._world.sm_count
+            for l in self.layers:
+                if hasattr(l, "bwd_num_sms"):
+                    l.bwd_num_sms = (sms - self.max_blocks) & ~1
+                else:       # layer kinds with one SM budget for all their kernels
+                    l.num_sms = (sms - self.max_blocks) & ~1
 
     def view_for(self, param) -> torch.Tensor:
         return self._views[id(param)]
@@ -98,13 +118,15 @@ class GradSink:
         off = self.flat_off + b["lo"] * 2
         tmp_off = self.dev.heap.offset_of(self.tmp) + b["lo"] * 2 if self.tmp is not None else 0
         cur = torch.cuda.current_stream()
-        st = self.stream if self.overlap else cur
-        if self.overlap:
+        side = self.overlap and not last
+        st = self.stream if side else cur
+        if side:
             ev = torch.cuda.Event()
             ev.record(cur)
             st.wait_event(ev)
+        blocks = 0 if not side else (self.max_blocks | N.BLOCKS_PAIRED if self.partitioned else self.max_blocks)
         CO.allreduce(self.dev.comms, N.BF16, N.SUM, off, off, count, tmp_off=tmp_off, algo=self.algo,
-                     scale=1.0 / self.dp, max_blocks=(0 if last else self.max_blocks), stream=st)
+                     scale=1.0 / self.dp, max_blocks=blocks, stream=st)
         self.launches += 1
 
     def finish(self):

@@ -128,6 +128,7 @@ class ColumnParallelLinear(nn.Module):
             from ..ops.fused_seq import AllGatherGemmAllGather
             self.out_ag = AllGatherGemmAllGather(mp_comm, tokens, in_features, self.N)
         self.num_sms = 0
+        self.bwd_num_sms = 0    # SM budget of the backward fused kernel (set by GradSink when a reduction runs next to it)
 
     def input_buffer(self) -> torch.Tensor:
         """Write the layer input here (symmetric memory) to skip one device copy."""
@@ -163,7 +164,7 @@ class ColumnParallelLinear(nn.Module):
         elif self.mp == 1:
             dx = self._gemm(dy, w, num_sms=self.num_sms)
         else:
-            dx = self.rs(dy, w, b_kn=False, num_sms=self.num_sms)
+            dx = self.rs(dy, w, b_kn=False, num_sms=self.bwd_num_sms)
         if self.sgd_lr is not None:
             dw = _weight_grad(self, x_full, dy)
         return dx, dw
@@ -184,6 +185,7 @@ class RowParallelLinear(nn.Module):
         self.rs = ops.GemmReduceScatter(mp_comm, tokens, out_features) if self.mp > 1 else None
         self.ag = ops.AllGatherGemm(mp_comm, tokens, out_features, num_comm_ctas=num_comm_ctas) if self.mp > 1 else None
         self.num_sms = 0
+        self.bwd_num_sms = 0
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         return _RowFn.apply(x.reshape(self.M, -1), self.weight, self)
@@ -200,7 +202,7 @@ class RowParallelLinear(nn.Module):
             dx = self._gemm(dy, w, num_sms=self.num_sms) if need_dx else None
             dy_full = dy
         else:
-            dx = self.ag(dy, w, b_kn=False, num_sms=self.num_sms)
+            dx = self.ag(dy, w, b_kn=False, num_sms=self.bwd_num_sms)
             dy_full = self.ag.gathered()
         dw = _weight_grad(self, x, dy_full)     # after dx: with fused SGD this kernel rewrites W
         return dx, dw

@@ -519,6 +519,7 @@ extern "C" int ccmpi_allreduce(const ccmpi_dev_comm* comms, int nvr, int algo, i
     if (count == 0) return CCMPI_OK;
     cudaStream_t st = (cudaStream_t)stream;
     if (out_dtype < 0) out_dtype = dtype;
+    CCMPI_REQUIRE(dtype >= 0 && dtype <= CCMPI_I64, "all-reduce: unsupported dtype %d", dtype);
     if (algo == CCMPI_AR_AUTO) {
         static const size_t esz[] = {4, 2, 2, 8, 4, 8, 1};
         const size_t bytes = count * esz[dtype];

@@ -158,7 +158,13 @@ static int fill_launch(Launch& lp, const ccmpi_dev_comm* comms, int nvr) {
     return CCMPI_OK;
 }
 
+// `max_blocks`: 0 = library default; otherwise the cap, optionally OR-ed with CCMPI_BLOCKS_PAIRED:
+// the grid is then even and launched as 2-CTA clusters, so the kernel occupies whole TPCs. A
+// reduction that overlaps a CTA-pair GEMM whose CTAs wait on peers must not fragment the SM pairs
+// that GEMM needs to become fully resident (see parallel/dp.py). A paired count is returned negative.
 static int clamp_blocks(size_t work_items, int max_blocks) {
+    const bool paired = max_blocks > 0 && (max_blocks & CCMPI_BLOCKS_PAIRED) != 0;
+    if (max_blocks > 0) max_blocks &= CCMPI_BLOCKS_PAIRED - 1;
     int cap = max_blocks > 0 ? max_blocks : 128;
     if (cap > CCMPI_MAX_BLOCKS) cap = CCMPI_MAX_BLOCKS;
     size_t want = (work_items + THREADS - 1) / THREADS;
@@ -166,12 +172,19 @@ static int clamp_blocks(size_t work_items, int max_blocks) {
     // barrier among few blocks is cheaper; large ones need every SM's worth of loads in flight
     want = (want + 7) / 8;
     if (want < 1) want = 1;
-    return (int)(want < (size_t)cap ? want : (size_t)cap);
+    int blocks = (int)(want < (size_t)cap ? want : (size_t)cap);
+    if (!paired) return blocks;
+    blocks = (blocks + 1) & ~1;
+    if (blocks > cap) blocks = cap & ~1;
+    if (blocks < 2) blocks = 2;
+    return -blocks;
 }
 
 template <typename... Args>
 static int launch(void (*kern)(Args...), int nvr, int blocks, cudaStream_t stream, Args... args) {
     void* ptrs[] = {(void*)&args...};
+    const bool paired = blocks < 0;
+    if (paired) blocks = -blocks;
     if (nvr > 1) {
         // emulated ranks spin on one another: co-residency must be guaranteed, so the grid is
         // clamped to what the device can hold at once (every kernel here is grid-stride)
@@ -181,6 +194,20 @@ static int launch(void (*kern)(Args...), int nvr, int blocks, cudaStream_t strea
         CCMPI_REQUIRE(cap >= 1, "device cannot hold %d emulated ranks at once", nvr);
         if (blocks > cap) blocks = cap;
         CCMPI_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)kern, dim3(blocks * nvr), dim3(THREADS), ptrs, 0, stream));
+    } else if (paired) {
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.gridDim = dim3(blocks);
+        cfg.blockDim = dim3(THREADS);
+        cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        CCMPI_CUDA_CHECK(cudaLaunchKernelExC(&cfg, (const void*)kern, ptrs));
     } else {
         CCMPI_CUDA_CHECK(cudaLaunchKernel((const void*)kern, dim3(blocks), dim3(THREADS), ptrs, 0, stream));
     }

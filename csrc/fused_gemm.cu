@@ -33,8 +33,8 @@ int grid_for(int nvr, int sms, int tiles, int extra) {
 // all-gather -> GEMM (K-gather): C_r[M][N] = [x_0 | ... | x_{n-1}] * B_r, x_r = rank r's [M][K/n] shard
 extern "C" int ccmpi_fused_ag_gemm(const ccmpi_dev_comm* comms, int nvr, size_t x_off, int ldx, size_t xfull_off,
                                    const void* const* B, void* const* C, int M, int N, int K, int ldb, int ldc,
-                                   int b_kn, int out_dtype, int flag_base, unsigned epoch, int num_comm_ctas,
-                                   int num_sms, int use_mc, void* stream) {
+                                   int b_kn, int out_dtype, int flag_base, unsigned epoch, unsigned flag_target,
+                                   int num_comm_ctas, int num_sms, int use_mc, void* stream) {
     int rc = check_shapes(M, N, K, ldx, ldb, ldc, out_dtype);
     if (rc) return rc;
     const int n = comms ? comms[0].size : 0;
@@ -71,16 +71,34 @@ extern "C" int ccmpi_fused_ag_gemm(const ccmpi_dev_comm* comms, int nvr, size_t 
         rp.off0 = x_off; rp.off1 = xfull_off;
         rp.chunk = chunk;
         rp.flag_base = flag_base;
-        rp.epoch = epoch;
+        // A ready flag counts the pushing CTAs of its source rank. flag_target (what the flags must
+        // reach for THIS launch: the caller's running sum of CTA counts, ccmpi_fused_ag_ctas) lets the
+        // CTA count differ from launch to launch; 0 = every launch on these flags has this CTA count.
+        rp.epoch = flag_target ? flag_target : epoch * (unsigned)gemm_ctas;
         rp.num_comm_ctas = ncomm;
         rp.aux0 = ldx;
         static const int env_push_first = [] { const char* e = getenv("CCMPI_AG_PUSH_FIRST"); return e ? atoi(e) : 0; }();
         rp.aux1 = (use_mc ? 1 : 0) | (env_push_first ? 4 : 0);
-        rp.aux2 = gemm_ctas;   // contributions per ready flag and launch: keep num_sms fixed per context
+        rp.aux2 = 1;
     }
     if (pairs)
         return dispatch2<AgKPolicy>(lp, BN, false, b_kn != 0, out_dtype, (gemm_ctas + ncomm) * nvr, (cudaStream_t)stream, nvr > 1);
     return dispatch<AgKPolicy>(lp, BN, false, b_kn != 0, out_dtype, (gemm_ctas + ncomm) * nvr, (cudaStream_t)stream, nvr > 1);
+}
+
+// CTAs per rank that a launch of an all-gather -> GEMM kernel will use (= contributions each ready flag
+// receives from one source rank): kind 0 K-gather (ccmpi_fused_ag_gemm, ccmpi_fused_ag_gemm_ag), 1 M-gather.
+extern "C" int ccmpi_fused_ag_ctas(int kind, int M, int N, int nvr, int num_sms) {
+    CCMPI_REQUIRE(nvr >= 1 && M > 0 && N > 0, "bad arguments");
+    const int sms = (num_sms > 0 ? num_sms : ccmpi::device_sm_count());
+    int budget = sms / nvr;
+    const bool pairs = use_2cta() || kind == 1;
+    if (pairs) budget &= ~1;
+    const int BN = pick_bn(M, N, budget);
+    const int m_blocks = (M + BM - 1) / BM;
+    const int nb = (N + BN - 1) / BN;
+    const int tiles = kind == 1 ? 2 * ((m_blocks / 2) * nb) : (pairs ? 2 * (((m_blocks + 1) / 2) * nb) : m_blocks * nb);
+    return budget < tiles ? budget : tiles;
 }
 
 namespace {

@@ -46,7 +46,8 @@ int dispatch_agm(const Launch& lp, int BN, bool b_mn, int out_dtype, int grid, c
 // x_off: symmetric [M/n][K] (row stride ldx), xfull_off: symmetric [M][K] that every member's rows are pushed into.
 extern "C" int ccmpi_fused_ag_gemm_m(const ccmpi_dev_comm* comms, int nvr, size_t x_off, int ldx, size_t xfull_off,
                                      const void* const* B, void* const* C, int M, int N, int K, int ldb, int ldc,
-                                     int b_kn, int out_dtype, int flag_base, unsigned epoch, int num_sms, void* stream) {
+                                     int b_kn, int out_dtype, int flag_base, unsigned epoch, unsigned flag_target,
+                                     int num_sms, void* stream) {
     int rc = check_shapes(M, N, K, ldx, ldb, ldc, out_dtype);
     if (rc) return rc;
     int Mr = 0;
@@ -77,9 +78,9 @@ extern "C" int ccmpi_fused_ag_gemm_m(const ccmpi_dev_comm* comms, int nvr, size_
         rp.off0 = x_off; rp.off1 = xfull_off;
         rp.chunk = Mr;
         rp.flag_base = flag_base;
-        rp.epoch = epoch;
+        rp.epoch = flag_target ? flag_target : epoch * (unsigned)ctas;   // see ccmpi_fused_ag_gemm
         rp.aux0 = ldx;
-        rp.aux2 = ctas;      // contributions per ready flag and launch: keep num_sms fixed per context
+        rp.aux2 = 1;
     }
     return dispatch_agm(lp, BN, b_kn != 0, out_dtype, ctas * nvr, (cudaStream_t)stream, nvr > 1);
 }
@@ -130,7 +131,8 @@ extern "C" int ccmpi_fused_gemm_rs_m(const ccmpi_dev_comm* comms, int nvr, const
 // on every member; x_r = rank r's [M][K/n] shard (K-gather as in ccmpi_fused_ag_gemm).
 extern "C" int ccmpi_fused_ag_gemm_ag(const ccmpi_dev_comm* comms, int nvr, size_t x_off, int ldx, size_t xfull_off,
                                       const void* const* B, size_t yfull_off, int M, int N, int K, int ldb, int b_kn,
-                                      int out_dtype, int flag_base, unsigned epoch, int num_sms, void* stream) {
+                                      int out_dtype, int flag_base, unsigned epoch, unsigned flag_target, int num_sms,
+                                      void* stream) {
     int rc = check_shapes(M, N, K, ldx, ldb, N, out_dtype);
     if (rc) return rc;
     CCMPI_REQUIRE(comms && nvr >= 1 && nvr <= CCMPI_MAX_VRANKS, "nvr=%d out of range", nvr);
@@ -164,10 +166,10 @@ extern "C" int ccmpi_fused_ag_gemm_ag(const ccmpi_dev_comm* comms, int nvr, size
         rp.off0 = x_off; rp.off1 = xfull_off; rp.off2 = yfull_off;
         rp.chunk = chunk;
         rp.flag_base = flag_base;
-        rp.epoch = epoch;
+        rp.epoch = flag_target ? flag_target : epoch * (unsigned)ctas;   // see ccmpi_fused_ag_gemm
         rp.aux0 = ldx;
         rp.aux1 = 0;         // bulk-copy push: the staging rows exist in this kernel
-        rp.aux2 = ctas;
+        rp.aux2 = 1;
     }
 #define CCMPI_AGAG_CASE(bn, bmn)                                                                                  \
     if (BN == bn && (b_kn != 0) == bmn) {                                                                         \

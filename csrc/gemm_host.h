@@ -15,10 +15,12 @@ int check_shapes(int M, int N, int K, long long lda, long long ldb, long long ld
 template <int BN, bool A_MN, bool B_MN, typename OutT, typename Policy>
 int launch(const Launch& lp, int grid, cudaStream_t stream, bool cooperative) {
     auto kern = gemm_kernel<BN, A_MN, B_MN, OutT, Policy>;
-    static bool configured = false;  // per instantiation
-    if (!configured) {
+    static bool configured[64] = {};   // the attribute is per device (and per instantiation)
+    int dev_ = 0;
+    CCMPI_CUDA_CHECK(cudaGetDevice(&dev_));
+    if (!configured[dev_ & 63]) {
         CCMPI_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM_BYTES));
-        configured = true;
+        configured[dev_ & 63] = true;
     }
     if (!cooperative) {
         kern<<<grid, NUM_THREADS, Cfg<BN>::SMEM_BYTES, stream>>>(lp);
@@ -35,10 +37,12 @@ int launch(const Launch& lp, int grid, cudaStream_t stream, bool cooperative) {
 template <int BN, bool A_MN, bool B_MN, typename OutT, typename Policy>
 int launch2(const Launch& lp, int grid, cudaStream_t stream, bool cooperative) {
     auto kern = gemm_kernel_2cta<BN, A_MN, B_MN, OutT, Policy>;
-    static bool configured = false;
-    if (!configured) {
+    static bool configured[64] = {};   // the attribute is per device (and per instantiation)
+    int dev_ = 0;
+    CCMPI_CUDA_CHECK(cudaGetDevice(&dev_));
+    if (!configured[dev_ & 63]) {
         CCMPI_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg2<BN, Policy::kNeedsStaging>::SMEM_BYTES));
-        configured = true;
+        configured[dev_ & 63] = true;
     }
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof(cfg));

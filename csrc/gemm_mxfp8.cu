@@ -275,10 +275,12 @@ extern "C" int ccmpi_gemm_mxfp8(const void* A, const void* sfa, const void* B, c
     p.out_bf16 = out_dtype == CCMPI_BF16;
     const int pair_tiles = (int)(((m_chunks + 1) / 2) * n_chunks);
     const int npairs = pair_tiles < sms / 2 ? pair_tiles : sms / 2;
-    static bool configured = false;
-    if (!configured) {
+    static bool configured[64] = {};   // the attribute is per device (and per instantiation)
+    int dev_ = 0;
+    CCMPI_CUDA_CHECK(cudaGetDevice(&dev_));
+    if (!configured[dev_ & 63]) {
         CCMPI_CUDA_CHECK(cudaFuncSetAttribute(gemm_mxfp8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-        configured = true;
+        configured[dev_ & 63] = true;
     }
     gemm_mxfp8_kernel<<<2 * npairs, NUM_THREADS, SMEM_BYTES, (cudaStream_t)stream>>>(p);
     CCMPI_CUDA_CHECK(cudaGetLastError());

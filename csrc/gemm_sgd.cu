@@ -45,10 +45,12 @@ struct SgdPolicy : PlainPolicy {
 template <int BN, bool A_MN, bool B_MN>
 static int launch_sgd(const Launch& lp, int grid, cudaStream_t stream) {
     auto kern = gemm_kernel_2cta<BN, A_MN, B_MN, __nv_bfloat16, SgdPolicy>;
-    static bool configured = false;
-    if (!configured) {
+    static bool configured[64] = {};   // the attribute is per device (and per instantiation)
+    int dev_ = 0;
+    CCMPI_CUDA_CHECK(cudaGetDevice(&dev_));
+    if (!configured[dev_ & 63]) {
         CCMPI_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg2<BN, false>::SMEM_BYTES));
-        configured = true;
+        configured[dev_ & 63] = true;
     }
     kern<<<grid, NUM_THREADS, Cfg2<BN, false>::SMEM_BYTES, stream>>>(lp);
     CCMPI_CUDA_CHECK(cudaGetLastError());

@@ -23,6 +23,9 @@ extern "C" {
 #define CCMPI_MAX_RANKS 8   /* one NVSwitch domain */
 #define CCMPI_MAX_VRANKS 4  /* emulated ranks per single-GPU launch (tests) */
 #define CCMPI_MAX_BLOCKS 160
+/* OR into a collective's `max_blocks`: even grid, launched as 2-CTA clusters (whole SM pairs), for a
+ * collective that runs next to a CTA-pair GEMM whose CTAs wait on peers */
+#define CCMPI_BLOCKS_PAIRED 0x10000
 
 /* signal pad layout, in uint32 words, one pad per (communicator, rank) */
 #define CCMPI_PAD_WORDS 16384                     /* 64 KiB */
@@ -185,11 +188,19 @@ int ccmpi_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, 
 
 /* all-gather -> GEMM on the gathered K axis (func_impl.py:76-91 + the consuming FC GEMM):
  * C[M][N] = [x_0 | ... | x_{n-1}] * B with x_r = rank r's [M][K/n] shard at x_off (row stride
- * ldx elements); xfull_off: [M][K] staging the peers push into. */
+ * ldx elements); xfull_off: [M][K] staging the peers push into.
+ *
+ * Ready flags count the pushing CTAs of each source rank. `flag_target` is the value the flags must
+ * reach for this launch: the caller's running sum, over all launches on these flags, of
+ * ccmpi_fused_ag_ctas() -- so shapes and SM budgets may change between launches. With flag_target = 0
+ * the kernel waits for epoch * (this launch's CTA count), which is only right when every launch on
+ * these flags has that count. */
 int ccmpi_fused_ag_gemm(const ccmpi_dev_comm* comms, int nvr, size_t x_off, int ldx, size_t xfull_off,
                         const void* const* B, void* const* C, int M, int N, int K, int ldb, int ldc,
-                        int b_kn, int out_dtype, int flag_base, unsigned epoch, int num_comm_ctas,
-                        int num_sms, int use_mc, void* stream);
+                        int b_kn, int out_dtype, int flag_base, unsigned epoch, unsigned flag_target,
+                        int num_comm_ctas, int num_sms, int use_mc, void* stream);
+/* kind 0: K-gather kernels (ccmpi_fused_ag_gemm, ccmpi_fused_ag_gemm_ag), 1: M-gather (ccmpi_fused_ag_gemm_m) */
+int ccmpi_fused_ag_ctas(int kind, int M, int N, int nvr, int num_sms);
 
 /* GEMM -> reduce-scatter on N (the dx GEMM + func_impl.py:150-187): C[M][N/n] = rank-ordered sum
  * over ranks of (A*B)[:, own column block]; slots_off: [n][M][N/n] staging (out dtype). */
@@ -220,7 +231,8 @@ int ccmpi_fused_gemm_ag(const ccmpi_dev_comm* comms, int nvr, const void* const*
  *              [n][M/n][N] staging of the output dtype. */
 int ccmpi_fused_ag_gemm_m(const ccmpi_dev_comm* comms, int nvr, size_t x_off, int ldx, size_t xfull_off,
                           const void* const* B, void* const* C, int M, int N, int K, int ldb, int ldc,
-                          int b_kn, int out_dtype, int flag_base, unsigned epoch, int num_sms, void* stream);
+                          int b_kn, int out_dtype, int flag_base, unsigned epoch, unsigned flag_target, int num_sms,
+                          void* stream);
 int ccmpi_fused_gemm_rs_m(const ccmpi_dev_comm* comms, int nvr, const void* const* A, const void* const* B,
                           size_t slots_off, void* const* C, int M, int N, int K, int lda, int ldb, int ldc,
                           int a_km, int b_kn, int out_dtype, int flag_base, unsigned epoch, int num_sms,
@@ -232,7 +244,8 @@ int ccmpi_fused_gemm_rs_m(const ccmpi_dev_comm* comms, int nvr, const void* cons
  * [M][N*n]; x_off / xfull_off as in ccmpi_fused_ag_gemm. */
 int ccmpi_fused_ag_gemm_ag(const ccmpi_dev_comm* comms, int nvr, size_t x_off, int ldx, size_t xfull_off,
                            const void* const* B, size_t yfull_off, int M, int N, int K, int ldb, int b_kn,
-                           int out_dtype, int flag_base, unsigned epoch, int num_sms, void* stream);
+                           int out_dtype, int flag_base, unsigned epoch, unsigned flag_target, int num_sms,
+                           void* stream);
 
 /* EXPERIMENTAL (compiled, not yet run on hardware in round 1): fused elementwise kernels of the
  * transformer-FC block (csrc/elementwise.cu), bf16 in / bf16 out, fp32 math, one pass over HBM each.

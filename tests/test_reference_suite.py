@@ -46,3 +46,36 @@ def test_reference_forward_file_on_8_ranks_with_empty_shards():
 
 def test_reference_backward_file_on_4_ranks():
     _run(4, "test_transformer_backward.py", "host", "2 passed")
+
+
+# ---- the same files on the DEVICE plane: every collective they make is a CUDA kernel over NVLink ----
+# (int64 SUM all-reduce over mp_comm / dp_comm, fp64 last-axis gather and reduce-scatter through the
+# strided all-gather / reduce-scatter kernels; NumPy arrays are staged through the symmetric heap)
+def _need_gpus(n):
+    from conftest import gpu_count
+    if gpu_count() < n:
+        pytest.skip(f"needs {n} GPUs")
+
+
+@pytest.mark.gpu
+def test_reference_get_info_file_on_8_gpus_device_plane():
+    _need_gpus(8)
+    _run(8, "test_get_info.py", "device", "2 passed")
+
+
+@pytest.mark.gpu
+def test_reference_forward_file_on_4_gpus_device_plane():
+    _need_gpus(4)
+    _run(4, "test_transformer_forward.py", "device", "2 passed")
+
+
+@pytest.mark.gpu
+def test_reference_backward_file_on_4_gpus_device_plane():
+    _need_gpus(4)
+    _run(4, "test_transformer_backward.py", "device", "2 passed")
+
+
+@pytest.mark.gpu
+def test_reference_forward_file_on_8_gpus_device_plane_with_empty_shards():
+    _need_gpus(8)
+    _run(8, "test_transformer_forward.py", "device", "2 passed")
