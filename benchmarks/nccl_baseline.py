@@ -4,8 +4,11 @@ after the other. Same layer math, same feature-sharded activation layout, same w
 same mixing / activation functions, same loss, same SGD as
 collective_communication_mpi_b200.models.TrainStep; only the communication + GEMM kernels differ.
 
-The gradient all-reduce is bucketed into one flat buffer and issued asynchronously on NCCL's
-stream as soon as backward has produced it, which is what DDP does.
+The gradient all-reduce is issued asynchronously on NCCL's stream as soon as backward has produced a
+gradient, which is what DDP does. No avoidable work is charged to this arm: the dW GEMMs write straight
+into their slice of the flat communication buffer (``torch.matmul(..., out=view)``: no packing copy, no
+accumulation pass), the 1/dp average is folded into the learning rate (no scaling pass), and like our
+arm it skips the input gradient of the first layer, which nobody consumes.
 """
 from __future__ import annotations
 
@@ -35,32 +38,36 @@ def _rscatter_last(y, group, mp):
 
 class _Column(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, w, group, mp):
+    def forward(ctx, x, w, group, mp, sink, idx):
         x_full = _gather_last(x, group, mp)
         ctx.save_for_backward(x_full, w)
-        ctx.group, ctx.mp = group, mp
+        ctx.group, ctx.mp, ctx.sink, ctx.idx = group, mp, sink, idx
         return x_full @ w
 
     @staticmethod
     def backward(ctx, dy):
         x_full, w = ctx.saved_tensors
-        dw = x_full.t() @ dy
-        dx = _rscatter_last(dy @ w.t(), ctx.group, ctx.mp)
-        return dx, dw, None, None
+        torch.matmul(x_full.t(), dy, out=ctx.sink.views[ctx.idx])
+        ctx.sink.grad_ready(ctx.idx)
+        dx = _rscatter_last(dy @ w.t(), ctx.group, ctx.mp) if ctx.needs_input_grad[0] else None
+        return dx, None, None, None, None, None
 
 
 class _Row(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, w, group, mp):
+    def forward(ctx, x, w, group, mp, sink, idx):
         ctx.save_for_backward(x, w)
-        ctx.group, ctx.mp = group, mp
+        ctx.group, ctx.mp, ctx.sink, ctx.idx = group, mp, sink, idx
         return _rscatter_last(x @ w, group, mp)
 
     @staticmethod
     def backward(ctx, dy):
         x, w = ctx.saved_tensors
         dy_full = _gather_last(dy.contiguous(), ctx.group, ctx.mp)
-        return dy_full @ w.t(), x.t() @ dy_full, None, None
+        torch.matmul(x.t(), dy_full, out=ctx.sink.views[ctx.idx])
+        ctx.sink.grad_ready(ctx.idx)
+        dx = dy_full @ w.t() if ctx.needs_input_grad[0] else None
+        return dx, None, None, None, None, None
 
 
 class NcclTrainStep:
@@ -90,45 +97,35 @@ class NcclTrainStep:
         self.w_qkv, self.w_o = w(h, 3 * h // mp, h), w(h // mp, h, h)
         self.w_1, self.w_2 = w(h, f // mp, h), w(f // mp, h, f)
         self.params = [self.w_qkv, self.w_o, self.w_1, self.w_2]
+        # the dW GEMMs write straight into their slice of one flat buffer, which is what NCCL reduces
         self.flat = torch.zeros(sum(p.numel() for p in self.params), dtype=torch.bfloat16, device=dev)
         self.views, off = [], 0
         for p in self.params:
             self.views.append(self.flat[off:off + p.numel()].view_as(p))
             off += p.numel()
-        # DDP-style overlap: a gradient is all-reduced (async, on NCCL's stream) as soon as
-        # autograd has produced it, while backward continues with the earlier layers
         self.pending = []
-        if dp > 1:
-            for v, p in zip(self.views, self.params):
-                p.register_post_accumulate_grad_hook(self._make_hook(v))
 
-    def _make_hook(self, view):
-        def hook(param):
-            view.copy_(param.grad)
-            self.pending.append(dist.all_reduce(view, group=self.dp_group, async_op=True))
-        return hook
+    def grad_ready(self, idx):
+        """DDP-style overlap: a gradient is all-reduced (async, on NCCL's stream) as soon as backward has
+        produced it, while backward continues with the earlier layers."""
+        if self.dp > 1:
+            self.pending.append(dist.all_reduce(self.views[idx], group=self.dp_group, async_op=True))
 
     def forward(self, x):
-        q, k, v = _Column.apply(x, self.w_qkv, self.mp_group, self.mp).chunk(3, dim=-1)
+        g, mp = self.mp_group, self.mp
+        q, k, v = _Column.apply(x, self.w_qkv, g, mp, self, 0).chunk(3, dim=-1)
         a = v * torch.sigmoid(q * k)
-        h = x + _Row.apply(a, self.w_o, self.mp_group, self.mp)
-        u = torch.nn.functional.gelu(_Column.apply(h, self.w_1, self.mp_group, self.mp), approximate="tanh")
-        return h + _Row.apply(u, self.w_2, self.mp_group, self.mp)
+        h = x + _Row.apply(a, self.w_o, g, mp, self, 1)
+        u = torch.nn.functional.gelu(_Column.apply(h, self.w_1, g, mp, self, 2), approximate="tanh")
+        return h + _Row.apply(u, self.w_2, g, mp, self, 3)
 
     def __call__(self, x, target):
-        for p in self.params:
-            p.grad = None
         y = self.forward(x)
         loss = torch.nn.functional.mse_loss(y.float(), target.float())
         loss.backward()
-        if self.dp > 1:
-            for work in self.pending:
-                work.wait()
-            self.pending.clear()
-            self.flat.mul_(1.0 / self.dp)
-        else:
-            for v, p in zip(self.views, self.params):
-                v.copy_(p.grad)
-        with torch.no_grad():
-            torch._foreach_add_([p.data for p in self.params], self.views, alpha=-self.lr)
+        for work in self.pending:
+            work.wait()
+        self.pending.clear()
+        with torch.no_grad():       # SUM over replicas, averaged by the step size
+            torch._foreach_add_([p.data for p in self.params], self.views, alpha=-self.lr / self.dp)
         return loss.detach()

@@ -28,7 +28,7 @@ DTYPE_SIZE = {F32: 4, BF16: 2, F16: 2, F64: 8, I32: 4, I64: 8, U8: 1}
 # ccmpi_op
 SUM, MIN, MAX = range(3)
 # ccmpi_ar_algo
-AR_AUTO, AR_ONESHOT, AR_TWOSHOT, AR_NVLS = range(4)
+AR_AUTO, AR_ONESHOT, AR_TWOSHOT, AR_NVLS, AR_TWOSHOT_GENERIC = range(5)
 
 ERR_UNSUPPORTED = -3
 

@@ -61,22 +61,20 @@ def barrier(comms, stream=None):
     N.count_launch()
 
 
-def _tight(flag) -> bool:
-    """Group-size-specialised reduction kernels (csrc/collectives_tight.cu): opt-in, not yet measured."""
-    return os.environ.get("CCMPI_COLL_TIGHT") == "1" if flag is None else bool(flag)
-
-
 def allreduce(comms, dtype: int, op: int, src_off: int, dst_off: int, count: int, *, tmp_off: int = 0,
               algo: int = N.AR_AUTO, scale: float = 1.0, out_dtype: int = -1, max_blocks: int = 0, stream=None,
               tight=None):
+    """``tight`` (benchmarks / tests): True forces the group-size-specialised two-shot kernel, False the
+    generic one; None lets the library choose (the specialised kernel whenever it applies)."""
     a, n = _arr(comms)
-    if algo == N.AR_TWOSHOT and out_dtype in (-1, dtype) and _tight(tight):
-        rc = N.device_lib().ccmpi_allreduce_twoshot_tight(a, n, dtype, op, src_off, dst_off, tmp_off, count,
-                                                          C.c_float(scale), max_blocks, _sp(stream))
-        if rc != N.ERR_UNSUPPORTED:
-            N.check(rc, "ccmpi_allreduce_twoshot_tight")
-            N.count_launch()
-            return
+    if tight is True and algo == N.AR_TWOSHOT:
+        N.check(N.device_lib().ccmpi_allreduce_twoshot_tight(a, n, dtype, op, src_off, dst_off, tmp_off, count,
+                                                             C.c_float(scale), max_blocks, _sp(stream)),
+                "ccmpi_allreduce_twoshot_tight")
+        N.count_launch()
+        return
+    if tight is False and algo == N.AR_TWOSHOT:
+        algo = N.AR_TWOSHOT_GENERIC
     N.check(N.device_lib().ccmpi_allreduce(a, n, algo, dtype, op, src_off, dst_off, tmp_off, count,
                                            C.c_float(scale), out_dtype, max_blocks, _sp(stream)), "ccmpi_allreduce")
     N.count_launch()
@@ -93,16 +91,17 @@ def allgather(comms, src_off: int, dst_off: int, rows: int, row_bytes: int, src_
 def reduce_scatter(comms, dtype: int, op: int, src_off: int, dst_off: int, rows: int, row_elems: int,
                    src_row_stride: int, dst_row_stride: int, *, use_mc: bool = True, max_blocks: int = 0,
                    stream=None, tight=None):
+    """``tight`` as in ``allreduce``: True / False force the specialised / generic peer-load kernel."""
     a, n = _arr(comms)
-    if _tight(tight) and (not use_mc or comms[0].size <= 2 or tight):
-        rc = N.device_lib().ccmpi_reduce_scatter_tight(a, n, dtype, op, src_off, dst_off, rows, row_elems, src_row_stride,
-                                                       dst_row_stride, max_blocks, _sp(stream))
-        if rc != N.ERR_UNSUPPORTED:
-            N.check(rc, "ccmpi_reduce_scatter_tight")
-            N.count_launch()
-            return
+    if tight is True:
+        N.check(N.device_lib().ccmpi_reduce_scatter_tight(a, n, dtype, op, src_off, dst_off, rows, row_elems,
+                                                          src_row_stride, dst_row_stride, max_blocks, _sp(stream)),
+                "ccmpi_reduce_scatter_tight")
+        N.count_launch()
+        return
+    mode = 2 if tight is False and not use_mc else int(use_mc)
     N.check(N.device_lib().ccmpi_reduce_scatter(a, n, dtype, op, src_off, dst_off, rows, row_elems,
-                                                src_row_stride, dst_row_stride, int(use_mc), max_blocks,
+                                                src_row_stride, dst_row_stride, mode, max_blocks,
                                                 _sp(stream)), "ccmpi_reduce_scatter")
     N.count_launch()
 

@@ -526,9 +526,18 @@ extern "C" int ccmpi_allreduce(const ccmpi_dev_comm* comms, int nvr, int algo, i
         const bool nvls_ok = lp.c[0].mc_heap && op == CCMPI_SUM && (dtype == CCMPI_F32 || dtype == CCMPI_BF16 || dtype == CCMPI_F16) &&
                              ((src_off | dst_off) & 15) == 0 && (bytes % 32) == 0;
         const bool vec_ok = ((src_off | dst_off | tmp_off) & 15) == 0 && bytes % 16 == 0;
+        // measured (profiles/r2_sweep_2gpu.jsonl, r1_sweep_8gpu.jsonl): one-shot up to 256 KB; between two
+        // GPUs NVLS wins up to ~8 MB and the P2P two-shot above; larger groups use NVLS throughout
         if (bytes <= 256 * 1024 || !vec_ok) algo = CCMPI_AR_ONESHOT;
-        else algo = (nvls_ok && lp.c[0].size > 2) ? CCMPI_AR_NVLS : CCMPI_AR_TWOSHOT;   // measured: P2P wins at n = 2
+        else if (nvls_ok && (lp.c[0].size > 2 || bytes <= (8u << 20))) algo = CCMPI_AR_NVLS;
+        else algo = CCMPI_AR_TWOSHOT;
     }
+    if (algo == CCMPI_AR_TWOSHOT && out_dtype == dtype) {
+        // group-size-specialised kernel (collectives_tight.cu) whenever it applies
+        rc = ccmpi_allreduce_twoshot_tight(comms, nvr, dtype, op, src_off, dst_off, tmp_off, count, scale, max_blocks, stream);
+        if (rc != CCMPI_ERR_UNSUPPORTED) return rc;
+    }
+    if (algo == CCMPI_AR_TWOSHOT_GENERIC) algo = CCMPI_AR_TWOSHOT;
     switch (dtype) {
         case CCMPI_F32: return allreduce_op<float>(lp, nvr, algo, op, src_off, dst_off, tmp_off, count, scale, out_dtype, dtype, max_blocks, st);
         case CCMPI_BF16: return allreduce_op<__nv_bfloat16>(lp, nvr, algo, op, src_off, dst_off, tmp_off, count, scale, out_dtype, dtype, max_blocks, st);
@@ -600,6 +609,16 @@ extern "C" int ccmpi_reduce_scatter(const ccmpi_dev_comm* comms, int nvr, int dt
     if (rc) return rc;
     if (rows == 0 || row_elems == 0) return CCMPI_OK;
     cudaStream_t st = (cudaStream_t)stream;
+    // use_mc: 0 = peer loads, 1 = NVLS when the group has a multicast mapping, 2 = peer loads with the kernel
+    // sized for any group (benchmarks). 0 -- and 1 without NVLS or between two GPUs, where peer loads measured
+    // faster -- take the group-size-specialised kernel when dtype / alignment allow (same bits, 1.2-1.7x).
+    if (use_mc == 0 || (use_mc == 1 && (lp.c[0].mc_heap == nullptr || lp.c[0].size <= 2))) {
+        rc = ccmpi_reduce_scatter_tight(comms, nvr, dtype, op, src_off, dst_off, rows, row_elems, src_row_stride,
+                                        dst_row_stride, max_blocks, stream);
+        if (rc != CCMPI_ERR_UNSUPPORTED) return rc;
+        use_mc = 0;
+    }
+    if (use_mc == 2) use_mc = 0;
     switch (dtype) {
         case CCMPI_F32: return rs_op<float>(lp, nvr, op, src_off, dst_off, rows, row_elems, src_row_stride, dst_row_stride, use_mc, max_blocks, st);
         case CCMPI_BF16: return rs_op<__nv_bfloat16>(lp, nvr, op, src_off, dst_off, rows, row_elems, src_row_stride, dst_row_stride, use_mc, max_blocks, st);

@@ -19,7 +19,7 @@ if CUDA:
 
 def sync():
     if CUDA:
-        sync()
+        torch.cuda.synchronize()
 
 
 TOK, K, NOUT = 512, 256 * n, 128 * n
