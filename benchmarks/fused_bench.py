@@ -21,6 +21,7 @@ os.environ.setdefault("CCMPI_TRANSPORT", "device")
 from mpi4py import MPI  # noqa: E402
 from collective_communication_mpi_b200.ops import fused as F  # noqa: E402
 from collective_communication_mpi_b200.ops.gemm import gemm  # noqa: E402
+from collective_communication_mpi_b200.utils import ktrace as KT  # noqa: E402
 
 PEAK_TFLOPS = 1670.0   # MEASURED_PEAKS.json bf16 burst
 LINK_GBS = 770.0       # measured peer copy, per direction
@@ -81,6 +82,11 @@ def main():
         link = M * (K // n) * 2 * (n - 1)     # bytes this rank must receive
         rows.append(dict(op=name, M=M, N=Nl, K=K, fused_ms=t_fused, our_gemm_ms=t_gemm, cublas_ms=t_cublas,
                          nccl_coll_ms=t_coll, nccl_cublas_ms=t_base, flops=flops, link_bytes=link))
+        if KT.enabled():        # CCMPI_KERNEL_TRACE=1: where the fused kernel's warp roles waited, next to the plain GEMM's
+            flush.zero_(); comm.Barrier(); op(xin, w, b_kn=b_kn, out=out)
+            rows[-1]["trace_fused"] = KT.summary(KT.last(op))
+            tb = KT.new_buffer(); flush.zero_(); gemm(xfull, w, b_kn=b_kn, out=out, trace=tb)
+            rows[-1]["trace_gemm"] = KT.summary(tb)
     # ---- GEMM -> reduce-scatter: forward of row layers, backward-dx of column layers --------
     cases = [(f"gemm_rs fwd {nm}", din // n, dout, True) for nm, din, dout in rshapes] + \
             [(f"gemm_rs bwd-dx {nm}", dout // n, din, False) for nm, din, dout in shapes]
@@ -104,6 +110,11 @@ def main():
         link = M * (Nf // n) * 2 * (n - 1)
         rows.append(dict(op=name, M=M, N=Nf, K=K, fused_ms=t_fused, our_gemm_ms=t_gemm, cublas_ms=t_cublas,
                          nccl_coll_ms=t_coll, nccl_cublas_ms=t_base, flops=flops, link_bytes=link))
+        if KT.enabled():
+            flush.zero_(); comm.Barrier(); op(a, w, b_kn=b_kn, out=out)
+            rows[-1]["trace_fused"] = KT.summary(KT.last(op))
+            tb = KT.new_buffer(); flush.zero_(); gemm(a, w, b_kn=b_kn, out=full, trace=tb)
+            rows[-1]["trace_gemm"] = KT.summary(tb)
     if rank == 0:
         os.makedirs("gpurun_out", exist_ok=True)
         with open(f"gpurun_out/fused_bench_{n}gpu.jsonl", "w") as f:

@@ -165,6 +165,10 @@ def _declare_device(lib):
         "ccmpi_put_signal": (i, [P(DevComm), i, i, sz, sz, sz, i, vp]),
         "ccmpi_wait_signal": (i, [P(DevComm), i, i, i, vp]),
         "ccmpi_gemm_bf16": (i, [vp, vp, vp, i, i, i, i, i, i, i, i, i, i, i, vp]),
+        "ccmpi_gemm_bf16_ex": (i, [vp, vp, vp, i, i, i, i, i, i, i, i, i, i, i, vp, vp, i64, vp, i, vp]),
+        "ccmpi_fused_ag_gemm_ex": (i, [P(DevComm), i, sz, i, sz, PV, PV, i, i, i, i, i, i, i, i, u, u, i, PV, PV, i64, vp, i,
+                                       i, i, vp]),
+        "ccmpi_fused_gemm_rs_ex": (i, [P(DevComm), i, PV, PV, sz, PV, i, i, i, i, i, i, i, i, i, i, u, PV, i64, vp, i, vp]),
     }
     for name, (res, args) in sigs.items():
         fn = getattr(lib, name)

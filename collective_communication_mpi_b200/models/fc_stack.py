@@ -21,7 +21,7 @@ from torch import nn
 
 from ..ops import elementwise as EW
 from ..parallel.dp import GradSink, sgd_step
-from ..parallel.tp_layers import ColumnParallelLinear, RowParallelLinear
+from ..parallel.tp_layers import ColumnParallelLinear, RowParallelLinear, attn_block, mlp_block
 
 
 class TransformerFCBlock(nn.Module):
@@ -35,11 +35,15 @@ class TransformerFCBlock(nn.Module):
         self.fc2 = RowParallelLinear(mp_comm, tokens, ffn_mult * hidden, hidden, seed=seed + 4, num_comm_ctas=num_comm_ctas)
         # one-pass gate / GELU kernels with hand-written backward (CCMPI_FUSED_ELEMENTWISE=0: eager op chains)
         self.fused_elementwise = EW.enabled()
+        # ... and GELU / GELU' / the residual adds inside the GEMM epilogues (CCMPI_FUSED_EPILOGUE=0: separate kernels)
+        self.fused_epilogue = self.fused_elementwise and os.environ.get("CCMPI_FUSED_EPILOGUE", "1") != "0"
 
     def tp_layers(self) -> List[nn.Module]:
         return [self.fc_qkv, self.fc_o, self.fc1, self.fc2]
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if self.fused_epilogue:
+            return mlp_block(self.fc1, self.fc2, attn_block(self.fc_qkv, self.fc_o, x))
         if self.fused_elementwise:
             h = x + self.fc_o(EW.gate(self.fc_qkv(x)))
             return h + self.fc2(EW.gelu(self.fc1(h)))

@@ -27,7 +27,9 @@ from typing import List, Optional, Sequence
 import torch
 
 from .. import _native as N
+from ..utils import ktrace as KT
 from .collectives import _arr, _sp
+from .gemm import EPI_GELU_DUAL, epilogue_args
 
 _OUT = {torch.bfloat16: N.BF16, torch.float32: N.F32}
 
@@ -41,16 +43,23 @@ def _ptrs(tensors: Sequence[Optional[torch.Tensor]]):
 # -------------------------------------------------------------------------------------------------
 def ag_gemm_raw(comms, x_off: int, ldx: int, xfull_off: int, B: List[torch.Tensor], Cout: List[torch.Tensor],
                 M: int, Nn: int, K: int, *, b_kn: bool, flag_base: int, epoch: int, flag_target: int = 0,
-                num_comm_ctas: int = 0, num_sms: int = 0, use_mc: bool = True, stream=None):
+                num_comm_ctas: int = 0, num_sms: int = 0, use_mc: bool = True, stream=None,
+                epi_op: int = 0, epi_in: Optional[List[torch.Tensor]] = None,
+                epi_out2: Optional[List[torch.Tensor]] = None, trace: Optional[torch.Tensor] = None):
     """``flag_target``: value the ready flags must reach for this launch (running sum of ``ag_ctas``
     over the launches on these flags); 0 = ``epoch`` times this launch's CTA count, which is right only
     when every launch on the flags has the same shape and SM budget (the tests' case)."""
     a, n = _arr(comms)
-    rc = N.device_lib().ccmpi_fused_ag_gemm(a, n, x_off, ldx, xfull_off, _ptrs(B), _ptrs(Cout), M, Nn, K,
-                                            B[0].stride(0), Cout[0].stride(0), int(b_kn), _OUT[Cout[0].dtype],
-                                            flag_base, epoch, flag_target & 0xFFFFFFFF, num_comm_ctas, num_sms,
-                                            int(use_mc), _sp(stream))
-    N.check(rc, "ccmpi_fused_ag_gemm")
+    e_t = epi_in if epi_in is not None else epi_out2
+    rc = N.device_lib().ccmpi_fused_ag_gemm_ex(a, n, x_off, ldx, xfull_off, _ptrs(B), _ptrs(Cout), M, Nn, K,
+                                               B[0].stride(0), Cout[0].stride(0), int(b_kn), _OUT[Cout[0].dtype],
+                                               flag_base, epoch, flag_target & 0xFFFFFFFF, epi_op,
+                                               _ptrs(epi_in) if epi_in is not None else None,
+                                               _ptrs(epi_out2) if epi_out2 is not None else None,
+                                               e_t[0].stride(0) if e_t is not None else 0,
+                                               C.c_void_p(trace.data_ptr() if trace is not None else None),
+                                               num_comm_ctas, num_sms, int(use_mc), _sp(stream))
+    N.check(rc, "ccmpi_fused_ag_gemm_ex")
     N.count_launch()
 
 
@@ -62,12 +71,18 @@ def ag_ctas(kind: int, M: int, Nn: int, nvr: int, num_sms: int) -> int:
 
 def gemm_rs_raw(comms, A: List[torch.Tensor], B: List[torch.Tensor], slots_off: int, Cout: List[torch.Tensor],
                 M: int, Nn: int, K: int, *, a_km: bool = False, b_kn: bool, flag_base: int, epoch: int,
-                num_sms: int = 0, stream=None):
+                num_sms: int = 0, stream=None, residual: Optional[List[torch.Tensor]] = None,
+                trace: Optional[torch.Tensor] = None):
+    """``residual``: one ``[M, Nn/n]`` bf16 tensor per rank, added to the reduced result by the reducer."""
     a, n = _arr(comms)
-    rc = N.device_lib().ccmpi_fused_gemm_rs(a, n, _ptrs(A), _ptrs(B), slots_off, _ptrs(Cout), M, Nn, K,
-                                            A[0].stride(0), B[0].stride(0), Cout[0].stride(0), int(a_km), int(b_kn),
-                                            _OUT[Cout[0].dtype], flag_base, epoch, num_sms, _sp(stream))
-    N.check(rc, "ccmpi_fused_gemm_rs")
+    rc = N.device_lib().ccmpi_fused_gemm_rs_ex(a, n, _ptrs(A), _ptrs(B), slots_off, _ptrs(Cout), M, Nn, K,
+                                               A[0].stride(0), B[0].stride(0), Cout[0].stride(0), int(a_km), int(b_kn),
+                                               _OUT[Cout[0].dtype], flag_base, epoch,
+                                               _ptrs(residual) if residual is not None else None,
+                                               residual[0].stride(0) if residual is not None else 0,
+                                               C.c_void_p(trace.data_ptr() if trace is not None else None),
+                                               num_sms, _sp(stream))
+    N.check(rc, "ccmpi_fused_gemm_rs_ex")
     N.count_launch()
 
 
@@ -164,12 +179,15 @@ class AllGatherGemm:
         return self.xfull[self.epoch & 1][1]
 
     def __call__(self, x: torch.Tensor, w: torch.Tensor, *, b_kn: bool = True, out: Optional[torch.Tensor] = None,
-                 out_dtype=torch.bfloat16, num_sms: int = 0, stream=None) -> torch.Tensor:
+                 out_dtype=torch.bfloat16, num_sms: int = 0, stream=None, gelu_out=None, dgelu_of=None, add=None):
+        """``gelu_out`` / ``dgelu_of`` / ``add``: elementwise work fused into the epilogue, as in
+        ``ops.gemm.gemm``; with ``gelu_out`` the call returns ``(y, gelu(y))``."""
         if x.data_ptr() != self.x.data_ptr():
             self.x.copy_(x.reshape(self.M, self.chunk))
         Nn = w.shape[1] if b_kn else w.shape[0]
         if out is None:
             out = torch.empty((self.M, Nn), dtype=out_dtype, device=w.device)
+        op, e_in, e_out2, _ = epilogue_args(self.M, Nn, w.device, gelu_out=gelu_out, dgelu_of=dgelu_of, add=add)
         self.epoch += 1
         # every member launches the same shape with the same SM budget, so this rank's CTA count is
         # also the number of contributions its flags receive from each peer
@@ -177,8 +195,10 @@ class AllGatherGemm:
         xf_off = self.xfull[self.epoch & 1][0]
         ag_gemm_raw(self.ctx.dev.comms, self.x_off, self.chunk, xf_off, [w], [out], self.M, Nn, self.K, b_kn=b_kn,
                     flag_base=self.flag_base, epoch=self.epoch, flag_target=self.flag_total,
-                    num_comm_ctas=self.num_comm_ctas, num_sms=num_sms, use_mc=self.use_mc, stream=stream)
-        return out
+                    num_comm_ctas=self.num_comm_ctas, num_sms=num_sms, use_mc=self.use_mc, stream=stream,
+                    epi_op=op, epi_in=[e_in] if e_in is not None else None,
+                    epi_out2=[e_out2] if e_out2 is not None else None, trace=KT.buffer_for(self, "ag_gemm"))
+        return (out, e_out2) if op == EPI_GELU_DUAL else out
 
 
 class GemmReduceScatter:
@@ -194,13 +214,19 @@ class GemmReduceScatter:
         self.epoch = 0
 
     def __call__(self, a: torch.Tensor, b: torch.Tensor, *, a_km: bool = False, b_kn: bool = False,
-                 out: Optional[torch.Tensor] = None, num_sms: int = 0, stream=None) -> torch.Tensor:
+                 out: Optional[torch.Tensor] = None, num_sms: int = 0, stream=None,
+                 add: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """``add``: a ``[M, N/n]`` bf16 tensor added to the reduced result by the reducer (residual
+        connection / gradient accumulation) before the single rounding."""
         K = a.shape[0] if a_km else a.shape[1]
         if out is None:
             out = torch.empty((self.M, self.chunk), dtype=self.dtype, device=a.device)
+        if add is not None and (add.dtype != torch.bfloat16 or tuple(add.shape) != (self.M, self.chunk) or add.stride(1) != 1):
+            raise ValueError(f"add must be a bfloat16 [{self.M}, {self.chunk}] tensor with unit column stride")
         self.epoch += 1
         gemm_rs_raw(self.ctx.dev.comms, [a], [b], self.slots[self.epoch & 1][0], [out], self.M, self.N, K, a_km=a_km,
-                    b_kn=b_kn, flag_base=self.flag_base, epoch=self.epoch, num_sms=num_sms, stream=stream)
+                    b_kn=b_kn, flag_base=self.flag_base, epoch=self.epoch, num_sms=num_sms, stream=stream,
+                    residual=[add] if add is not None else None, trace=KT.buffer_for(self, "gemm_rs"))
         return out
 
 

@@ -34,14 +34,44 @@ def _check_operand(t: torch.Tensor, name: str):
         raise ValueError(f"{name} needs 16-byte aligned rows (row stride {t.stride(0)} elements)")
 
 
+EPI_NONE, EPI_GELU_DUAL, EPI_MUL_DGELU, EPI_ADD = range(4)      # EpiOp in csrc/gemm_tcgen05.cuh
+
+
+def epilogue_args(M: int, Nn: int, device, *, gelu_out=None, dgelu_of=None, add=None):
+    """Translate the three fused-epilogue keywords into ``(op, in_tensor, out2_tensor, ld)``.
+
+    ``gelu_out``  a ``[M, N]`` bf16 tensor (or ``True`` to allocate one): the GEMM writes its result AND
+                  ``gelu(result)`` there -- forward through an activation without a pass over HBM
+    ``dgelu_of``  the saved pre-activation ``u``: result = ``(a @ b) * gelu'(u)`` -- backward through it
+    ``add``       a ``[M, N]`` bf16 tensor: result = ``a @ b + add`` -- residual / gradient accumulation
+    """
+    given = [(EPI_GELU_DUAL, gelu_out), (EPI_MUL_DGELU, dgelu_of), (EPI_ADD, add)]
+    given = [(op, t) for op, t in given if t is not None and t is not False]
+    if not given:
+        return EPI_NONE, None, None, 0
+    if len(given) > 1:
+        raise ValueError("at most one of gelu_out / dgelu_of / add")
+    op, t = given[0]
+    if t is True:
+        t = torch.empty((M, Nn), dtype=torch.bfloat16, device=device)
+    if t.dtype != torch.bfloat16 or t.dim() != 2 or tuple(t.shape) != (M, Nn) or t.stride(1) != 1 or t.stride(0) % 8:
+        raise ValueError(f"epilogue operand must be a bfloat16 [{M}, {Nn}] tensor with unit column stride and 16-byte rows")
+    if Nn % 32:
+        raise ValueError("fused epilogues need N % 32 == 0")
+    return (op, None, t, t.stride(0)) if op == EPI_GELU_DUAL else (op, t, None, t.stride(0))
+
+
 def gemm(a: torch.Tensor, b: torch.Tensor, *, a_km: bool = False, b_kn: bool = False,
          out: torch.Tensor | None = None, out_dtype: torch.dtype = torch.bfloat16,
-         accumulate: bool = False, num_sms: int = 0, stream=None) -> torch.Tensor:
+         accumulate: bool = False, num_sms: int = 0, stream=None, gelu_out=None, dgelu_of=None, add=None,
+         trace: torch.Tensor | None = None):
     """``C[M,N] = A[M,K] @ B[K,N]`` with fp32 accumulation in tensor memory.
 
     ``a`` is stored ``[M,K]`` (or ``[K,M]`` when ``a_km``); ``b`` is stored ``[N,K]`` (the
     ``nn.Linear`` weight layout) or ``[K,N]`` when ``b_kn``. ``num_sms`` caps the persistent grid
-    (leave SMs free for a communication kernel running alongside).
+    (leave SMs free for a communication kernel running alongside). ``gelu_out`` / ``dgelu_of`` /
+    ``add`` fuse elementwise work into the epilogue (``epilogue_args``); with ``gelu_out`` the call
+    returns ``(C, gelu(C))``. ``trace``: a ``utils.ktrace`` buffer the kernel fills.
     """
     _check_operand(a, "a")
     _check_operand(b, "b")
@@ -65,15 +95,19 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_km: bool = False, b_kn: bool = F
         raise TypeError("GEMM output must be bfloat16 or float32")
     if accumulate and out_dtype != torch.float32:
         raise TypeError("accumulate=True needs a float32 output")
+    op, e_in, e_out2, e_ld = epilogue_args(M, Nn, a.device, gelu_out=gelu_out, dgelu_of=dgelu_of, add=add)
     lib = N.device_lib()
-    rc = lib.ccmpi_gemm_bf16(
+    rc = lib.ccmpi_gemm_bf16_ex(
         C.c_void_p(a.data_ptr()), C.c_void_p(b.data_ptr()), C.c_void_p(out.data_ptr()),
         M, Nn, K, a.stride(0), b.stride(0), out.stride(0), int(a_km), int(b_kn),
-        N.BF16 if out_dtype == torch.bfloat16 else N.F32, int(accumulate), int(num_sms),
+        N.BF16 if out_dtype == torch.bfloat16 else N.F32, int(accumulate), op,
+        C.c_void_p(e_in.data_ptr() if e_in is not None else None),
+        C.c_void_p(e_out2.data_ptr() if e_out2 is not None else None), e_ld,
+        C.c_void_p(trace.data_ptr() if trace is not None else None), int(num_sms),
         C.c_void_p(_stream_ptr(stream)))
-    N.check(rc, "ccmpi_gemm_bf16")
+    N.check(rc, "ccmpi_gemm_bf16_ex")
     N.count_launch()
-    return out
+    return (out, e_out2) if op == EPI_GELU_DUAL else out
 
 
 def matmul_nn(x: torch.Tensor, w: torch.Tensor, **kw) -> torch.Tensor:

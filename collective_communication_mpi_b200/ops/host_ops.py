@@ -17,20 +17,43 @@ from typing import Optional
 import torch
 
 
+def _epilogue(c: torch.Tensor, out_dtype, gelu_out, dgelu_of, add):
+    """The fused epilogues of csrc/gemm_kernel.cuh on an fp32 product ``c``: returns ``(result, gelu or None)``."""
+    from .elementwise import gelu_reference
+    if dgelu_of is not None:
+        from .elementwise import gelu_backward_reference
+        c = gelu_backward_reference(c, dgelu_of.float()).float()
+    if add is not None:
+        c = c + add.float()
+    y = c.to(out_dtype)
+    if gelu_out is None or gelu_out is False:
+        return y, None
+    g = gelu_reference(y)           # from the rounded pre-activation, like the kernel
+    if gelu_out is not True:
+        gelu_out.copy_(g)
+        g = gelu_out
+    return y, g
+
+
 def gemm(a: torch.Tensor, b: torch.Tensor, *, a_km: bool = False, b_kn: bool = False, out: Optional[torch.Tensor] = None,
-         out_dtype: torch.dtype = torch.bfloat16, accumulate: bool = False, num_sms: int = 0, stream=None) -> torch.Tensor:
+         out_dtype: torch.dtype = torch.bfloat16, accumulate: bool = False, num_sms: int = 0, stream=None,
+         gelu_out=None, dgelu_of=None, add=None, trace=None):
     """Same contract as ``ops.gemm.gemm``: ``a`` is ``[M,K]`` (``[K,M]`` with ``a_km``), ``b`` is
-    ``[N,K]`` (``[K,N]`` with ``b_kn``); fp32 accumulation, result cast to ``out_dtype``."""
+    ``[N,K]`` (``[K,N]`` with ``b_kn``); fp32 accumulation, result cast to ``out_dtype``; the fused
+    epilogue keywords are applied in fp32 before that cast."""
     A = a.float().t() if a_km else a.float()
     B = b.float() if b_kn else b.float().t()
     c = A @ B
-    if out is None:
-        return c.to(out_dtype)
-    if accumulate:
-        out.add_(c.to(out.dtype))
-    else:
-        out.copy_(c.to(out.dtype))
-    return out
+    if out is not None:
+        out_dtype = out.dtype
+    y, g = _epilogue(c, out_dtype, gelu_out, dgelu_of, add)
+    if out is not None:
+        if accumulate:
+            out.add_(y)
+        else:
+            out.copy_(y)
+        y = out
+    return (y, g) if g is not None else y
 
 
 def matmul_tn(x: torch.Tensor, dy: torch.Tensor, **kw) -> torch.Tensor:
@@ -54,9 +77,10 @@ class AllGatherGemm:
     def gathered(self) -> torch.Tensor:
         return self._gathered
 
-    def __call__(self, x, w, *, b_kn: bool = True, out=None, out_dtype=torch.bfloat16, num_sms: int = 0, stream=None):
+    def __call__(self, x, w, *, b_kn: bool = True, out=None, out_dtype=torch.bfloat16, num_sms: int = 0, stream=None,
+                 gelu_out=None, dgelu_of=None, add=None):
         self._gathered = self.comm.gather_last_axis(x.reshape(self.M, -1).contiguous())
-        return gemm(self._gathered, w, b_kn=b_kn, out=out, out_dtype=out_dtype)
+        return gemm(self._gathered, w, b_kn=b_kn, out=out, out_dtype=out_dtype, gelu_out=gelu_out, dgelu_of=dgelu_of, add=add)
 
 
 class GemmReduceScatter:
@@ -65,9 +89,12 @@ class GemmReduceScatter:
     def __init__(self, comm, M: int, Nfull: int, *, dtype=torch.bfloat16):
         self.comm, self.M, self.N, self.dtype = comm, M, Nfull, dtype
 
-    def __call__(self, a, b, *, a_km: bool = False, b_kn: bool = False, out=None, num_sms: int = 0, stream=None):
+    def __call__(self, a, b, *, a_km: bool = False, b_kn: bool = False, out=None, num_sms: int = 0, stream=None, add=None):
         part = gemm(a, b, a_km=a_km, b_kn=b_kn, out_dtype=torch.float32)
-        red = self.comm.reduce_scatter_last_axis(part).to(self.dtype)
+        red = self.comm.reduce_scatter_last_axis(part)
+        if add is not None:
+            red = red.float() + add.float()
+        red = red.to(self.dtype)
         if out is not None:
             out.copy_(red)
             return out

@@ -10,10 +10,11 @@
 // 16-byte vectors (8 bf16), fp32 math, one rounding at the end, grid = a few CTAs per SM looping
 // with a grid stride.
 //
-// EXPERIMENTAL in round 1: written after the round's GPU budget was spent; compiled, not yet run on
-// hardware, opt-in (CCMPI_FUSED_ELEMENTWISE=1) and tested only with CCMPI_TEST_UNVERIFIED=1.
+// GELU forward / backward also exist as GEMM epilogues (gemm_kernel.cuh), which is what the models use;
+// the kernels here serve activations that do not come straight out of a GEMM.
 #include <cuda_bf16.h>
 
+#include "act.cuh"
 #include "host_common.h"
 
 namespace ew {
@@ -91,14 +92,6 @@ __global__ void __launch_bounds__(THREADS) gate_bwd_kernel(const __nv_bfloat16* 
     }
 }
 
-constexpr float kGeluC = 0.7978845608028654f;   // sqrt(2 / pi)
-constexpr float kGeluA = 0.044715f;
-
-__device__ __forceinline__ float tanh_fast(float x) {
-    // tanh(x) = 1 - 2 / (exp(2x) + 1); exact enough in fp32 for a bf16 result, saturates cleanly
-    const float e = __expf(2.0f * x);
-    return 1.0f - 2.0f / (e + 1.0f);
-}
 
 __global__ void __launch_bounds__(THREADS) gelu_fwd_kernel(const __nv_bfloat16* __restrict__ u, __nv_bfloat16* __restrict__ y,
                                                            long long nvec) {
@@ -106,10 +99,7 @@ __global__ void __launch_bounds__(THREADS) gelu_fwd_kernel(const __nv_bfloat16* 
         float x[8], o[8];
         unpack8(ldg16(u + i * 8), x);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            const float th = tanh_fast(kGeluC * (x[e] + kGeluA * x[e] * x[e] * x[e]));
-            o[e] = 0.5f * x[e] * (1.0f + th);
-        }
+        for (int e = 0; e < 8; ++e) o[e] = act::gelu(x[e]);
         stg16(y + i * 8, pack8(o));
     }
 }
@@ -121,12 +111,7 @@ __global__ void __launch_bounds__(THREADS) gelu_bwd_kernel(const __nv_bfloat16* 
         unpack8(ldg16(u + i * 8), x);
         unpack8(ldg16(dy + i * 8), g);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            const float x2 = x[e] * x[e];
-            const float th = tanh_fast(kGeluC * (x[e] + kGeluA * x2 * x[e]));
-            const float dth = (1.0f - th * th) * kGeluC * (1.0f + 3.0f * kGeluA * x2);
-            o[e] = g[e] * (0.5f * (1.0f + th) + 0.5f * x[e] * dth);
-        }
+        for (int e = 0; e < 8; ++e) o[e] = g[e] * act::gelu_grad(x[e]);
         stg16(du + i * 8, pack8(o));
     }
 }

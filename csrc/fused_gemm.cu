@@ -35,6 +35,16 @@ extern "C" int ccmpi_fused_ag_gemm(const ccmpi_dev_comm* comms, int nvr, size_t 
                                    const void* const* B, void* const* C, int M, int N, int K, int ldb, int ldc,
                                    int b_kn, int out_dtype, int flag_base, unsigned epoch, unsigned flag_target,
                                    int num_comm_ctas, int num_sms, int use_mc, void* stream) {
+    return ccmpi_fused_ag_gemm_ex(comms, nvr, x_off, ldx, xfull_off, B, C, M, N, K, ldb, ldc, b_kn, out_dtype, flag_base,
+                                  epoch, flag_target, 0, nullptr, nullptr, 0, nullptr, num_comm_ctas, num_sms, use_mc, stream);
+}
+
+// ... with a fused elementwise epilogue (EpiOp; epi_in / epi_out2: one pointer per rank, or NULL) and a device trace
+extern "C" int ccmpi_fused_ag_gemm_ex(const ccmpi_dev_comm* comms, int nvr, size_t x_off, int ldx, size_t xfull_off,
+                                      const void* const* B, void* const* C, int M, int N, int K, int ldb, int ldc,
+                                      int b_kn, int out_dtype, int flag_base, unsigned epoch, unsigned flag_target,
+                                      int epi_op, const void* const* epi_in, void* const* epi_out2, long long epi_ld,
+                                      void* trace, int num_comm_ctas, int num_sms, int use_mc, void* stream) {
     int rc = check_shapes(M, N, K, ldx, ldb, ldc, out_dtype);
     if (rc) return rc;
     const int n = comms ? comms[0].size : 0;
@@ -80,6 +90,9 @@ extern "C" int ccmpi_fused_ag_gemm(const ccmpi_dev_comm* comms, int nvr, size_t 
         static const int env_push_first = [] { const char* e = getenv("CCMPI_AG_PUSH_FIRST"); return e ? atoi(e) : 0; }();
         rp.aux1 = (use_mc ? 1 : 0) | (env_push_first ? 4 : 0);
         rp.aux2 = 1;
+        rc = set_epilogue(rp, epi_op, epi_in ? epi_in[v] : nullptr, epi_out2 ? epi_out2[v] : nullptr, epi_ld, N, out_dtype, pairs);
+        if (rc) return rc;
+        rp.trace = pairs ? (unsigned long long*)trace : nullptr;
     }
     if (pairs)
         return dispatch2<AgKPolicy>(lp, BN, false, b_kn != 0, out_dtype, (gemm_ctas + ncomm) * nvr, (cudaStream_t)stream, nvr > 1);
@@ -106,7 +119,8 @@ namespace {
 template <typename Policy>
 int gemm_scatter(const ccmpi_dev_comm* comms, int nvr, const void* const* A, const void* const* B, size_t slots_off,
                  void* const* C, size_t out_off, int M, int N, int K, int lda, int ldb, int ldc, int a_km, int b_kn,
-                 int out_dtype, int flag_base, unsigned epoch, int num_sms, int use_mc, void* stream) {
+                 int out_dtype, int flag_base, unsigned epoch, int num_sms, int use_mc, void* stream,
+                 const void* const* residual = nullptr, long long res_ld = 0, void* trace = nullptr) {
     int rc = check_shapes(M, N, K, lda, ldb, ldc, out_dtype);
     if (rc) return rc;
     const int n = comms ? comms[0].size : 0;
@@ -142,6 +156,14 @@ int gemm_scatter(const ccmpi_dev_comm* comms, int nvr, const void* const* A, con
         rp.epoch = epoch;
         rp.aux0 = BN;
         rp.aux1 = use_mc;
+        if (residual) {     // added to the reduced tile by the reducer (RsNPolicy::reduce_tile)
+            CCMPI_REQUIRE(out_dtype == CCMPI_BF16 && residual[v] != nullptr && res_ld % 8 == 0 && res_ld >= chunk,
+                          "reduce-scatter residual: bf16 output, non-null pointer, row stride %% 8 == 0 and >= N/n");
+            rp.epi_op = EPI_ADD;
+            rp.epi_in = residual[v];
+            rp.epi_ld = res_ld;
+        }
+        rp.trace = pairs ? (unsigned long long*)trace : nullptr;
     }
     if (pairs) return dispatch2<Policy>(lp, BN, a_km != 0, b_kn != 0, out_dtype, per_rank * nvr, (cudaStream_t)stream, nvr > 1);
     return dispatch<Policy>(lp, BN, a_km != 0, b_kn != 0, out_dtype, per_rank * nvr, (cudaStream_t)stream, nvr > 1);
@@ -156,6 +178,16 @@ extern "C" int ccmpi_fused_gemm_rs(const ccmpi_dev_comm* comms, int nvr, const v
     CCMPI_REQUIRE(C != nullptr, "gemm_rs needs an output pointer per rank");
     return gemm_scatter<RsNPolicy>(comms, nvr, A, B, slots_off, C, 0, M, N, K, lda, ldb, ldc, a_km, b_kn, out_dtype,
                                    flag_base, epoch, num_sms, 0, stream);
+}
+
+// ... plus `residual` ([M][N/n] bf16 per rank, row stride res_ld) added to the reduced result, and a device trace
+extern "C" int ccmpi_fused_gemm_rs_ex(const ccmpi_dev_comm* comms, int nvr, const void* const* A, const void* const* B,
+                                      size_t slots_off, void* const* C, int M, int N, int K, int lda, int ldb, int ldc,
+                                      int a_km, int b_kn, int out_dtype, int flag_base, unsigned epoch,
+                                      const void* const* residual, long long res_ld, void* trace, int num_sms, void* stream) {
+    CCMPI_REQUIRE(C != nullptr, "gemm_rs needs an output pointer per rank");
+    return gemm_scatter<RsNPolicy>(comms, nvr, A, B, slots_off, C, 0, M, N, K, lda, ldb, ldc, a_km, b_kn, out_dtype,
+                                   flag_base, epoch, num_sms, 0, stream, residual, res_ld, trace);
 }
 
 // GEMM -> all-reduce: out[M][N] (symmetric, row stride N) = sum over ranks s of A_s * B_s, on every rank

@@ -267,6 +267,7 @@ struct AgKPolicy : PlainPolicy {
 // ================================================================================================
 //   aux0 : the launch's BN (tile width), so one policy type serves every tile shape
 struct RsNPolicy : PlainPolicy {
+    static constexpr bool kEpiOps = false;   // own store: no fused elementwise epilogue
     static constexpr bool kCommCtas = false;
     static constexpr bool kStagedStore = true;
     static constexpr bool kNeedsStaging = true;
@@ -335,8 +336,12 @@ struct RsNPolicy : PlainPolicy {
         const int rows = min(BM, p.M - m_blk * BM);
         const OutT* slots = reinterpret_cast<const OutT*>(c.heap[c.rank] + p.off1);
         constexpr int U = 4;   // vectors per thread in flight (x n sources): the slots sit in HBM / far L2
+        // EPI_ADD (bf16 reduce-scatter only): the residual / incoming gradient [M][chunk] (row stride
+        // epi_ld) is added to the reduced tile on its way out, in fp32, before the one rounding
+        const bool add_res = !BROADCAST && sizeof(OutT) == 2 && p.epi_op == EPI_ADD;
         for (int v0 = epi_tid; v0 < rows * VPR; v0 += U * EPI_THREADS) {
             uint4 raw[U][CCMPI_MAX_RANKS];
+            uint4 res[U];
 #pragma unroll
             for (int u = 0; u < U; ++u) {
                 const int v = v0 + u * EPI_THREADS;
@@ -346,6 +351,8 @@ struct RsNPolicy : PlainPolicy {
 #pragma unroll
                     for (int s = 0; s < CCMPI_MAX_RANKS; ++s)
                         if (s < c.size) raw[u][s] = ptx::ld_v4(slots + ((size_t)s * p.M + row) * p.chunk + lcol);
+                    if (add_res)
+                        res[u] = ptx::ld_v4(reinterpret_cast<const __nv_bfloat16*>(p.epi_in) + (size_t)row * p.epi_ld + lcol);
                 }
             }
 #pragma unroll
@@ -375,6 +382,15 @@ struct RsNPolicy : PlainPolicy {
                 }
                 uint4 out;
                 if constexpr (sizeof(OutT) == 2) {
+                    if (add_res) {
+                        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&res[u]);
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const float2 f = __bfloat1622float2(h[e]);
+                            acc[2 * e] += f.x;
+                            acc[2 * e + 1] += f.y;
+                        }
+                    }
                     out.x = pack_bf16(__float_as_uint(acc[0]), __float_as_uint(acc[1]));
                     out.y = pack_bf16(__float_as_uint(acc[2]), __float_as_uint(acc[3]));
                     out.z = pack_bf16(__float_as_uint(acc[4]), __float_as_uint(acc[5]));
@@ -475,6 +491,7 @@ struct ArPolicy : RsNPolicy {
 // overlaps the first tile's mainloop.
 // ================================================================================================
 struct AgOutPolicy : PlainPolicy {
+    static constexpr bool kEpiOps = false;   // own store: no fused elementwise epilogue
     static constexpr bool kStagedStore = true;
     static constexpr bool kNeedsStaging = true;
 

@@ -151,6 +151,7 @@ struct AgMPolicy : PlainPolicy {
 //   chunk: Mr;  aux0: BN
 // ================================================================================================
 struct RsMPolicy : PlainPolicy {
+    static constexpr bool kEpiOps = false;   // own store: no fused elementwise epilogue
     static constexpr bool kStagedStore = true;
     static constexpr bool kNeedsStaging = true;
     static constexpr bool kBackground = true;
@@ -286,6 +287,7 @@ namespace gemm {
 // EXPERIMENTAL in round 1 (compiled, not yet run on hardware). CTA-pair kernel only.
 // ================================================================================================
 struct AgKAgOutPolicy : AgKPolicy {
+    static constexpr bool kEpiOps = false;   // own store: no fused elementwise epilogue
     static constexpr bool kStagedStore = true;
 
     template <typename OutT>

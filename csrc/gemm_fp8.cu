@@ -12,6 +12,7 @@
 namespace gemm {
 
 struct ScaledPolicy : PlainPolicy {
+    static constexpr bool kEpiOps = false;   // own store: no fused elementwise epilogue
     template <typename OutT>
     __device__ static void store(const RankParams& p, const TileCoord& tc, int row, int col0, const uint32_t (&v)[32]) {
         if (row >= p.M) return;

@@ -11,6 +11,8 @@ int pick_bn(int M, int N, int sms);
 // CTA-pair kernels are the default; CCMPI_GEMM_1CTA=1 selects the single-CTA kernels
 bool use_2cta();
 int check_shapes(int M, int N, int K, long long lda, long long ldb, long long ldc, int out_dtype);
+int set_epilogue(RankParams& rp, int epi_op, const void* epi_in, void* epi_out2, long long epi_ld, int N, int out_dtype,
+                 bool pairs);
 
 template <int BN, bool A_MN, bool B_MN, typename OutT, typename Policy>
 int launch(const Launch& lp, int grid, cudaStream_t stream, bool cooperative) {

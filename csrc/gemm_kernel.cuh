@@ -1,5 +1,6 @@
 // The persistent tcgen05 GEMM kernel body, parameterised by a Policy (see gemm_tcgen05.cuh).
 #pragma once
+#include "act.cuh"
 #include "gemm_tcgen05.cuh"
 
 namespace gemm {
@@ -90,6 +91,51 @@ struct PlainPolicy {
                 store_row32<OutT>(reinterpret_cast<OutT*>(p.C) + (long long)row * p.ldc + col0, v, ncols,
                                   p.accumulate != 0);
         }
+    }
+    // ---- fused elementwise epilogues (RankParams::epi_op; bf16 C, N % 32 == 0 checked on the host) ----
+    // Policies that keep PlainPolicy's store (plain GEMM, all-gather -> GEMM) inherit these; policies with
+    // their own store set kEpiOps = false.
+    static constexpr bool kEpiOps = true;
+    __device__ static bool epi_has_input(const RankParams& p) { return p.epi_op == EPI_MUL_DGELU || p.epi_op == EPI_ADD; }
+    // this lane's 32 bf16 of the second operand at (row, col0): issued one chunk ahead of its use
+    __device__ static void epi_load(const RankParams& p, int row, int col0, uint4 (&e)[4]) {
+        if (row < p.M && col0 < p.N) {
+            const __nv_bfloat16* s = reinterpret_cast<const __nv_bfloat16*>(p.epi_in) + (long long)row * p.epi_ld + col0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) e[j] = ptx::ld_v4(s + 8 * j);
+        }
+    }
+    template <typename OutT>
+    __device__ static void store_epi(const RankParams& p, const TileCoord& tc, int row, int col0, uint32_t (&v)[32],
+                                     const uint4 (&e)[4]) {
+        if (row >= p.M || col0 >= p.N) return;
+        OutT* dst = reinterpret_cast<OutT*>(p.C) + (long long)row * p.ldc + col0;
+        if (p.epi_op == EPI_GELU_DUAL) {
+            store_row32<OutT>(dst, v, 32, false);
+            // the activation is computed from the ROUNDED pre-activation, i.e. from what backward will read
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+                v[i] = __float_as_uint(act::gelu(__bfloat162float(__float2bfloat16_rn(__uint_as_float(v[i])))));
+            store_row32<OutT>(reinterpret_cast<OutT*>(p.epi_out2) + (long long)row * p.epi_ld + col0, v, 32, false);
+            return;
+        }
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&e[0]);
+        if (p.epi_op == EPI_MUL_DGELU) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const float2 u = __bfloat1622float2(h[i]);
+                v[2 * i] = __float_as_uint(__uint_as_float(v[2 * i]) * act::gelu_grad(u.x));
+                v[2 * i + 1] = __float_as_uint(__uint_as_float(v[2 * i + 1]) * act::gelu_grad(u.y));
+            }
+        } else {   // EPI_ADD
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const float2 r = __bfloat1622float2(h[i]);
+                v[2 * i] = __float_as_uint(__uint_as_float(v[2 * i]) + r.x);
+                v[2 * i + 1] = __float_as_uint(__uint_as_float(v[2 * i + 1]) + r.y);
+            }
+        }
+        store_row32<OutT>(dst, v, 32, false);
     }
     // called by all 128 epilogue threads before their first tile
     __device__ static void prologue(const RankParams& p, int cta, int nctas, int epi_tid) {}

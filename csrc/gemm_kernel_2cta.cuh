@@ -80,6 +80,10 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
+    // device trace (RankParams::trace): each role's elected thread accumulates cycle counts in registers
+    // and writes its slots once, at the end; with tracing off this costs a few predicated instructions
+    unsigned long long* const trace = p.trace ? p.trace + (size_t)blockIdx.x * TRACE_WORDS : nullptr;
+    if (trace && threadIdx.x == 0) trace[TR_T0_NS] = ptx::globaltimer_ns();
 
     if constexpr (Policy::kCommCtas) {
         const int ncomm = p.num_comm_ctas;  // even: whole clusters
@@ -130,6 +134,7 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
+            long long tr_flag = 0, tr_empty = 0;
             for (int t = pair; t < ntiles; t += npairs) {
                 const TileCoord tc = my_tile(t);
                 const bool valid = tc.m_blk < m_blocks;
@@ -137,7 +142,9 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
                     int k0, a_k0, a_m0;
                     const CUtensorMap* ta;
                     if (valid) {
+                        const long long c0 = trace ? clock64() : 0;
                         Policy::kblock(p, tc, it, k0, ta, a_k0, a_m0);
+                        if (trace) tr_flag += clock64() - c0;
                     } else {
                         // phantom m-block of an odd tail: its rows are out of range, TMA zero-fills
                         // them and there is nothing to wait for -- but the B half it loads feeds the
@@ -151,7 +158,11 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
                         k0 *= KSCALE;
                         a_k0 *= KSCALE;
                     }
-                    ptx::mbar_wait(&empty[stage], phase ^ 1, 100 + stage);
+                    {
+                        const long long c0 = trace ? clock64() : 0;
+                        ptx::mbar_wait(&empty[stage], phase ^ 1, 100 + stage);
+                        if (trace) tr_empty += clock64() - c0;
+                    }
                     if (leader) ptx::mbar_arrive_expect_tx(&full[stage], 2 * C::STAGE_BYTES);
                     else ptx::mbar_arrive_cluster(&full[stage], 0);
                     if constexpr (!A_MN) {
@@ -172,6 +183,10 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
                     if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
                 }
             }
+            if (trace) {
+                trace[TR_PROD_FLAG] = (unsigned long long)tr_flag;
+                trace[TR_PROD_EMPTY] = (unsigned long long)tr_empty;
+            }
         }
         __syncwarp();
     } else if (warp == 1) {
@@ -182,14 +197,23 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
             int stage = 0;
             uint32_t phase = 0;
             int local = 0;
+            long long tr_full = 0, tr_acc = 0;
             for (int t = pair; t < ntiles; t += npairs, ++local) {
                 const int acc = local & 1;
                 const uint32_t acc_phase = (local >> 1) & 1;
-                ptx::mbar_wait(&tmem_empty[acc], acc_phase ^ 1, 200 + acc);
+                {
+                    const long long c0 = trace ? clock64() : 0;
+                    ptx::mbar_wait(&tmem_empty[acc], acc_phase ^ 1, 200 + acc);
+                    if (trace) tr_acc += clock64() - c0;
+                }
                 ptx::tc_fence_after();
                 const uint32_t tmem_d = tmem_base + acc * BN;
                 for (int it = 0; it < k_blocks; ++it) {
-                    ptx::mbar_wait(&full[stage], phase, 300 + stage);
+                    {
+                        const long long c0 = trace ? clock64() : 0;
+                        ptx::mbar_wait(&full[stage], phase, 300 + stage);
+                        if (trace) tr_full += clock64() - c0;
+                    }
                     ptx::tc_fence_after();
                     const uint32_t a_addr = ptx::smem_u32(smem_a(stage));
                     const uint32_t b_addr = ptx::smem_u32(smem_b(stage));
@@ -206,6 +230,10 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
                     if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
                 }
                 ptx::umma_commit_2sm(&tmem_full[acc], 0b11);
+            }
+            if (trace) {
+                trace[TR_MMA_FULL] = (unsigned long long)tr_full;
+                trace[TR_MMA_ACC] = (unsigned long long)tr_acc;
             }
         }
         __syncwarp();
@@ -226,11 +254,23 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
                 while (Policy::template background<OutT>(p, st, cta, nctas, epi_tid, bcast + 2)) {}
         }
         uint32_t poll = 0;
+        long long tr_bg = 0, tr_wait = 0;
+        const bool tr_on = trace != nullptr && epi_tid == 0;
         for (int t = pair; t < ntiles; t += npairs, ++local) {
             const TileCoord tc = my_tile(t);
             const bool valid = tc.m_blk < m_blocks;
             const int acc = local & 1;
             const uint32_t acc_phase = (local >> 1) & 1;
+            const int row = tc.m_blk * BM + q * 32 + lane;
+            // second operand of a fused elementwise epilogue: the first chunk's 64 bytes are requested
+            // before the wait for the accumulator, every further chunk one chunk ahead of its use
+            uint4 epi_nxt[4];
+            bool epi_in = false;
+            if constexpr (Policy::kEpiOps && !Policy::kStagedStore) {
+                epi_in = valid && Policy::epi_has_input(p);
+                if (epi_in) Policy::epi_load(p, row, tc.n_blk * BN, epi_nxt);
+            }
+            const long long c_bg = tr_on ? clock64() : 0;
             if constexpr (Policy::kBackground) {
                 // While the MMAs of this tile are still running, spend the time on the policy's
                 // background work, one bounded slice at a time; the decision is taken by one
@@ -243,15 +283,28 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
                     if (!Policy::template background<OutT>(p, st, cta, nctas, epi_tid, bcast + 2)) break;
                 }
             }
+            const long long c_w = tr_on ? clock64() : 0;
             ptx::mbar_wait(&tmem_full[acc], acc_phase, 400 + acc);
+            if (tr_on) {
+                const long long c1 = clock64();
+                tr_bg += c_w - c_bg;
+                tr_wait += c1 - c_w;
+            }
             ptx::tc_fence_after();
-            const int row = tc.m_blk * BM + q * 32 + lane;
             const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + acc * BN;
             if constexpr (!Policy::kStagedStore) {
 #pragma unroll 1
                 for (int c = 0; c < BN; c += 32) {
                     uint32_t v[32];
                     ptx::tmem_ld_32x32b_x32(taddr + c, v);
+                    uint4 epi_cur[4];
+                    if constexpr (Policy::kEpiOps) {
+                        if (epi_in) {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) epi_cur[j] = epi_nxt[j];
+                            if (c + 32 < BN) Policy::epi_load(p, row, tc.n_blk * BN + c + 32, epi_nxt);
+                        }
+                    }
                     ptx::tmem_ld_wait();
                     if (c + 32 >= BN) {
                         ptx::tc_fence_before();
@@ -259,6 +312,12 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
                         if (lane == 0) {
                             if (leader) ptx::mbar_arrive(&tmem_empty[acc]);
                             else ptx::mbar_arrive_cluster(&tmem_empty[acc], 0);
+                        }
+                    }
+                    if constexpr (Policy::kEpiOps && sizeof(OutT) == 2) {
+                        if (valid && p.epi_op != EPI_NONE) {
+                            Policy::template store_epi<OutT>(p, tc, row, tc.n_blk * BN + c, v, epi_cur);
+                            continue;
                         }
                     }
                     if (valid) Policy::template store<OutT>(p, tc, row, tc.n_blk * BN + c, v);
@@ -307,7 +366,15 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
             }
             if (valid) Policy::tile_done(p, tc, epi_tid);
         }
+        const long long c_tail = tr_on ? clock64() : 0;
         Policy::template tail<OutT>(p, st, cta, nctas, epi_tid, bcast + 2);
+        if (tr_on) {
+            trace[TR_EPI_BG] = (unsigned long long)tr_bg;
+            trace[TR_EPI_ACC] = (unsigned long long)tr_wait;
+            trace[TR_EPI_TAIL] = (unsigned long long)(clock64() - c_tail);
+            trace[TR_T1_NS] = ptx::globaltimer_ns();
+            trace[TR_TILES] = (unsigned long long)local;
+        }
     }
 
     // ---- teardown: nobody leaves (or frees TMEM) while the partner may still read its smem ----

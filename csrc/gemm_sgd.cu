@@ -14,6 +14,7 @@
 namespace gemm {
 
 struct SgdPolicy : PlainPolicy {
+    static constexpr bool kEpiOps = false;   // own store: no fused elementwise epilogue
     template <typename OutT>
     __device__ static void store(const RankParams& p, const TileCoord& tc, int row, int col0, const uint32_t (&v)[32]) {
         static_assert(sizeof(OutT) == 2, "weights are bf16");

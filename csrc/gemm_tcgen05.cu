@@ -63,9 +63,33 @@ int check_shapes(int M, int N, int K, long long lda, long long ldb, long long ld
 
 }  // namespace gemm
 
-extern "C" int ccmpi_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
-                               int a_mn_major, int b_mn_major, int out_dtype, int accumulate, int num_sms,
-                               void* stream) {
+namespace gemm {
+// Checks shared by every entry point that takes a fused elementwise epilogue; fills the RankParams fields.
+int set_epilogue(RankParams& rp, int epi_op, const void* epi_in, void* epi_out2, long long epi_ld, int N, int out_dtype,
+                 bool pairs) {
+    rp.epi_op = EPI_NONE;
+    if (epi_op == EPI_NONE) return CCMPI_OK;
+    CCMPI_REQUIRE(epi_op >= EPI_GELU_DUAL && epi_op <= EPI_ADD, "unknown epilogue op %d", epi_op);
+    CCMPI_REQUIRE(pairs, "fused epilogues exist in the CTA-pair GEMM only (unset CCMPI_GEMM_1CTA)");
+    CCMPI_REQUIRE(out_dtype == CCMPI_BF16, "fused epilogues need a bf16 output");
+    CCMPI_REQUIRE(N % 32 == 0, "fused epilogues need N %% 32 == 0 (N = %d)", N);
+    CCMPI_REQUIRE(epi_ld % 8 == 0 && epi_ld >= N, "epilogue operand row stride %lld must be a multiple of 8 and >= N", epi_ld);
+    if (epi_op == EPI_GELU_DUAL) CCMPI_REQUIRE(epi_out2 != nullptr, "EPI_GELU_DUAL needs a second output");
+    else CCMPI_REQUIRE(epi_in != nullptr, "this epilogue needs a second operand");
+    rp.epi_op = epi_op;
+    rp.epi_in = epi_in;
+    rp.epi_out2 = epi_out2;
+    rp.epi_ld = epi_ld;
+    return CCMPI_OK;
+}
+}  // namespace gemm
+
+// C = A * B with optional elementwise work in the epilogue (EpiOp in gemm_tcgen05.cuh): 1 = also write
+// gelu(C) to epi_out2, 2 = multiply by gelu'(epi_in), 3 = add epi_in. `trace`: TRACE_WORDS uint64 per CTA.
+extern "C" int ccmpi_gemm_bf16_ex(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                                  int a_mn_major, int b_mn_major, int out_dtype, int accumulate, int epi_op,
+                                  const void* epi_in, void* epi_out2, long long epi_ld, void* trace, int num_sms,
+                                  void* stream) {
     using namespace gemm;
     int rc = check_shapes(M, N, K, lda, ldb, ldc, out_dtype);
     if (rc) return rc;
@@ -86,6 +110,9 @@ extern "C" int ccmpi_gemm_bf16(const void* A, const void* B, void* C, int M, int
     rp.N = N;
     rp.K = K;
     rp.accumulate = accumulate;
+    rc = set_epilogue(rp, epi_op, epi_in, epi_out2, epi_ld, N, out_dtype, pairs);
+    if (rc) return rc;
+    rp.trace = pairs ? (unsigned long long*)trace : nullptr;
     if (pairs) {
         const int pair_tiles = (((M + BM - 1) / BM + 1) / 2) * ((N + BN - 1) / BN);
         const int npairs = pair_tiles < sms / 2 ? pair_tiles : sms / 2;
@@ -94,4 +121,11 @@ extern "C" int ccmpi_gemm_bf16(const void* A, const void* B, void* C, int M, int
     const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
     const int grid = tiles < sms ? tiles : sms;
     return dispatch<PlainPolicy>(lp, BN, a_mn_major != 0, b_mn_major != 0, out_dtype, grid, (cudaStream_t)stream, false);
+}
+
+extern "C" int ccmpi_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                               int a_mn_major, int b_mn_major, int out_dtype, int accumulate, int num_sms,
+                               void* stream) {
+    return ccmpi_gemm_bf16_ex(A, B, C, M, N, K, lda, ldb, ldc, a_mn_major, b_mn_major, out_dtype, accumulate, 0, nullptr,
+                              nullptr, 0, nullptr, num_sms, stream);
 }

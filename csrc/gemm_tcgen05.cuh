@@ -57,6 +57,38 @@ struct alignas(64) RankParams {
     unsigned int epoch;   // value flags must reach for this launch
     int num_comm_ctas;    // CTAs (per rank) that move data instead of computing tiles
     int aux0, aux1, aux2;
+    // ---- elementwise work fused into the epilogue (bf16 outputs; see EpiOp) ----
+    int epi_op;
+    const void* epi_in;   // second epilogue operand  [M][epi_ld] bf16: u for EPI_MUL_DGELU, the residual for EPI_ADD
+    void* epi_out2;       // second output            [M][epi_ld] bf16: gelu(C) for EPI_GELU_DUAL
+    long long epi_ld;
+    // ---- per-CTA device trace (nullptr: off): TRACE_WORDS x uint64 per CTA, see TraceSlot ----
+    unsigned long long* trace;
+};
+
+// Elementwise work a GEMM can do on its accumulator tile before it leaves the SM, so that the
+// activation / residual passes between the FC GEMMs cost no extra trip through HBM.
+enum EpiOp : int {
+    EPI_NONE = 0,
+    EPI_GELU_DUAL = 1,   // C = acc (the pre-activation, kept for backward) and epi_out2 = gelu(acc)
+    EPI_MUL_DGELU = 2,   // C = acc * gelu'(epi_in)      (backward through the activation)
+    EPI_ADD = 3,         // C = acc + epi_in             (residual connection / gradient accumulation)
+};
+
+// What each CTA records when RankParams::trace is set (SM cycles unless noted). Written once, at the end,
+// by the elected thread of each role; read on the host by utils/ktrace.py.
+enum TraceSlot : int {
+    TR_T0_NS = 0,        // %globaltimer at kernel entry
+    TR_PROD_FLAG = 1,    // TMA producer: cycles inside Policy::kblock (waits for gathered chunks)
+    TR_PROD_EMPTY = 2,   // TMA producer: cycles waiting for a free pipeline stage (MMA-bound: good)
+    TR_MMA_FULL = 3,     // MMA issuer: cycles waiting for operands (starved)
+    TR_MMA_ACC = 4,      // MMA issuer: cycles waiting for a free accumulator (epilogue-bound)
+    TR_EPI_BG = 5,       // epilogue: cycles in background work (pushes, reductions)
+    TR_EPI_ACC = 6,      // epilogue: cycles waiting for a finished accumulator
+    TR_EPI_TAIL = 7,     // epilogue: cycles in the policy's tail (left-over pushes / reductions / barriers)
+    TR_T1_NS = 8,        // %globaltimer when the epilogue warps are done
+    TR_TILES = 9,        // tiles this CTA computed
+    TRACE_WORDS = 16
 };
 
 struct Launch {

@@ -177,6 +177,16 @@ int ccmpi_wait_signal(const ccmpi_dev_comm* comms, int nvr, int peer, int flag_i
 int ccmpi_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb,
                     int ldc, int a_mn_major, int b_mn_major, int out_dtype, int accumulate,
                     int num_sms, void* stream);
+/* The same GEMM with elementwise work fused into its epilogue, so the activation / residual passes between
+ * the FC GEMMs cost no extra trip through HBM (bf16 C, N % 32 == 0, CTA-pair kernel):
+ *   epi_op 1: C = A*B and epi_out2 = gelu(C)            (tanh-approximated; C is kept for backward)
+ *          2: C = (A*B) * gelu'(epi_in)                 (backward through the activation)
+ *          3: C = A*B + epi_in                          (residual / gradient accumulation)
+ * epi_in / epi_out2: [M][epi_ld] bf16. `trace`: NULL, or 16 uint64 per CTA that the kernel fills with where
+ * each warp role spent its cycles (utils/ktrace.py decodes them). */
+int ccmpi_gemm_bf16_ex(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                       int a_mn_major, int b_mn_major, int out_dtype, int accumulate, int epi_op, const void* epi_in,
+                       void* epi_out2, long long epi_ld, void* trace, int num_sms, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Fused GEMM + collective kernels (csrc/fused_gemm.cu, csrc/fused_policies.cuh). One kernel
@@ -203,6 +213,19 @@ int ccmpi_fused_ag_gemm(const ccmpi_dev_comm* comms, int nvr, size_t x_off, int 
                         int num_comm_ctas, int num_sms, int use_mc, void* stream);
 /* kind 0: K-gather kernels (ccmpi_fused_ag_gemm, ccmpi_fused_ag_gemm_ag), 1: M-gather (ccmpi_fused_ag_gemm_m) */
 int ccmpi_fused_ag_ctas(int kind, int M, int N, int nvr, int num_sms);
+/* ccmpi_fused_ag_gemm with a fused elementwise epilogue (as ccmpi_gemm_bf16_ex; one epi_in / epi_out2 pointer
+ * per rank, or NULL) and an optional device trace. */
+int ccmpi_fused_ag_gemm_ex(const ccmpi_dev_comm* comms, int nvr, size_t x_off, int ldx, size_t xfull_off,
+                           const void* const* B, void* const* C, int M, int N, int K, int ldb, int ldc, int b_kn,
+                           int out_dtype, int flag_base, unsigned epoch, unsigned flag_target, int epi_op,
+                           const void* const* epi_in, void* const* epi_out2, long long epi_ld, void* trace,
+                           int num_comm_ctas, int num_sms, int use_mc, void* stream);
+/* ccmpi_fused_gemm_rs whose reducer adds `residual` ([M][N/n] bf16 per rank, row stride res_ld; NULL: none) to
+ * the reduced result before the single rounding, and an optional device trace. */
+int ccmpi_fused_gemm_rs_ex(const ccmpi_dev_comm* comms, int nvr, const void* const* A, const void* const* B,
+                           size_t slots_off, void* const* C, int M, int N, int K, int lda, int ldb, int ldc, int a_km,
+                           int b_kn, int out_dtype, int flag_base, unsigned epoch, const void* const* residual,
+                           long long res_ld, void* trace, int num_sms, void* stream);
 
 /* GEMM -> reduce-scatter on N (the dx GEMM + func_impl.py:150-187): C[M][N/n] = rank-ordered sum
  * over ranks of (A*B)[:, own column block]; slots_off: [n][M][N/n] staging (out dtype). */
