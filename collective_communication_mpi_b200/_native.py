@@ -141,6 +141,8 @@ def check_host(rc: int, what: str = "") -> int:
 def _declare_device(lib):
     vp, i, i64, sz, f = C.c_void_p, C.c_int, C.c_int64, C.c_size_t, C.c_float
     P = C.POINTER
+    PV = P(vp)
+    u = C.c_uint
     sigs = {
         "ccmpi_last_error": (C.c_char_p, []),
         "ccmpi_version": (i, []),
@@ -174,7 +176,6 @@ def _declare_device(lib):
         fn = getattr(lib, name)
         fn.restype = res
         fn.argtypes = args
-    PV = P(vp)
     u = C.c_uint
     fused = {
         "ccmpi_fused_ag_gemm": (i, [P(DevComm), i, sz, i, sz, PV, PV, i, i, i, i, i, i, i, i, u, u, i, i, i, vp]),
