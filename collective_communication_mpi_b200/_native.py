@@ -196,6 +196,9 @@ def _declare_device(lib):
         "ccmpi_reduce_scatter_tight": (i, [P(DevComm), i, i, i, sz, sz, sz, sz, sz, sz, i, vp]),
         "ccmpi_allreduce_twoshot_tight": (i, [P(DevComm), i, i, i, sz, sz, sz, sz, f, i, vp]),
         "ccmpi_gemm_sgd_bf16": (i, [vp, vp, vp, i, i, i, i, i, i, i, i, f, i, vp]),
+        "ccmpi_gemm_sgd_bf16_sr": (i, [vp, vp, vp, i, i, i, i, i, i, i, i, f, i, u, i, vp]),
+        "ccmpi_sgd_sr_bf16": (i, [vp, vp, C.c_longlong, f, C.c_ulonglong, u, u, vp]),
+        "ccmpi_allreduce_sgd_nvls": (i, [P(DevComm), i, sz, sz, sz, f, C.c_ulonglong, u, u, i, vp]),
         "ccmpi_gemm_mxfp8": (i, [vp, vp, vp, vp, vp, i, i, i, i, i, i, i, i, vp]),
         "ccmpi_mse_workspace_bytes": (sz, []),
         "ccmpi_mse_fwd_bwd": (i, [vp, vp, vp, ll, vp, vp, vp]),

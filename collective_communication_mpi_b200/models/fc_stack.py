@@ -142,10 +142,17 @@ class TrainStep:
             self.sink = None
         else:
             self.sink = GradSink(dp_comm, model.tp_layers(), bucket_mb=bucket_mb, overlap=overlap)
-        self.weights = [l.weight.data for l in model.tp_layers()]
+        self.step_no = 0
         self.fused_loss = EW.enabled()
 
     def __call__(self, x: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        # the step counter selects this step's stochastic-rounding stream (csrc/sr.cuh)
+        if self.fused_sgd:
+            for layer in self.model.tp_layers():
+                layer.sgd_step = self.step_no
+        else:
+            self.sink.begin_step(self.lr, self.step_no)
+        self.step_no += 1
         y = self.model(x)
         if self.fused_loss and y.dtype == torch.bfloat16 and target.dtype == torch.bfloat16:
             loss, dy = EW.mse_loss_and_grad(y, target)      # loss and its gradient in one pass
@@ -154,6 +161,5 @@ class TrainStep:
             loss = torch.nn.functional.mse_loss(y.float(), target.float())
             loss.backward()
         if not self.fused_sgd:
-            self.sink.finish()
-            sgd_step(self.weights, self.sink.grads(), self.lr)
+            self.sink.apply()       # nothing left to do when the reductions were the optimizer step
         return loss.detach()

@@ -80,6 +80,16 @@ def allreduce(comms, dtype: int, op: int, src_off: int, dst_off: int, count: int
     N.count_launch()
 
 
+def allreduce_sgd(comms, grad_off: int, w_off: int, count: int, lr_eff: float, *, base_index: int, step: int, seed: int = 0,
+                  max_blocks: int = 0, stream=None):
+    """Data-parallel gradient all-reduce fused with the SGD update (NVLS, bf16): see ``ccmpi_allreduce_sgd_nvls``."""
+    a, n = _arr(comms)
+    N.check(N.device_lib().ccmpi_allreduce_sgd_nvls(a, n, grad_off, w_off, count, C.c_float(lr_eff), int(base_index),
+                                                    int(step) & 0xFFFFFFFF, int(seed) & 0xFFFFFFFF, max_blocks, _sp(stream)),
+            "ccmpi_allreduce_sgd_nvls")
+    N.count_launch()
+
+
 def allgather(comms, src_off: int, dst_off: int, rows: int, row_bytes: int, src_row_stride: int,
               dst_row_stride: int, *, use_mc: bool = True, max_blocks: int = 0, stream=None):
     a, n = _arr(comms)

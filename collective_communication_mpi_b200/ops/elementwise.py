@@ -155,6 +155,22 @@ def mse_loss_and_grad(y: torch.Tensor, t: torch.Tensor, stream=None) -> Tuple[to
     return loss, dy
 
 
+def sgd_sr_(w: torch.Tensor, g: torch.Tensor, lr: float, *, base_index: int = 0, step: int = 0, seed: int = 0, stream=None):
+    """``w = SR(w - lr * g)`` in place on contiguous bf16 tensors: the optimizer pass for gradients that came
+    out of a collective, with stochastic rounding (csrc/sr.cuh) so that steps below one bf16 ulp are not
+    lost. ``base_index``: index of ``w``'s first element in the model's flat parameter numbering."""
+    if not w.is_cuda:
+        from ..utils import sr
+        w.copy_(sr.sgd_update(w.reshape(-1), g.reshape(-1), lr, base_index, step & 0xFFFFFFFF, seed).view(w.shape))
+        return w
+    if w.dtype != torch.bfloat16 or g.dtype != torch.bfloat16 or not w.is_contiguous() or not g.is_contiguous() or w.shape != g.shape:
+        raise TypeError("sgd_sr_ takes two contiguous bfloat16 tensors of the same shape")
+    N.check(N.device_lib().ccmpi_sgd_sr_bf16(w.data_ptr(), g.data_ptr(), w.numel(), float(lr), int(base_index),
+                                             int(step) & 0xFFFFFFFF, int(seed) & 0xFFFFFFFF, _stream(stream)), "ccmpi_sgd_sr_bf16")
+    N.count_launch()
+    return w
+
+
 # -------------------------------------------------------------------------------------------------
 # autograd
 # -------------------------------------------------------------------------------------------------

@@ -126,11 +126,12 @@ def matmul_tn(x: torch.Tensor, dy: torch.Tensor, **kw) -> torch.Tensor:
 
 
 def gemm_sgd_(w: torch.Tensor, a: torch.Tensor, b: torch.Tensor, lr: float, *, a_km: bool = False, b_kn: bool = False,
-              num_sms: int = 0, stream=None) -> torch.Tensor:
+              step: int | None = None, seed: int = 0, num_sms: int = 0, stream=None) -> torch.Tensor:
     """``w -= lr * (a @ b)`` in ONE kernel: the weight-gradient GEMM applies the SGD step from its
     fp32 accumulator instead of writing the gradient (csrc/gemm_sgd.cu). Operand layouts as in
     ``gemm``; ``w`` is a bf16 ``[M, N]`` tensor with unit column stride, updated in place.
-    Experimental: not yet run on hardware."""
+    With ``step`` (an optimizer step counter >= 0) the new weights are rounded stochastically
+    (csrc/sr.cuh; bits from (row * ld + col, step, seed)); without it, to nearest."""
     _check_operand(a, "a")
     _check_operand(b, "b")
     K, M = a.shape if a_km else a.shape[::-1]
@@ -139,9 +140,10 @@ def gemm_sgd_(w: torch.Tensor, a: torch.Tensor, b: torch.Tensor, lr: float, *, a
         raise ValueError(f"inner dimensions differ: {K} vs {Kb}")
     if w.dtype != torch.bfloat16 or w.shape != (M, Nn) or w.stride(1) != 1 or not w.is_cuda:
         raise ValueError("w must be a CUDA bfloat16 [M, N] tensor with unit column stride")
-    rc = N.device_lib().ccmpi_gemm_sgd_bf16(
+    rc = N.device_lib().ccmpi_gemm_sgd_bf16_sr(
         C.c_void_p(a.data_ptr()), C.c_void_p(b.data_ptr()), C.c_void_p(w.data_ptr()), M, Nn, K, a.stride(0), b.stride(0),
-        w.stride(0), int(a_km), int(b_kn), float(lr), int(num_sms), C.c_void_p(_stream_ptr(stream)))
-    N.check(rc, "ccmpi_gemm_sgd_bf16")
+        w.stride(0), int(a_km), int(b_kn), float(lr), -1 if step is None else int(step) & 0x7FFFFFFF, int(seed) & 0xFFFFFFFF,
+        int(num_sms), C.c_void_p(_stream_ptr(stream)))
+    N.check(rc, "ccmpi_gemm_sgd_bf16_sr")
     N.count_launch()
     return w

@@ -61,9 +61,17 @@ def matmul_tn(x: torch.Tensor, dy: torch.Tensor, **kw) -> torch.Tensor:
 
 
 def gemm_sgd_(w: torch.Tensor, a: torch.Tensor, b: torch.Tensor, lr: float, *, a_km: bool = False, b_kn: bool = False,
-              num_sms: int = 0, stream=None) -> torch.Tensor:
-    """``w -= lr * (a @ b)`` with the product kept in fp32 (what csrc/gemm_sgd.cu does in its epilogue)."""
-    w.copy_((w.float() - lr * gemm(a, b, a_km=a_km, b_kn=b_kn, out_dtype=torch.float32)).to(w.dtype))
+              step=None, seed: int = 0, num_sms: int = 0, stream=None) -> torch.Tensor:
+    """``w -= lr * (a @ b)`` with the product kept in fp32 (what csrc/gemm_sgd.cu does in its epilogue); with
+    ``step`` the result is rounded stochastically with the kernel's own arithmetic (utils/sr.py)."""
+    new = w.float() - torch.tensor(lr, dtype=torch.float32) * gemm(a, b, a_km=a_km, b_kn=b_kn, out_dtype=torch.float32)
+    if step is None:
+        w.copy_(new.to(w.dtype))
+    else:
+        from ..utils import sr
+        rows = torch.arange(w.shape[0], dtype=torch.int64).view(-1, 1) * w.stride(0)
+        idx = rows + torch.arange(w.shape[1], dtype=torch.int64).view(1, -1)
+        w.copy_(sr.round_bf16(new, idx, int(step) & 0x7FFFFFFF, seed))
     return w
 
 

@@ -24,9 +24,19 @@ launched as 2-CTA clusters so that it takes whole SM pairs (the GEMM's CTA pairs
 pair), and the layers' backward fused kernels are sized to the remaining SMs. Together they always
 fit, whatever order the hardware starts them in. The last bucket has nothing to hide behind: it is
 launched on the main stream, after the kernels before it, and may use every SM.
+
+Optimizer. With NVLS the reduction IS the optimizer step (``fused_update``): the weights live in a
+second flat symmetric buffer with the gradients' layout, and the kernel of a bucket sums its slice of
+every replica's gradients in the switch, updates its slice of the weights (stochastic rounding,
+csrc/sr.cuh) and multicasts the new weights to all replicas -- no reduced gradient is written, no
+optimizer pass runs, replicas stay bit-identical. Because that kernel rewrites a layer's weights
+during backward, layers attached to such a sink compute dx (which reads W) before dW
+(``layer.dw_last``). Without NVLS the gradients are all-reduced in place and ``apply`` runs the
+stand-alone update kernel per layer.
 """
 from __future__ import annotations
 
+import os
 from typing import Dict, List
 
 import torch
@@ -78,6 +88,21 @@ class GradSink:
         self.max_blocks = max_blocks & ~1
         self.algo = N.AR_NVLS if self.use_nvls else N.AR_TWOSHOT
         self.launches = 0
+        self.lr, self.step_no, self.seed = 0.0, 0, 0x5EED
+        # the reduction doubles as the optimizer step when the switch can do it (see the module docstring)
+        self.fused_update = bool(self.on_gpu and self.dp > 1 and self.dev.has_mc and
+                                 os.environ.get("CCMPI_DP_FUSED_UPDATE", "1") != "0")
+        self.wflat = None
+        if self.fused_update:
+            self.wflat = dp_comm.symm_empty(self.flat.numel(), torch.bfloat16)
+            self.wflat.zero_()
+            self.wflat_off = self.dev.heap.offset_of(self.wflat)
+            for l in self.layers:       # the parameters move into the flat buffer, at their gradients' offsets
+                v = self._views[id(l.weight)]
+                off = int(v.storage_offset() - self.flat.storage_offset())
+                wv = self.wflat[off:off + l.weight.numel()].view_as(l.weight)
+                wv.copy_(l.weight.data)
+                l.weight.data = wv
         # reserve the reduction's SMs in the backward fused kernels of a model-parallel group
         self.partitioned = self.overlap and any(getattr(l, "mp", 1) > 1 for l in self.layers)
         if self.partitioned:
@@ -93,6 +118,16 @@ class GradSink:
 
     def grads(self) -> List[torch.Tensor]:
         return [self._views[id(l.weight)] for l in self.layers]
+
+    @property
+    def updates_in_backward(self) -> bool:
+        """True when a bucket's kernel rewrites weights while backward is still running (layers then
+        read W for dx before they hand over dW)."""
+        return self.fused_update
+
+    def begin_step(self, lr: float, step_no: int):
+        """Learning rate and step counter (stochastic-rounding stream) of the step that is about to run."""
+        self.lr, self.step_no = float(lr), int(step_no)
 
     def ready(self, param):
         b = self.buckets[self._bucket_of[id(param)]]
@@ -125,8 +160,12 @@ class GradSink:
             ev.record(cur)
             st.wait_event(ev)
         blocks = 0 if not side else (self.max_blocks | N.BLOCKS_PAIRED if self.partitioned else self.max_blocks)
-        CO.allreduce(self.dev.comms, N.BF16, N.SUM, off, off, count, tmp_off=tmp_off, algo=self.algo,
-                     scale=1.0 / self.dp, max_blocks=blocks, stream=st)
+        if self.fused_update:
+            CO.allreduce_sgd(self.dev.comms, off, self.wflat_off + b["lo"] * 2, count, self.lr / self.dp, base_index=b["lo"],
+                             step=self.step_no, seed=self.seed, max_blocks=blocks, stream=st)
+        else:
+            CO.allreduce(self.dev.comms, N.BF16, N.SUM, off, off, count, tmp_off=tmp_off, algo=self.algo,
+                         scale=1.0 / self.dp, max_blocks=blocks, stream=st)
         self.launches += 1
 
     def finish(self):
@@ -135,6 +174,21 @@ class GradSink:
             torch.cuda.current_stream().wait_stream(self.stream)
 
 
+    def apply(self):
+        """The optimizer step for what the reductions left to do: nothing with ``fused_update``; otherwise one
+        stand-alone update kernel per layer on the (already averaged) gradients, ``w = SR(w - lr * g)``."""
+        self.finish()
+        if self.fused_update:
+            return
+        from ..ops import elementwise as EW
+        with torch.no_grad():
+            for l in self.layers:
+                g = self._views[id(l.weight)]
+                base = int(g.storage_offset() - self.flat.storage_offset())     # position in the flat numbering
+                EW.sgd_sr_(l.weight.data, g, self.lr, base_index=base, step=self.step_no, seed=self.seed)
+
+
 def sgd_step(weights: List[torch.Tensor], grads: List[torch.Tensor], lr: float):
+    """Plain round-to-nearest SGD (kept for comparisons; the training step uses ``GradSink.apply``)."""
     with torch.no_grad():
         torch._foreach_add_(weights, grads, alpha=-lr)

@@ -86,9 +86,10 @@ def _weight_grad(layer, x, dy):
     into the data-parallel bucket in symmetric memory and the reducer is told the bucket entry is
     ready; autograd then gets ``None`` for the weight."""
     if layer.sgd_lr is not None:
-        # no data-parallel reduction needed: the dW kernel applies the step itself (W -= lr * x^T dy)
+        # no data-parallel reduction needed: the dW kernel applies the step itself (W = SR(W - lr * x^T dy))
         with torch.no_grad():
-            layer._gemm_sgd(layer.weight.data, x, dy, layer.sgd_lr, a_km=True, b_kn=True, num_sms=layer.num_sms)
+            layer._gemm_sgd(layer.weight.data, x, dy, layer.sgd_lr, a_km=True, b_kn=True, step=layer.sgd_step,
+                            seed=layer.sgd_seed, num_sms=layer.num_sms)
         return None
     sink = getattr(layer, "grad_sink", None)
     if sink is None:
@@ -96,6 +97,16 @@ def _weight_grad(layer, x, dy):
     layer._matmul_tn(x, dy, out=sink.view_for(layer.weight), num_sms=layer.num_sms)
     sink.ready(layer.weight)
     return None
+
+
+def _dw_last(layer) -> bool:
+    """dW must come AFTER dx when producing it lets a kernel rewrite W during backward: the dW GEMM with the
+    SGD step in its epilogue, or a gradient sink whose reduction is the optimizer step. Otherwise dW goes
+    first, so that its data-parallel bucket can start reducing while dx is computed."""
+    if layer.sgd_lr is not None:
+        return True
+    sink = getattr(layer, "grad_sink", None)
+    return sink is not None and sink.updates_in_backward
 
 
 def _init_weight(rows: int, cols: int, fan_in: int, device, seed: int) -> nn.Parameter:
@@ -116,6 +127,7 @@ class ColumnParallelLinear(nn.Module):
         self.grad_dtype = grad_dtype
         dev, ops, self._gemm, self._matmul_tn, self._gemm_sgd = _backend()
         self.sgd_lr = None      # set by TrainStep when the optimizer step is fused into the dW GEMM
+        self.sgd_step, self.sgd_seed = None, seed
         self.weight = _init_weight(in_features, self.N, in_features, dev, seed * 1000 + mp_comm.Get_rank())
         # a 1-member group needs no staging buffers or flags: plain GEMMs
         self.ag = ops.AllGatherGemm(mp_comm, tokens, in_features, num_comm_ctas=num_comm_ctas) if self.mp > 1 else None
@@ -158,14 +170,15 @@ class ColumnParallelLinear(nn.Module):
             dy = dy[:, r * self.N:(r + 1) * self.N].contiguous()     # func_impl.py:111-147
         # dW first: its data-parallel bucket can start reducing while dx is computed -- unless the
         # dW kernel itself rewrites W (fused SGD), in which case dx must read W before that
-        dw = _weight_grad(self, x_full, dy) if self.sgd_lr is None else None
+        late = _dw_last(self)
+        dw = _weight_grad(self, x_full, dy) if not late else None
         if not need_dx:
             dx = None
         elif self.mp == 1:
             dx = self._gemm(dy, w, num_sms=self.num_sms)
         else:
             dx = self.rs(dy, w, b_kn=False, num_sms=self.bwd_num_sms)
-        if self.sgd_lr is not None:
+        if late:
             dw = _weight_grad(self, x_full, dy)
         return dx, dw
 
@@ -181,6 +194,7 @@ class RowParallelLinear(nn.Module):
         self.grad_dtype = grad_dtype
         dev, ops, self._gemm, self._matmul_tn, self._gemm_sgd = _backend()
         self.sgd_lr = None
+        self.sgd_step, self.sgd_seed = None, seed
         self.weight = _init_weight(self.K, out_features, in_features, dev, seed * 1000 + mp_comm.Get_rank())
         self.rs = ops.GemmReduceScatter(mp_comm, tokens, out_features) if self.mp > 1 else None
         self.ag = ops.AllGatherGemm(mp_comm, tokens, out_features, num_comm_ctas=num_comm_ctas) if self.mp > 1 else None
@@ -271,9 +285,10 @@ class _MlpBlockFn(torch.autograd.Function):
         du, dout_full = _row_dx(fc2, dout, w2, dgelu_of=u)          # dx of fc2, through the activation
         dw2 = _weight_grad(fc2, act, dout_full)
         # dW before dx lets its data-parallel bucket start early -- unless the dW kernel rewrites W (fused SGD)
-        dw1 = _weight_grad(fc1, ctx.h_full, du) if fc1.sgd_lr is None else None
+        late = _dw_last(fc1)
+        dw1 = _weight_grad(fc1, ctx.h_full, du) if not late else None
         dh = _col_dx(fc1, du, w1, add=dout)                         # + the residual path's gradient
-        if fc1.sgd_lr is not None:
+        if late:
             dw1 = _weight_grad(fc1, ctx.h_full, du)
         ctx.h_full = None
         return dh, dw1, dw2, None, None
@@ -301,9 +316,10 @@ class _AttnBlockFn(torch.autograd.Function):
         dwo = _weight_grad(fc_o, a, dh_full)
         dqkv = EW.gate_backward(da, qkv)
         need_dx = ctx.needs_input_grad[0]
-        dwqkv = _weight_grad(fc_qkv, ctx.x_full, dqkv) if fc_qkv.sgd_lr is None else None
+        late = _dw_last(fc_qkv)
+        dwqkv = _weight_grad(fc_qkv, ctx.x_full, dqkv) if not late else None
         dx = _col_dx(fc_qkv, dqkv, wqkv, add=dh) if need_dx else None
-        if fc_qkv.sgd_lr is not None:
+        if late:
             dwqkv = _weight_grad(fc_qkv, ctx.x_full, dqkv)
         ctx.x_full = None
         return dx, dwqkv, dwo, None, None

@@ -13,6 +13,7 @@
 // (blockIdx.x % nvr selects the rank), which exercises the same protocol code without ever
 // having two kernels wait on each other on one GPU.
 #include "collectives_common.cuh"
+#include "sr.cuh"
 
 namespace coll {
 
@@ -177,17 +178,29 @@ allreduce_nvls_kernel(const __grid_constant__ Launch lp, size_t src_off, size_t 
             return;
         }
     }
-    for (size_t g = lo + (size_t)x.blk * THREADS + threadIdx.x; g < hi; g += (size_t)x.nblk * THREADS) {
-        if constexpr (std::is_same<T, OutT>::value) {
-            uint4 r = mc_ld_reduce<T>(msrc + g * 16);
-            if (!identity) {
+    if constexpr (std::is_same<T, OutT>::value) {
+        // scaled, same type (the data-parallel gradient path: scale = 1/dp): eight reductions in flight per
+        // thread, like the unscaled path -- one at a time leaves the switch round trip exposed
+        for_range_unrolled<8>(lo, hi, x, [&](size_t g, size_t stride, auto uc) {
+            constexpr int U = decltype(uc)::value;
+            uint4 v[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) v[u] = mc_ld_reduce<T>(msrc + (g + u * stride) * 16);
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
                 AccVec<T> a;
-                a.init(r);
+                a.init(v[u]);
 #pragma unroll
                 for (int i = 0; i < N; ++i) a.e[i] = a.e[i] * scale;
-                r = a.pack();
+                ptx::multimem_st_v4(mdst + (g + u * stride) * 16, a.pack());
             }
-            ptx::multimem_st_v4(mdst + g * 16, r);
+        });
+        block_barrier(x);
+        return;
+    }
+    for (size_t g = lo + (size_t)x.blk * THREADS + threadIdx.x; g < hi; g += (size_t)x.nblk * THREADS) {
+        if constexpr (std::is_same<T, OutT>::value) {
+            // (handled above)
         } else if constexpr (sizeof(OutT) < sizeof(T)) {
             // fp32 in -> 16-bit out: two input vectors make one output vector
             Vec<OutT> o;
@@ -214,6 +227,55 @@ allreduce_nvls_kernel(const __grid_constant__ Launch lp, size_t src_off, size_t 
         }
     }
     block_barrier(x);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Data-parallel gradient all-reduce FUSED WITH THE OPTIMIZER (bf16, NVLS). Rank r owns slice r of the
+// bucket: it lets the switch sum that slice of every replica's gradient (multimem.ld_reduce), applies
+//     w = SR(w - lr_eff * sum)            (fp32 math, stochastic rounding, sr.cuh; lr_eff = lr / dp)
+// to ITS copy of the weights and multicasts the new weights into every replica (multimem.st). The
+// reduced gradient is never written anywhere, there is no optimizer pass, and since each weight is
+// computed by exactly one rank the replicas stay bit-identical. Weights and gradients live at the same
+// symmetric offsets on all members (parallel/dp.py lays both out as one flat buffer each).
+// Per parameter and rank: 2 B read over NVLink (its slice only) + 2 B local read + 2 B multicast write.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(THREADS)
+allreduce_sgd_nvls_kernel(const __grid_constant__ Launch lp, size_t grad_off, size_t w_off, size_t count, float lr_eff,
+                          unsigned long long base_index, uint32_t step, uint32_t seed) {
+    Ctx x = make_ctx(lp);
+    const ccmpi_dev_comm& c = *x.c;
+    const size_t nvec = count / 8;
+    const size_t per = (nvec + c.size - 1) / c.size;
+    const size_t lo = per * c.rank, hi = min(nvec, lo + per);
+    const uint8_t* mgrad = c.mc_heap + grad_off;
+    uint8_t* mw = c.mc_heap + w_off;
+    const uint8_t* w_loc = c.heap[c.rank] + w_off;
+    block_barrier(x);       // every replica's gradients are final, nobody still reads the old weights
+    for_range_unrolled<8>(lo, hi, x, [&](size_t g, size_t stride, auto uc) {
+        constexpr int U = decltype(uc)::value;
+        uint4 gs[U], ws[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            gs[u] = ptx::multimem_ld_reduce_add_bf16x8(mgrad + (g + u * stride) * 16);
+            ws[u] = ptx::ld_v4(w_loc + (g + u * stride) * 16);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const __nv_bfloat162* gh = reinterpret_cast<const __nv_bfloat162*>(&gs[u]);
+            const __nv_bfloat162* wh = reinterpret_cast<const __nv_bfloat162*>(&ws[u]);
+            uint4 out;
+            uint32_t* o = reinterpret_cast<uint32_t*>(&out);
+            const unsigned long long pair0 = (base_index >> 1) + (unsigned long long)(g + u * stride) * 4;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float2 gf = __bfloat1622float2(gh[e]);
+                const float2 wf = __bfloat1622float2(wh[e]);
+                o[e] = sr::pack2(sr::axpy(wf.x, lr_eff, gf.x), sr::axpy(wf.y, lr_eff, gf.y), sr::bits(pair0 + e, step, seed));
+            }
+            ptx::multimem_st_v4(mw + (g + u * stride) * 16, out);
+        }
+    });
+    block_barrier(x);       // all slices of the new weights have landed everywhere
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -548,6 +610,24 @@ extern "C" int ccmpi_allreduce(const ccmpi_dev_comm* comms, int nvr, int algo, i
     }
     ccmpi::set_error("all-reduce: unsupported dtype %d", dtype);
     return CCMPI_ERR_UNSUPPORTED;
+}
+
+// Fused data-parallel step for one bucket: weights[w_off ...] = SR(weights - lr_eff * sum over replicas of
+// grads[grad_off ...]), bf16, `count` elements (multiple of 16), both offsets symmetric and 16-byte aligned.
+// Needs a multicast mapping (NVLS). lr_eff already contains the 1/dp of the average.
+extern "C" int ccmpi_allreduce_sgd_nvls(const ccmpi_dev_comm* comms, int nvr, size_t grad_off, size_t w_off, size_t count,
+                                        float lr_eff, unsigned long long base_index, unsigned step, unsigned seed,
+                                        int max_blocks, void* stream) {
+    Launch lp;
+    int rc = fill_launch(lp, comms, nvr);
+    if (rc) return rc;
+    if (count == 0) return CCMPI_OK;
+    CCMPI_REQUIRE(lp.c[0].mc_heap != nullptr, "the fused all-reduce + SGD kernel needs a multicast mapping (NVLS)");
+    CCMPI_REQUIRE(((grad_off | w_off) & 15) == 0 && count % 16 == 0 && base_index % 2 == 0,
+                  "all-reduce + SGD: 16-byte aligned offsets, count %% 16 == 0 (count = %zu), even base index", count);
+    const int blocks = clamp_blocks(count / 8 / lp.c[0].size, max_blocks);
+    return launch(allreduce_sgd_nvls_kernel, nvr, blocks, (cudaStream_t)stream, lp, grad_off, w_off, count, lr_eff, base_index,
+                  (uint32_t)step, (uint32_t)seed);
 }
 
 extern "C" int ccmpi_allgather(const ccmpi_dev_comm* comms, int nvr, size_t src_off, size_t dst_off, size_t rows,

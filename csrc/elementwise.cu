@@ -16,6 +16,7 @@
 
 #include "act.cuh"
 #include "host_common.h"
+#include "sr.cuh"
 
 namespace ew {
 
@@ -161,6 +162,26 @@ __global__ void __launch_bounds__(THREADS) mse_kernel(const __nv_bfloat16* __res
     }
 }
 
+// w -= lr * g for a flat run of bf16 weights, fp32 math, the new weight rounded stochastically (sr.cuh):
+// the optimizer pass for gradients that came out of a collective. 2 reads + 1 write of 2 bytes per parameter.
+// `base` = index of w[0] in the model's flat parameter numbering (random bits depend on it, not on addresses).
+__global__ void __launch_bounds__(THREADS) sgd_sr_kernel(__nv_bfloat16* __restrict__ w, const __nv_bfloat16* __restrict__ g,
+                                                         long long nvec, float lr, unsigned long long base, uint32_t step,
+                                                         uint32_t seed) {
+    for (long long i = blockIdx.x * (long long)THREADS + threadIdx.x; i < nvec; i += (long long)gridDim.x * THREADS) {
+        float x[8], d[8];
+        unpack8(ldg16(w + i * 8), x);
+        unpack8(ldg16(g + i * 8), d);
+        uint4 r;
+        uint32_t* ro = reinterpret_cast<uint32_t*>(&r);
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+            ro[e] = sr::pack2(sr::axpy(x[2 * e], lr, d[2 * e]), sr::axpy(x[2 * e + 1], lr, d[2 * e + 1]),
+                              sr::bits((base >> 1) + (unsigned long long)i * 4 + e, step, seed));
+        stg16(w + i * 8, r);
+    }
+}
+
 static int grid_for(long long work_items) {
     const int sms = ccmpi::device_sm_count();
     long long want = (work_items + THREADS - 1) / THREADS;
@@ -230,6 +251,17 @@ extern "C" int ccmpi_mse_fwd_bwd(const void* y, const void* t, void* dy, long lo
     float* partial = reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + 16);
     mse_kernel<<<grid, THREADS, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)y, (const __nv_bfloat16*)t, (__nv_bfloat16*)dy,
                                                            n / 8, 1.0f / (float)n, partial, ticket, (float*)loss);
+    CCMPI_CUDA_CHECK(cudaGetLastError());
+    return CCMPI_OK;
+}
+
+// SGD step on a flat run of bf16 weights with stochastic rounding: w[i] = SR(w[i] - lr * g[i]).
+extern "C" int ccmpi_sgd_sr_bf16(void* w, const void* g, long long n, float lr, unsigned long long base_index, unsigned step,
+                                 unsigned seed, void* stream) {
+    CCMPI_REQUIRE(w && g && n > 0 && n % 8 == 0 && aligned16(w) && aligned16(g) && base_index % 2 == 0,
+                  "sgd_sr: 16-byte aligned tensors with a multiple of 8 elements (n = %lld), even base index", n);
+    sgd_sr_kernel<<<grid_for(n / 8), THREADS, 0, (cudaStream_t)stream>>>((__nv_bfloat16*)w, (const __nv_bfloat16*)g, n / 8, lr,
+                                                                         base_index, step, seed);
     CCMPI_CUDA_CHECK(cudaGetLastError());
     return CCMPI_OK;
 }

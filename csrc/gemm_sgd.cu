@@ -7,9 +7,11 @@
 // the gradient is applied unrounded. The reference has no optimizer (or GEMM); this belongs to the
 // training step the new framework adds around its communicators.
 //
-// EXPERIMENTAL in round 1: compiled, not yet run on hardware; models use it only with
-// CCMPI_FUSED_SGD=1 and dp = 1. CTA-pair kernel, bf16 weights.
+// The new weight is rounded to bf16 STOCHASTICALLY (sr.cuh; aux1 = step counter, aux2 = seed; aux1 < 0
+// selects round-to-nearest): a step far below one bf16 ulp still moves the weights in expectation, with
+// no fp32 master copy. CTA-pair kernel, bf16 weights; the models use it when dp = 1.
 #include "gemm_host.h"
+#include "sr.cuh"
 
 namespace gemm {
 
@@ -22,6 +24,8 @@ struct SgdPolicy : PlainPolicy {
         const int ncols = min(32, p.N - col0);
         if (ncols <= 0) return;
         const float lr = __int_as_float(p.aux0);
+        const bool stochastic = p.aux1 >= 0;
+        const unsigned long long pair0 = ((unsigned long long)row * (unsigned long long)p.ldc + (unsigned long long)col0) >> 1;
         __nv_bfloat16* w = reinterpret_cast<__nv_bfloat16*>(p.C) + (long long)row * p.ldc + col0;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -33,9 +37,10 @@ struct SgdPolicy : PlainPolicy {
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
                     const float2 f = __bfloat1622float2(h[e]);
-                    const float lo = f.x - lr * __uint_as_float(v[8 * j + 2 * e]);
-                    const float hi = f.y - lr * __uint_as_float(v[8 * j + 2 * e + 1]);
-                    qo[e] = pack_bf16(__float_as_uint(lo), __float_as_uint(hi));
+                    const float lo = sr::axpy(f.x, lr, __uint_as_float(v[8 * j + 2 * e]));
+                    const float hi = sr::axpy(f.y, lr, __uint_as_float(v[8 * j + 2 * e + 1]));
+                    qo[e] = stochastic ? sr::pack2(lo, hi, sr::bits(pair0 + 4 * j + e, (uint32_t)p.aux1, (uint32_t)p.aux2))
+                                       : pack_bf16(__float_as_uint(lo), __float_as_uint(hi));
                 }
                 ptx::st_v4(w + 8 * j, q);
             }
@@ -62,6 +67,14 @@ static int launch_sgd(const Launch& lp, int grid, cudaStream_t stream) {
 
 extern "C" int ccmpi_gemm_sgd_bf16(const void* A, const void* B, void* W, int M, int N, int K, int lda, int ldb, int ldw,
                                    int a_mn_major, int b_mn_major, float lr, int num_sms, void* stream) {
+    return ccmpi_gemm_sgd_bf16_sr(A, B, W, M, N, K, lda, ldb, ldw, a_mn_major, b_mn_major, lr, -1, 0, num_sms, stream);
+}
+
+// `step` >= 0: stochastic rounding of the updated weights, random bits from (element, step, seed);
+// `step` < 0: round to nearest.
+extern "C" int ccmpi_gemm_sgd_bf16_sr(const void* A, const void* B, void* W, int M, int N, int K, int lda, int ldb, int ldw,
+                                      int a_mn_major, int b_mn_major, float lr, int step, unsigned seed, int num_sms,
+                                      void* stream) {
     using namespace gemm;
     int rc = check_shapes(M, N, K, lda, ldb, ldw, CCMPI_BF16);
     if (rc) return rc;
@@ -81,6 +94,8 @@ extern "C" int ccmpi_gemm_sgd_bf16(const void* A, const void* B, void* W, int M,
     rp.ldc = ldw;
     rp.M = M; rp.N = N; rp.K = K;
     rp.aux0 = __builtin_bit_cast(int, lr);
+    rp.aux1 = step;
+    rp.aux2 = (int)seed;
     const int pair_tiles = (((M + BM - 1) / BM + 1) / 2) * ((N + BN - 1) / BN);
     const int npairs = pair_tiles < sms / 2 ? pair_tiles : sms / 2;
     const cudaStream_t st = (cudaStream_t)stream;

@@ -298,12 +298,27 @@ int ccmpi_reduce_scatter_tight(const ccmpi_dev_comm* comms, int nvr, int dtype, 
 int ccmpi_allreduce_twoshot_tight(const ccmpi_dev_comm* comms, int nvr, int dtype, int op, size_t src_off, size_t dst_off,
                                   size_t tmp_off, size_t count, float scale, int max_blocks, void* stream);
 
-/* EXPERIMENTAL (compiled, not yet run on hardware in round 1): weight-gradient GEMM with the SGD
- * update in its epilogue, W[M][N] -= lr * (A * B), bf16 W updated in place from the fp32
- * accumulator (csrc/gemm_sgd.cu). For layers whose gradient needs no data-parallel reduction.
- * Operand layout flags as in ccmpi_gemm_bf16. */
+/* Weight-gradient GEMM with the SGD update in its epilogue, W[M][N] -= lr * (A * B), bf16 W updated in
+ * place from the fp32 accumulator (csrc/gemm_sgd.cu). For layers whose gradient needs no data-parallel
+ * reduction. Operand layout flags as in ccmpi_gemm_bf16. The _sr form rounds the new weights
+ * stochastically (step >= 0; random bits from (element, step, seed)) so that updates below one bf16 ulp
+ * are not lost; step < 0 = round to nearest, which is what the plain form does. The reference has no
+ * optimizer; it is part of the training step this framework adds around its communicators. */
 int ccmpi_gemm_sgd_bf16(const void* A, const void* B, void* W, int M, int N, int K, int lda, int ldb, int ldw,
                         int a_mn_major, int b_mn_major, float lr, int num_sms, void* stream);
+int ccmpi_gemm_sgd_bf16_sr(const void* A, const void* B, void* W, int M, int N, int K, int lda, int ldb, int ldw,
+                           int a_mn_major, int b_mn_major, float lr, int step, unsigned seed, int num_sms, void* stream);
+/* w[i] = SR(w[i] - lr * g[i]) on a flat run of n bf16 weights (n % 8 == 0): the optimizer pass for gradients
+ * that came out of a collective. base_index = position of w[0] in the model's flat parameter numbering. */
+int ccmpi_sgd_sr_bf16(void* w, const void* g, long long n, float lr, unsigned long long base_index, unsigned step,
+                      unsigned seed, void* stream);
+/* Data-parallel gradient all-reduce fused with that update (NVLS, bf16): every member sums its slice of all
+ * replicas' gradients in the switch, updates its slice of the weights and multicasts the new weights to every
+ * replica. grad_off / w_off: symmetric offsets of the bucket's gradients / weights; lr_eff = lr / dp.
+ * (The data-parallel all-reduce the reference implies with dp_comm, func_impl.py:60-62.) */
+int ccmpi_allreduce_sgd_nvls(const ccmpi_dev_comm* comms, int nvr, size_t grad_off, size_t w_off, size_t count,
+                             float lr_eff, unsigned long long base_index, unsigned step, unsigned seed, int max_blocks,
+                             void* stream);
 
 /* EXPERIMENTAL (compiled, not yet run on hardware in round 1): fp8 e4m3 GEMM on the CTA-pair
  * kernel, C[M][N] = scale * A[M][K] * B[N][K]^T, both operands K-major (tcgen05.mma.kind::f8f6f4).

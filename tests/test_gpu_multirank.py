@@ -58,3 +58,11 @@ def test_single_gpu_train_step():
     if gpu_count() < 1:
         pytest.skip("needs a GPU")
     _ok(run_ranks(1, ["tests/workers/w_layers.py", "1", "1"], transport="device"), "LAYERS OK mp=1 dp=1")
+
+
+def test_dp_allreduce_fused_with_sgd_update_on_every_group_size():
+    """multimem.ld_reduce of the gradients + stochastic-rounding update + multimem.st of the weights."""
+    for n in _ranks_for_box([2, 4, 8]):
+        p = run_ranks(n, ["tests/workers/w_dp_update.py"], transport="device")
+        assert p.returncode == 0, f"rc={p.returncode}\n{p.stdout[-3000:]}\n{p.stderr[-3000:]}"
+        assert f"DP UPDATE OK ranks={n}" in p.stdout or "DP UPDATE SKIPPED" in p.stdout, p.stdout[-2000:]

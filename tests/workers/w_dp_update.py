@@ -1,0 +1,53 @@
+"""Rank-side check of the data-parallel all-reduce fused with the SGD update (csrc/collectives.cu:
+allreduce_sgd_nvls_kernel) on real GPUs: every replica must end with the SAME bits, and those must be
+``SR(w - lr/dp * sum_over_replicas(g))`` as utils/sr.py states it. The switch's fp32 summation order is
+not specified, so a sum that lands exactly between two bf16 values may round either way: a handful of
+elements may differ from the oracle, by one ulp of the weight at most."""
+import torch
+
+from mpi4py import MPI
+from collective_communication_mpi_b200.ops import collectives as CO
+from collective_communication_mpi_b200.utils import sr
+
+world = MPI.COMM_WORLD
+rank, n = world.Get_rank(), world.Get_size()
+torch.cuda.set_device(rank)
+dev = world.device_comm()
+if not dev.has_mc:
+    if rank == 0:
+        print(f"DP UPDATE SKIPPED (no NVLS multicast) ranks={n}")
+    raise SystemExit(0)
+BF = torch.bfloat16
+for count, base, step in ((1 << 16, 0, 0), ((1 << 20) + 48 * 16, 4096, 12345)):
+    grads = world.symm_empty(count, BF)
+    weights = world.symm_empty(count, BF)
+    gw = torch.Generator(device="cuda").manual_seed(100)              # same weights everywhere
+    weights.copy_((torch.randn(count, device="cuda", generator=gw) * 0.02).to(BF))
+    gg = torch.Generator(device="cuda").manual_seed(200 + rank)       # every replica its own gradient
+    grads.copy_((torch.randn(count, device="cuda", generator=gg) * 0.01).to(BF))
+    w0 = weights.clone()
+    torch.cuda.synchronize()
+    world.Barrier()
+    lr = 1e-2
+    CO.allreduce_sgd(dev.comms, dev.heap.offset_of(grads), dev.heap.offset_of(weights), count, lr / n, base_index=base,
+                     step=step, seed=77)
+    torch.cuda.synchronize()
+    world.Barrier()
+    all_g = world.allgather(grads.float().cpu())
+    total = torch.zeros(count)
+    for g_ in all_g:
+        total += g_
+    want = sr.sgd_update(w0.cpu(), total.to(BF), lr / n, base, step, 77)
+    got = weights.cpu()
+    same = (got == want).float().mean().item()
+    ulp = torch.exp2(torch.floor(torch.log2(w0.float().abs().clamp_min(2.0 ** -30))) - 7).cpu()
+    worst = ((got.float() - want.float()).abs() / ulp).max().item()
+    assert same > 0.99 and worst <= 2.0, f"rank {rank}: {same:.4f} equal, worst {worst:.2f} ulp"
+    sums = world.allgather(int(got.view(torch.int16).to(torch.int64).sum()))
+    assert len(set(sums)) == 1, f"replicas diverged: {sums}"
+    assert (got != w0.cpu()).float().mean().item() > 0.05
+    world.symm_free(weights)
+    world.symm_free(grads)
+world.Barrier()
+if rank == 0:
+    print(f"DP UPDATE OK ranks={n}")

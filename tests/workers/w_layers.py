@@ -125,7 +125,8 @@ g_qkv = params[mp_idx].grad
 g_o = params[mp].grad[mp_idx * sh:(mp_idx + 1) * sh]
 g_1 = params[mp + 1].grad[:, mp_idx * (4 * H // mp):(mp_idx + 1) * (4 * H // mp)]
 g_2 = params[mp + 2].grad[mp_idx * (4 * H // mp):(mp_idx + 1) * (4 * H // mp)]
-sink_grads = step.sink.grads() if step.sink is not None else [None] * 4
+# (a sink whose reduction is the optimizer step never materialises the averaged gradient: only the weights can be checked)
+sink_grads = step.sink.grads() if step.sink is not None and not step.sink.fused_update else [None] * 4
 for name, layer, w0, gref, gbuf in zip(("qkv", "o", "fc1", "fc2"), model.tp_layers(), before, (g_qkv, g_o, g_1, g_2), sink_grads):
     scale = gref.abs().max().item()
     if gbuf is not None:
@@ -143,4 +144,4 @@ for name, layer, w0, gref, gbuf in zip(("qkv", "o", "fc1", "fc2"), model.tp_laye
     assert e < 0.05 * LR * scale + 2 * ulp, f"{name}: weight update mismatch {e} (update scale {LR * scale}, ulp {ulp})"
 world.Barrier()
 if rank == 0:
-    print(f"LAYERS OK mp={mp} dp={dp} sp={int(SP)} megatron={int(MEGATRON)} loss={loss.item():.4f} ar_launches={step.sink.launches if step.sink else 0} fused_sgd={int(step.fused_sgd)}")
+    print(f"LAYERS OK mp={mp} dp={dp} sp={int(SP)} megatron={int(MEGATRON)} loss={loss.item():.4f} ar_launches={step.sink.launches if step.sink else 0} fused_sgd={int(step.fused_sgd)} fused_update={int(bool(step.sink and step.sink.fused_update))}")
