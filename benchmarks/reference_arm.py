@@ -19,7 +19,7 @@ exit code is 0, as the task statement prescribes.
 
 Wall budget: one CPU step of this configuration takes tens of seconds (54 s on 8 cores, measured), so
 the requested ``--warmup W --steps K`` may not fit the caller's time limit. The first step is timed;
-when ``(W + K)`` steps would exceed ``CCMPI_REF_BUDGET_S`` (default 780 s) the arm runs as many as
+when ``(W + K)`` steps would exceed ``CCMPI_REF_BUDGET_S`` (default 720 s) the arm runs as many as
 fit (never fewer than 1 warm-up + 1 timed step), reports the counts it really ran in ``steps`` /
 ``warmup`` and says so in ``note``. Per-step time on the CPU is stable to a few per cent, so the
 tokens/s of a shortened run is the same measurement with a wider error bar, not a different one.
@@ -151,7 +151,7 @@ def run_reference(args, emit, grid_for, cfg):
     comm.Barrier()
     first = time.perf_counter() - t0
     first = max(comm.allgather(first))
-    budget = float(os.environ.get("CCMPI_REF_BUDGET_S", "780"))
+    budget = float(os.environ.get("CCMPI_REF_BUDGET_S", "720"))
     warm, steps, note = max(3, args.warmup), args.steps, None
     fit = int((budget - (time.perf_counter() - t_start)) / (first * 1.05))     # steps that still fit, first one excluded
     if (warm - 1) + steps > fit:

@@ -156,7 +156,7 @@ int gemm_scatter(const ccmpi_dev_comm* comms, int nvr, const void* const* A, con
         rp.epoch = epoch;
         rp.aux0 = BN;
         rp.aux1 = use_mc;
-        if (residual) {     // added to the reduced tile by the reducer (RsNPolicy::reduce_tile)
+        if (residual) {     // added to the reduced tile where it is finished (RsNPolicy::own_store / RsNSlotPolicy::reduce_tile)
             CCMPI_REQUIRE(out_dtype == CCMPI_BF16 && residual[v] != nullptr && res_ld % 8 == 0 && res_ld >= chunk,
                           "reduce-scatter residual: bf16 output, non-null pointer, row stride %% 8 == 0 and >= N/n");
             rp.epi_op = EPI_ADD;
@@ -166,7 +166,7 @@ int gemm_scatter(const ccmpi_dev_comm* comms, int nvr, const void* const* A, con
         rp.trace = pairs ? (unsigned long long*)trace : nullptr;
     }
     if (pairs) return dispatch2<Policy>(lp, BN, a_km != 0, b_kn != 0, out_dtype, per_rank * nvr, (cudaStream_t)stream, nvr > 1);
-    return dispatch<Policy>(lp, BN, a_km != 0, b_kn != 0, out_dtype, per_rank * nvr, (cudaStream_t)stream, nvr > 1);
+    return dispatch<typename Policy::SingleCta>(lp, BN, a_km != 0, b_kn != 0, out_dtype, per_rank * nvr, (cudaStream_t)stream, nvr > 1);
 }
 }  // namespace
 

@@ -93,7 +93,8 @@ struct AgKPolicy : PlainPolicy {
     static constexpr bool kPushFirst = true;
     static constexpr bool kNeedsStaging = true;
     struct State {
-        long long base;   // first work-item index of this CTA's next batch
+        long long base;   // first work-item index of this CTA's next batch (register path: 16-byte vectors)
+        long long item;   // ... bulk path: first piece index of this CTA's next slice
         int flagged;      // m-blocks [0, flagged) already signalled by this CTA
         int m_blocks;
         uint32_t stg;     // this lane's staging row in shared memory (0: register path)
@@ -102,6 +103,7 @@ struct AgKPolicy : PlainPolicy {
     };
     __device__ static void init_state(State& st, const RankParams& p, int cta, int nctas, int epi_tid, uint32_t stg, uint64_t* wbar) {
         st.base = (long long)cta * EPI_THREADS;
+        st.item = (long long)cta * 4;
         st.flagged = 0;
         st.m_blocks = p.comm.size == 1 ? 0 : (p.M + BM - 1) / BM;
         st.stg = stg;
@@ -116,11 +118,16 @@ struct AgKPolicy : PlainPolicy {
         }
     }
 
-    // Bulk-copy flavour of the push (CTA-pair kernel): every epilogue lane moves one 256-byte
-    // piece of the shard per slice -- cp.async.bulk global -> its staging row, then one
-    // cp.async.bulk per member out of it. The copies run on the TMA engine, so NVLink sees
-    // 256-byte bursts from ~19 k lanes at once instead of 16-byte stores that a few warps per SM
-    // cannot keep in flight.
+    // Bulk-copy flavour of the push (CTA-pair kernel). The TMA engine of an SM retires small bulk copies at
+    // a fixed rate of a few tens of nanoseconds each, whatever their size (the first version moved one
+    // 256-byte piece per epilogue LANE and measured 12 us per 32 KB slice -- 384 copies -- with the device
+    // trace, i.e. ~400 GB/s over the whole chip and a producer that waited 135 us for gathered chunks). So
+    // the copies are made as large as the staging area allows: each of the four epilogue WARPS moves one
+    // piece of up to 8 KB per slice -- whole shard rows when a row is at most 4 KB, a column segment of one
+    // row otherwise -- with ONE bulk load (the shard is contiguous) and one bulk store per row and member,
+    // issued by lane 0. Remote members are served first; the copy into this rank's own x_full (which only
+    // the backward dW GEMM reads) goes last.
+    static constexpr int PUSH_PIECE = 8192;
     template <typename OutT>
     __device__ static bool background(const RankParams& p, State& st, int cta, int nctas, int epi_tid, volatile uint32_t* bcast) {
         if (st.flagged >= st.m_blocks) return false;
@@ -130,42 +137,56 @@ struct AgKPolicy : PlainPolicy {
         // bulk path would send n-1 unicast copies (measured at mp = 8: 5.55 vs 5.73 ms per step).
         if (st.stg == 0 || ((p.aux1 & 1) != 0 && c.mc_heap != nullptr && c.size > 2))
             return background_regs<OutT>(p, st, cta, nctas, epi_tid, bcast);
+        const int lane = epi_tid & 31, w = epi_tid >> 5;
         const int row_bytes = p.chunk * 2;
-        const int PB = (row_bytes % 256 == 0) ? 256 : 128;         // piece size
-        const int ppr = row_bytes / PB;                            // pieces per shard row
-        const long long total = (long long)p.M * ppr;
-        const long long per_blk = (long long)BM * ppr;
-        const long long stride = (long long)nctas * EPI_THREADS;
+        int segs = 1;                                              // column segments per row (power of two)
+        while (row_bytes / segs > PUSH_PIECE) segs <<= 1;
+        const int seg_bytes = row_bytes / segs;
+        int rows_per = 1;                                          // whole rows per piece (power of two), contiguous source only
+        if (segs == 1 && p.aux0 == p.chunk)
+            while (rows_per * 2 * row_bytes <= PUSH_PIECE && rows_per < BM) rows_per <<= 1;
+        const long long items_per_blk = (long long)(BM / rows_per) * segs;
+        const long long total = ((long long)(p.M + rows_per - 1) / rows_per) * segs;
+        const long long stride = (long long)nctas * 4;            // one piece per epilogue warp and slice
         const uint8_t* x = c.heap[c.rank] + p.off0;
         const size_t src_ld = (size_t)p.aux0 * 2, dst_ld = (size_t)p.K * 2;
         const size_t col0 = (size_t)c.rank * row_bytes;
-        const long long i = st.base + epi_tid;
+        const long long i = st.item + w;
         const bool ok = i < total;
-        ptx::tma_store_wait_read<0>();                             // my previous piece has left my row
-        ptx::mbar_arrive_expect_tx(st.wbar, ok ? (uint32_t)PB : 0u);
-        size_t d = 0;
+        const uint32_t wbuf = st.stg - (uint32_t)lane * STG_ROW_STRIDE;          // this warp's 8.5 KB of staging
+        long long row0 = 0;
+        int seg = 0, nrows = 0;
         if (ok) {
-            const long long row = i / ppr;
-            const int w = (int)(i - row * ppr);
-            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(st.stg),
-                         "l"(x + (size_t)row * src_ld + (size_t)w * PB), "r"(PB), "r"(ptx::smem_u32(st.wbar))
+            const long long ri = i / segs;
+            seg = (int)(i - ri * segs);
+            row0 = ri * rows_per;
+            nrows = (int)min((long long)rows_per, (long long)p.M - row0);
+        }
+        const uint32_t bytes = ok ? (uint32_t)(nrows * seg_bytes) : 0u;
+        if (lane == 0) ptx::tma_store_wait_read<0>();              // my previous piece has left the staging buffer
+        ptx::mbar_arrive_expect_tx(st.wbar, lane == 0 ? bytes : 0u);
+        if (lane == 0 && ok) {
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(wbuf),
+                         "l"(x + (size_t)row0 * src_ld + (size_t)seg * seg_bytes), "r"(bytes), "r"(ptx::smem_u32(st.wbar))
                          : "memory");
-            d = p.off1 + (size_t)row * dst_ld + col0 + (size_t)w * PB;
         }
         ptx::mbar_wait(st.wbar, st.phase, 800);
         st.phase ^= 1;
-        if (ok) {
-#pragma unroll
-            for (int s = 0; s < CCMPI_MAX_RANKS; ++s)
-                if (s < c.size) ptx::bulk_s2g(c.heap[(c.rank + s) % c.size] + d, st.stg, PB);
+        if (lane == 0 && ok) {
+#pragma unroll 1
+            for (int s = 1; s <= c.size; ++s) {                    // peers first, this rank's own copy last
+                uint8_t* dst = c.heap[(c.rank + s) % c.size] + p.off1 + (size_t)row0 * dst_ld + col0 + (size_t)seg * seg_bytes;
+                for (int r = 0; r < nrows; ++r) ptx::bulk_s2g(dst + (size_t)r * dst_ld, wbuf + (uint32_t)(r * seg_bytes), seg_bytes);
+            }
         }
         ptx::tma_store_commit();
-        const long long next = st.base + stride;
-        int done = (int)min((long long)st.m_blocks, next / per_blk);
-        constexpr int GRANULE = 16;
+        // every piece of THIS CTA below `next` is on its way (its later pieces start at next + w)
+        const long long next = st.item + stride;
+        int done = (int)min((long long)st.m_blocks, next / items_per_blk);
+        constexpr int GRANULE = 8;
         done = (done / GRANULE) * GRANULE;
         if (next >= total) done = st.m_blocks;
-        st.base = next;
+        st.item = next;
         if (done <= st.flagged) return true;
         ptx::tma_store_wait<0>();          // my pieces have landed ...
         ptx::fence_proxy_async_all();      // ... and are ordered before the flag traffic
@@ -266,7 +287,8 @@ struct AgKPolicy : PlainPolicy {
 // sum the slots in rank order 0..n-1 (the order of np.sum(axis=0) in func_impl.py:186).
 // ================================================================================================
 //   aux0 : the launch's BN (tile width), so one policy type serves every tile shape
-struct RsNPolicy : PlainPolicy {
+struct RsNSlotPolicy : PlainPolicy {
+    using SingleCta = RsNSlotPolicy;
     static constexpr bool kEpiOps = false;   // own store: no fused elementwise epilogue
     static constexpr bool kCommCtas = false;
     static constexpr bool kStagedStore = true;
@@ -458,9 +480,176 @@ struct RsNPolicy : PlainPolicy {
     }
 };
 
+// ------------------------------------------------------------------------------------------------
+// GEMM -> reduce-scatter for the CTA-pair kernel: OWN TILES LAST, reduced in their own epilogue.
+//
+// RsNSlotPolicy writes every partial tile -- the owner's own included -- to a slot and lets reducer
+// passes sum the slots afterwards; the device trace showed those passes (latency-bound 128-thread loops
+// in the gaps and in the tail) costing 70-130 us per kernel at mp = 2. Here a rank first computes the
+// tiles its PEERS own (interleaved over the peers, pushed into their slots exactly as before) and its
+// own tiles at the end. By then the peers, who run the mirrored order, have long delivered their
+// partials for those tiles, so the epilogue of an own tile adds them to its accumulator straight out of
+// TMEM -- rank-ordered, every partial rounded to the slot type first, i.e. bit-identical to the slot
+// path and to np.sum(axis=0) order (func_impl.py:186) -- plus the optional residual (EPI_ADD), and
+// stores the final values. No slot write for own tiles, no reducer, no tail.
+// ------------------------------------------------------------------------------------------------
+struct RsNPolicy : RsNSlotPolicy {
+    using SingleCta = RsNSlotPolicy;        // the single-CTA kernel keeps the slot path
+    static constexpr bool kOwnTileDirect = true;
+    static constexpr bool kBackground = false;
+    struct State {};
+    __device__ static void init_state(State&, const RankParams&, int, int, int, uint32_t, uint64_t*) {}
+    template <typename OutT>
+    __device__ static bool background(const RankParams&, State&, int, int, int, volatile uint32_t*) { return false; }
+    template <typename OutT>
+    __device__ static void tail(const RankParams&, State&, int, int, int, volatile uint32_t*) {}
+
+    __device__ static TileCoord tile(const RankParams& p, int t, int mb, int nb) {
+        const int n = p.comm.size, per = nb_per_owner(p);
+        const int remote = (n - 1) * mb * per;
+        int owner, in_g;
+        if (t < remote) {
+            const int g = t % (n - 1);
+            in_g = t / (n - 1);
+            owner = (p.comm.rank + 1 + g) % n;
+        } else {
+            owner = p.comm.rank;
+            in_g = t - remote;
+        }
+        TileCoord tc = raster(in_g, mb, per);
+        tc.n_blk += owner * per;
+        return tc;
+    }
+    __device__ static bool is_own(const RankParams& p, const TileCoord& tc) { return tc.n_blk / nb_per_owner(p) == p.comm.rank; }
+
+    __device__ static void tile_done(const RankParams& p, const TileCoord& tc, int epi_tid) {
+        if (!is_own(p, tc)) RsNSlotPolicy::tile_done(p, tc, epi_tid);
+    }
+    // all 128 epilogue threads: every peer's partial of this own tile has landed in its slot
+    __device__ static void own_wait(const RankParams& p, const TileCoord& tc, int epi_tid) {
+        const ccmpi_dev_comm& c = p.comm;
+        const int n_local = tc.n_blk - c.rank * nb_per_owner(p);
+        if (epi_tid < c.size && epi_tid != c.rank)
+            ptx::wait_flag_ge_sys(user_flag(c, c.rank, flag_idx(p, tc.m_blk, n_local, epi_tid)), p.epoch, 600 + epi_tid);
+        epi_bar_sync();
+    }
+
+    // What an own tile adds to its accumulator, as a list of "pseudo-sources": the peers' slots in rank
+    // order, then the residual. The first PF of them are requested one 32-column chunk ahead of their use.
+    static constexpr int PF = 2;
+    template <typename OutT>
+    struct OwnPf {
+        uint4 v[PF][32 * sizeof(OutT) / 16];
+    };
+    __device__ static int own_nsrc(const RankParams& p) { return p.comm.size - 1 + (p.epi_op == EPI_ADD ? 1 : 0); }
+    template <typename OutT>
+    __device__ static void own_load(const RankParams& p, int k, int row, int lcol, uint4 (&out)[32 * sizeof(OutT) / 16]) {
+        constexpr int VPC = 32 * sizeof(OutT) / 16;
+        const ccmpi_dev_comm& c = p.comm;
+        const uint8_t* src;
+        if (k < c.size - 1) {
+            const int s = k < c.rank ? k : k + 1;
+            src = c.heap[c.rank] + p.off1 + (((size_t)s * p.M + row) * p.chunk + lcol) * sizeof(OutT);
+        } else {
+            src = reinterpret_cast<const uint8_t*>(p.epi_in) + ((size_t)row * p.epi_ld + lcol) * 2;   // bf16 residual
+        }
+        const int nv = (k < c.size - 1) ? VPC : 4;
+#pragma unroll
+        for (int j = 0; j < VPC; ++j)
+            if (j < nv) out[j] = ptx::ld_v4(src + 16 * j);
+    }
+    template <typename OutT>
+    __device__ static void own_prefetch(const RankParams& p, int row, int col0, OwnPf<OutT>& pf) {
+        if (row >= p.M) return;
+        const int lcol = col0 - p.comm.rank * p.chunk;
+        const int ns = own_nsrc(p);
+#pragma unroll
+        for (int k = 0; k < PF; ++k)
+            if (k < ns) own_load<OutT>(p, k, row, lcol, pf.v[k]);
+    }
+    template <typename OutT>
+    __device__ static void own_store(const RankParams& p, const TileCoord& tc, int row, int col0, uint32_t (&v)[32],
+                                     const OwnPf<OutT>& pf) {
+        if (row >= p.M) return;
+        constexpr int VPC = 32 * sizeof(OutT) / 16;
+        const ccmpi_dev_comm& c = p.comm;
+        const int lcol = col0 - c.rank * p.chunk;
+        const int ns = own_nsrc(p);
+        float own[32], acc[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            float f = __uint_as_float(v[i]);
+            if constexpr (sizeof(OutT) == 2) f = __bfloat162float(__float2bfloat16_rn(f));   // what a slot would hold
+            own[i] = f;
+        }
+        // Rank-ordered sum with this rank's partial at position `rank`. Every index into the prefetch
+        // registers is a compile-time constant (a run-time index would push them to local memory).
+        bool started = false;
+        auto add_own = [&] {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) acc[i] = started ? acc[i] + own[i] : own[i];
+            started = true;
+        };
+        auto add_bf16 = [&](const uint4* src) {
+            const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(src);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const float2 f = __bfloat1622float2(h[i]);
+                acc[2 * i] = started ? acc[2 * i] + f.x : f.x;
+                acc[2 * i + 1] = started ? acc[2 * i + 1] + f.y : f.y;
+            }
+            started = true;
+        };
+        auto add_slot = [&](const uint4* src) {
+            if constexpr (sizeof(OutT) == 2) {
+                add_bf16(src);
+            } else {
+                const float* f = reinterpret_cast<const float*>(src);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) acc[i] = started ? acc[i] + f[i] : f[i];
+                started = true;
+            }
+        };
+#pragma unroll
+        for (int k = 0; k < CCMPI_MAX_RANKS - 1; ++k) {
+            if (k < c.size - 1) {
+                if (k == c.rank) add_own();
+                if (k < PF) {
+                    add_slot(pf.v[k < PF ? k : 0]);
+                } else {                            // more peers than prefetch slots: fetch now
+                    uint4 late[VPC];
+                    own_load<OutT>(p, k, row, lcol, late);
+                    add_slot(late);
+                }
+            }
+        }
+        if (c.rank >= c.size - 1) add_own();
+        if (p.epi_op == EPI_ADD) {
+            const int kr = c.size - 1;              // the residual is the last pseudo-source
+            bool done = false;
+#pragma unroll
+            for (int k = 0; k < PF; ++k)
+                if (k == kr) {
+                    add_bf16(pf.v[k]);
+                    done = true;
+                }
+            if (!done) {
+                uint4 late[VPC];
+                own_load<OutT>(p, kr, row, lcol, late);
+                add_bf16(late);
+            }
+        }
+        (void)ns;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(acc[i]);
+        store_row32<OutT>(reinterpret_cast<OutT*>(p.C) + (size_t)row * p.ldc + lcol, v, 32, false);
+    }
+};
+
 // GEMM -> all-reduce: RsN, but the reducer broadcasts and a final cross-rank barrier makes sure
 // every rank's output is complete when its kernel ends.
-struct ArPolicy : RsNPolicy {
+struct ArPolicy : RsNSlotPolicy {
+    using SingleCta = ArPolicy;
     // peers' kernels store into our output: they must not start before we are done with the
     // previous contents
     __device__ static void prologue(const RankParams& p, int cta, int nctas, int epi_tid) {

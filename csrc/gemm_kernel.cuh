@@ -57,6 +57,7 @@ struct PlainPolicy {
     static constexpr bool kCommCtas = false;
     static constexpr bool kStagedStore = false;   // CTA-pair kernel: stage tiles in smem + bulk copies
     static constexpr bool kNeedsStaging = false;  // CTA-pair kernel: reserve the per-lane staging rows
+    static constexpr bool kOwnTileDirect = false; // CTA-pair kernel, staged policies: some tiles are finished in place (RsNPolicy)
 
     // Background work: something the epilogue warps do while no accumulator is ready (pushing a
     // gathered operand, reducing scattered tiles). `State` carries its progress.

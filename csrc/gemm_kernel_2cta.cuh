@@ -28,9 +28,7 @@ namespace gemm {
 // output row in shared memory and ships them with one cp.async.bulk per destination, so NVLink
 // sees 256-byte bursts instead of 16-byte stores from registers. Rows are padded by 16 bytes,
 // which makes the lanes' 16-byte shared stores conflict-free.
-constexpr int STG_CHUNK_BYTES = 256;
-constexpr int STG_ROW_STRIDE = STG_CHUNK_BYTES + 16;
-constexpr int STG_BYTES = 4 * 32 * STG_ROW_STRIDE;       // 4 epilogue warps x 32 rows
+// (STG_CHUNK_BYTES / STG_ROW_STRIDE / STG_BYTES live in gemm_tcgen05.cuh: the policies use them too)
 
 template <int BN, bool STAGED = false>
 struct Cfg2 {
@@ -50,6 +48,12 @@ struct Cfg2 {
 // only). A K-block is always one 128-byte swizzle row, i.e. 64 bf16 or 128 fp8 elements, and an MMA
 // always consumes 32 bytes of K, so the shared-memory descriptors and the pipeline are identical;
 // only the instruction kind, the instruction descriptor and the K coordinates differ.
+template <typename Policy>
+__device__ __forceinline__ bool own_tile(const RankParams& p, const TileCoord& tc) {
+    if constexpr (Policy::kOwnTileDirect) return Policy::is_own(p, tc);
+    else return false;
+}
+
 template <int BN, bool A_MN, bool B_MN, typename OutT, typename Policy, int EB = 2>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 gemm_kernel_2cta(const __grid_constant__ Launch lp) {
@@ -321,6 +325,30 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
                         }
                     }
                     if (valid) Policy::template store<OutT>(p, tc, row, tc.n_blk * BN + c, v);
+                }
+            } else if (Policy::kOwnTileDirect && valid && own_tile<Policy>(p, tc)) {
+                // a tile this rank owns (reduce-scatter): add the peers' partials and store the final values
+                if constexpr (Policy::kOwnTileDirect) {
+                    Policy::own_wait(p, tc, epi_tid);
+                    typename Policy::template OwnPf<OutT> pf_nxt;
+                    Policy::template own_prefetch<OutT>(p, row, tc.n_blk * BN, pf_nxt);
+#pragma unroll 1
+                    for (int c = 0; c < BN; c += 32) {
+                        uint32_t v[32];
+                        ptx::tmem_ld_32x32b_x32(taddr + c, v);
+                        const typename Policy::template OwnPf<OutT> pf_cur = pf_nxt;
+                        if (c + 32 < BN) Policy::template own_prefetch<OutT>(p, row, tc.n_blk * BN + c + 32, pf_nxt);
+                        ptx::tmem_ld_wait();
+                        if (c + 32 >= BN) {
+                            ptx::tc_fence_before();
+                            __syncwarp();
+                            if (lane == 0) {
+                                if (leader) ptx::mbar_arrive(&tmem_empty[acc]);
+                                else ptx::mbar_arrive_cluster(&tmem_empty[acc], 0);
+                            }
+                        }
+                        Policy::template own_store<OutT>(p, tc, row, tc.n_blk * BN + c, v, pf_cur);
+                    }
                 }
             } else {
                 constexpr int CW = STG_CHUNK_BYTES / (int)sizeof(OutT);   // columns per staged chunk

@@ -92,7 +92,7 @@ int encode(CUtensorMap* out, const void* base, long long rows, long long cols, l
 
 template <int BN, bool A_MN, bool B_MN, typename OutT>
 int run(const Launch& lp, int grid, cudaStream_t stream) {
-    auto kern = gemm_kernel<BN, A_MN, B_MN, OutT, RsNPolicy>;
+    auto kern = gemm_kernel<BN, A_MN, B_MN, OutT, RsNSlotPolicy>;
     CCMPI_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM_BYTES));
     kern<<<grid, NUM_THREADS, Cfg<BN>::SMEM_BYTES, stream>>>(lp);
     CCMPI_CUDA_CHECK(cudaGetLastError());

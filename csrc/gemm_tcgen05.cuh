@@ -23,6 +23,11 @@ constexpr int UMMA_K = 16;   // fixed for 16-bit inputs
 constexpr int NUM_THREADS = 192;
 constexpr int EPI_WARP0 = 2;  // first epilogue warp
 constexpr int EPI_THREADS = 128;
+// staging area of the CTA-pair kernel's epilogue warps: one 256-byte row (+16 bytes of padding) per lane,
+// i.e. 8.5 KB contiguous per warp
+constexpr int STG_CHUNK_BYTES = 256;
+constexpr int STG_ROW_STRIDE = STG_CHUNK_BYTES + 16;
+constexpr int STG_BYTES = 4 * 32 * STG_ROW_STRIDE;       // 4 epilogue warps x 32 rows
 
 template <int BN>
 struct Cfg {

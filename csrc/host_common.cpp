@@ -75,6 +75,15 @@ int make_tmap_2d(CUtensorMap* out, const void* base, int elem_bytes, long long r
     }
     auto encode = drv<EncodeTiledFn>("cuTensorMapEncodeTiled");
     if (!encode) return CCMPI_ERR_CUDA;
+    // Encoding a map over a VMM-mapped address (the symmetric heap) makes the driver look the allocation up,
+    // which needs a current context. A thread that has issued no runtime call yet -- autograd's worker thread
+    // entering its first backward node -- has none bound (CUDA_ERROR_INVALID_CONTEXT); bind the device's
+    // primary context once per thread.
+    static thread_local bool ctx_bound = false;
+    if (!ctx_bound) {
+        CCMPI_CUDA_CHECK(cudaFree(nullptr));
+        ctx_bound = true;
+    }
     CCMPI_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA operand base %p is not 16-byte aligned", base);
     CCMPI_REQUIRE((ld * elem_bytes) % 16 == 0, "TMA operand leading dimension %lld (x%d B) is not a multiple of 16 B", ld,
                   elem_bytes);
