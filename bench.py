@@ -190,16 +190,35 @@ def run_gpu(args, impl: str):
         while losses.pending:
             losses.pop()
 
-    for i in range(max(3, args.warmup)):
-        device_step(i)
+    # Both timed regions are prepared the same way: idle, then W warm-up steps of the region's own kind, then
+    # K timed steps. A B200 at its power cap (sw_power_cap is reported in "clocks") drops its clocks within a
+    # few tenths of a second of sustained load -- measured here: the same 20 device steps take 7.16 ms/step
+    # first and 8.24 ms/step when repeated right after the end-to-end region -- so without the idle the
+    # region that happens to run second would be charged for the first.
+    idle_s = float(os.environ.get("CCMPI_BENCH_IDLE_S", "2.0"))
+    warm = max(3, args.warmup)
+
+    def settle(kind):
+        torch.cuda.synchronize()
+        time.sleep(idle_s)
+        if kind == "device":
+            for i in range(warm):
+                device_step(i)
+        else:
+            e2e_loop(warm)
+
+    settle("device")
     sampler = ClockSampler(local)
     time.sleep(0.25)
     before = N.LAUNCHES[0]
     ms, t0, t1 = timed(device_step, args.steps)
     launches = N.LAUNCHES[0] - before
     clocks = sampler.summary(t0, t1)
-    e2e_loop(2)
-    ms_e2e, _, _ = timed(lambda i: e2e_loop(args.steps) if i == 0 else None, 1)
+    settle("e2e")
+    sampler = ClockSampler(local)
+    time.sleep(0.25)
+    ms_e2e, t0, t1 = timed(lambda i: e2e_loop(args.steps) if i == 0 else None, 1)
+    clocks_e2e = sampler.summary(t0, t1)
     if os.environ.get("CCMPI_BENCH_DEBUG") == "1":      # stderr only: is the e2e gap order / heat or copies?
         ms2, _, _ = timed(device_step, args.steps)
         ms3, _, _ = timed(lambda i: e2e_loop(args.steps) if i == 0 else None, 1)
@@ -218,16 +237,17 @@ def run_gpu(args, impl: str):
     if rank == 0:
         emit({
             "metric": METRIC, "value": round(value, 1), "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
-            "warmup": max(3, args.warmup), "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True,
+            "warmup": warm, "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": impl,
             "config": {"model": f"transformer FC layers fc_q/k/v/o + fc1/fc2, hidden {HIDDEN}, ffn {FFN_MULT}x (random init)"
                        + (" [TINY smoke override, not a benchmark]" if os.environ.get("CCMPI_BENCH_TINY") else ""),
                        "global_batch": SEQS_PER_REPLICA * dp, "seq_len": SEQ, "parallelism": f"mp{mp}xdp{dp}",
                        "tokens_per_replica": tokens, "optimizer": "sgd", "l2": "per-step working set (weights 200 MB + "
-                       "activations > 1 GB per GPU) exceeds the 126 MB L2; inputs rotate over 4 batches"},
+                       "activations > 1 GB per GPU) exceeds the 126 MB L2; inputs rotate over 4 batches",
+                       "protocol": f"each timed region: {idle_s:g} s idle, {warm} warm-up steps of its own kind, {args.steps} timed steps"},
             "clocks": clocks,
             "e2e": {"value": round(e2e, 1), "unit": "tokens/s", "h2d_bytes_per_step": int(2 * tokens * shard * 2),
-                    "d2h_bytes_per_step": 4, "ms_per_step": round(ms_e2e / args.steps, 4)},
+                    "d2h_bytes_per_step": 4, "ms_per_step": round(ms_e2e / args.steps, 4), "clocks": clocks_e2e},
             "gpu_launches": int(launches) if impl == "ours" else 0,
             **({"selfcheck": check} if check is not None else {}),
             "gemm_tflops_per_gpu": round(tflops_per_gpu, 1),

@@ -17,6 +17,7 @@ run() { local label=$1 limit=$2; shift 2
 torchrun_() { P=$((P + 1)); python -m torch.distributed.run --nnodes=1 --nproc-per-node "$NG" --master-addr 127.0.0.1 --master-port $P "$@"; }
 launch_() { python -m collective_communication_mpi_b200.launch -n "$NG" --transport device "$@"; }
 export -f torchrun_ launch_; export NG P
+[ "$NG" -ge 8 ] && export CCMPI_TEST_LARGEST_ONLY=1     # budgeted box: multi-rank tests at the largest group size only
 run tests 1500 python -m pytest tests -x -q -m gpu
 run bench_ours 400 bash -c 'torchrun_ bench.py --gpus $NG --steps 20 --warmup 5'
 run bench_nccl 400 bash -c 'torchrun_ bench.py --impl nccl --gpus $NG --steps 20 --warmup 5'
@@ -25,5 +26,13 @@ run fused 600 bash -c 'launch_ python benchmarks/fused_bench.py'
 run seq 600 bash -c 'launch_ python benchmarks/seq_bench.py'
 run e2e_probe 300 python scripts/e2e_probe.py
 run profile 300 bash -c 'torchrun_ benchmarks/profile_step.py ours'
+if [ "$NG" -ge 8 ]; then
+    # the N = 4 point of the scaling curve on the first four GPUs, both GPU arms
+    export NG4=4
+    run bench4_ours 400 bash -c 'P=$((P + 11)); CUDA_VISIBLE_DEVICES=0,1,2,3 python -m torch.distributed.run --nnodes=1 --nproc-per-node 4 --master-addr 127.0.0.1 --master-port $P bench.py --gpus 4 --steps 20 --warmup 5'
+    run bench4_nccl 400 bash -c 'P=$((P + 12)); CUDA_VISIBLE_DEVICES=0,1,2,3 python -m torch.distributed.run --nnodes=1 --nproc-per-node 4 --master-addr 127.0.0.1 --master-port $P bench.py --impl nccl --gpus 4 --steps 20 --warmup 5'
+    # one CPU step of the reference arm at N = 8 (how long the driver's run of that arm will take)
+    run ref8_probe 400 bash -c 'P=$((P + 13)); CCMPI_REF_BUDGET_S=${REF_PROBE_BUDGET_S:-60} python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port $P bench.py --impl reference --gpus 8 --steps 2 --warmup 3'
+fi
 [ -n "$EXTRA" ] && run extra 900 bash -c "$EXTRA"
 cat "$OUT"

@@ -1,8 +1,9 @@
 """Rank-side check of the data-parallel all-reduce fused with the SGD update (csrc/collectives.cu:
 allreduce_sgd_nvls_kernel) on real GPUs: every replica must end with the SAME bits, and those must be
 ``SR(w - lr/dp * sum_over_replicas(g))`` as utils/sr.py states it. The switch's fp32 summation order is
-not specified, so a sum that lands exactly between two bf16 values may round either way: a handful of
-elements may differ from the oracle, by one ulp of the weight at most."""
+not specified, and a sum that lands exactly between two bf16 values is not rounded the way torch rounds it
+(measured: 0.36 % of the elements of two random bf16 gradients, the tie rate): those few elements may differ
+from the oracle, by one ulp of the new weight at most."""
 import torch
 
 from mpi4py import MPI
@@ -40,9 +41,11 @@ for count, base, step in ((1 << 16, 0, 0), ((1 << 20) + 48 * 16, 4096, 12345)):
     want = sr.sgd_update(w0.cpu(), total.to(BF), lr / n, base, step, 77)
     got = weights.cpu()
     same = (got == want).float().mean().item()
-    ulp = torch.exp2(torch.floor(torch.log2(w0.float().abs().clamp_min(2.0 ** -30))) - 7).cpu()
+    # (ulp of the NEW weight: a weight near zero moves by many of its old ulps in one step)
+    big = torch.maximum(want.float().abs(), got.float().abs()).clamp_min(2.0 ** -30)
+    ulp = torch.exp2(torch.floor(torch.log2(big)) - 7)
     worst = ((got.float() - want.float()).abs() / ulp).max().item()
-    assert same > 0.99 and worst <= 2.0, f"rank {rank}: {same:.4f} equal, worst {worst:.2f} ulp"
+    assert same > 0.99 and worst <= 1.0, f"rank {rank}: {same:.4f} equal, worst {worst:.2f} ulp"
     sums = world.allgather(int(got.view(torch.int16).to(torch.int64).sum()))
     assert len(set(sums)) == 1, f"replicas diverged: {sums}"
     assert (got != w0.cpu()).float().mean().item() > 0.05
