@@ -59,6 +59,9 @@ def main():
     # ---- all-gather -> GEMM: forward of column layers, backward-dx of row layers ------------
     cases = [(f"ag_gemm fwd {nm}", din, dout // n, True) for nm, din, dout in shapes] + \
             [(f"ag_gemm bwd-dx {nm}", dout, din // n, False) for nm, din, dout in rshapes]
+    only = os.environ.get("FB_ONLY", "")      # "ag" / "rs": one family only (kernel work in progress)
+    if only == "rs":
+        cases = []
     for name, K, Nl, b_kn in cases:
         op = F.AllGatherGemm(comm, M, K)
         x = (torch.randn(M, K // n, device="cuda") * 0.5).bfloat16()
@@ -90,6 +93,8 @@ def main():
     # ---- GEMM -> reduce-scatter: forward of row layers, backward-dx of column layers --------
     cases = [(f"gemm_rs fwd {nm}", din // n, dout, True) for nm, din, dout in rshapes] + \
             [(f"gemm_rs bwd-dx {nm}", dout // n, din, False) for nm, din, dout in shapes]
+    if only == "ag":
+        cases = []
     for name, K, Nf, b_kn in cases:
         op = F.GemmReduceScatter(comm, M, Nf)
         a = (torch.randn(M, K, device="cuda") * 0.5).bfloat16()

@@ -96,6 +96,7 @@ struct AgKPolicy : PlainPolicy {
         long long base;   // first work-item index of this CTA's next batch (register path: 16-byte vectors)
         long long item;   // ... bulk path: first piece index of this CTA's next slice
         int pending;      // ... bulk path: m-blocks covered by the slices issued so far (published one slice later)
+        bool local_started, local_done;   // ... bulk path: pass 1 (copy into this rank's own x_full)
         int flagged;      // m-blocks [0, flagged) already signalled by this CTA
         int m_blocks;
         uint32_t stg;     // this lane's staging row in shared memory (0: register path)
@@ -106,6 +107,7 @@ struct AgKPolicy : PlainPolicy {
         st.base = (long long)cta * EPI_THREADS;
         st.item = (long long)cta * 4;
         st.pending = 0;
+        st.local_started = st.local_done = false;
         st.flagged = 0;
         st.m_blocks = p.comm.size == 1 ? 0 : (p.M + BM - 1) / BM;
         st.stg = stg;
@@ -132,13 +134,22 @@ struct AgKPolicy : PlainPolicy {
     static constexpr int PUSH_PIECE = 8192;
     template <typename OutT>
     __device__ static bool background(const RankParams& p, State& st, int cta, int nctas, int epi_tid, volatile uint32_t* bcast) {
-        if (st.flagged >= st.m_blocks) return false;
         const ccmpi_dev_comm& c = p.comm;
         // Groups larger than two with an NVLS multicast mapping keep the register path: one
         // multimem.st per vector leaves the GPU once and is replicated by the switch, while the
         // bulk path would send n-1 unicast copies (measured at mp = 8: 5.55 vs 5.73 ms per step).
         if (st.stg == 0 || ((p.aux1 & 1) != 0 && c.mc_heap != nullptr && c.size > 2))
             return background_regs<OutT>(p, st, cta, nctas, epi_tid, bcast);
+        // Two passes over the shard. Pass 0 serves the PEERS, who are waiting for it, and publishes the
+        // ready flags; pass 1 copies the shard into this rank's own x_full, which nothing reads before the
+        // backward dW GEMM -- so it must not share the copy engine's time with what the peers' tensor
+        // cores are starved for.
+        if (st.m_blocks == 0 || st.local_done) return false;
+        const bool local_pass = st.flagged >= st.m_blocks;
+        if (local_pass && !st.local_started) {
+            st.local_started = true;
+            st.item = (long long)cta * 4;
+        }
         const int lane = epi_tid & 31, w = epi_tid >> 5;
         const int row_bytes = p.chunk * 2;
         int segs = 1;                                              // column segments per row (power of two)
@@ -175,13 +186,22 @@ struct AgKPolicy : PlainPolicy {
         ptx::mbar_wait(st.wbar, st.phase, 800);
         st.phase ^= 1;
         if (lane == 0 && ok) {
+            const int s0 = local_pass ? 0 : 1, s1 = local_pass ? 1 : c.size;
 #pragma unroll 1
-            for (int s = 1; s <= c.size; ++s) {                    // peers first, this rank's own copy last
+            for (int s = s0; s < s1; ++s) {
                 uint8_t* dst = c.heap[(c.rank + s) % c.size] + p.off1 + (size_t)row0 * dst_ld + col0 + (size_t)seg * seg_bytes;
                 for (int r = 0; r < nrows; ++r) ptx::bulk_s2g(dst + (size_t)r * dst_ld, wbuf + (uint32_t)(r * seg_bytes), seg_bytes);
             }
         }
         ptx::tma_store_commit();
+        if (local_pass) {
+            st.item += stride;
+            if (st.item >= total) {                        // this CTA has no pieces left
+                ptx::tma_store_wait<0>();
+                st.local_done = true;
+            }
+            return true;
+        }
         // every piece of THIS CTA below `next` is on its way (its later pieces start at next + w)
         const long long next = st.item + stride;
         int done = (int)min((long long)st.m_blocks, next / items_per_blk);
