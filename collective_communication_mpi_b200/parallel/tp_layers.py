@@ -88,8 +88,8 @@ def _weight_grad(layer, x, dy):
     if layer.sgd_lr is not None:
         # no data-parallel reduction needed: the dW kernel applies the step itself (W = SR(W - lr * x^T dy))
         with torch.no_grad():
-            layer._gemm_sgd(layer.weight.data, x, dy, layer.sgd_lr, a_km=True, b_kn=True, step=layer.sgd_step,
-                            seed=layer.sgd_seed, num_sms=layer.num_sms)
+            layer._gemm_sgd(layer.weight.data, x, dy, layer.sgd_lr, a_km=True, b_kn=True, step=getattr(layer, "sgd_step", None),
+                            seed=getattr(layer, "sgd_seed", 0), num_sms=layer.num_sms)
         return None
     sink = getattr(layer, "grad_sink", None)
     if sink is None:

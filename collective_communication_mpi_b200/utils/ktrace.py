@@ -62,6 +62,13 @@ def summary(buf: torch.Tensor, sm_mhz: float = 1965.0) -> dict:
     out = {"ctas": int(t.shape[0]), "kernel_us": round(float(t[:, 8].max() - t[:, 0].min()) / 1e3, 1),
            "start_skew_us": round(float(t[:, 0].max() - t[:, 0].min()) / 1e3, 1),
            "tiles_per_cta": round(float(t[:, 9].float().mean()), 2)}
+    out["prod_slow_calls"] = round(float(t[:, 10].float().mean()), 1)
+    out["prod_max_us"] = round(float(t[:, 11].float().max()) * cyc, 1)
+    first = t[:, 12][t[:, 12] != 0]
+    if first.numel():
+        out["first_slow_wait_done_us"] = {"mean": round(float((first - t[:, 0].min()).float().mean()) / 1e3, 1),
+                                          "max": round(float((first - t[:, 0].min()).float().max()) / 1e3, 1)}
+    out["epi_slices"] = round(float(t[:, 13].float().mean()), 1)
     for i, name in enumerate(SLOTS):
         if name in ("t0_ns", "t1_ns", "tiles"):
             continue

@@ -138,7 +138,8 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            long long tr_flag = 0, tr_empty = 0;
+            long long tr_flag = 0, tr_empty = 0, tr_max = 0, tr_slow = 0;
+            unsigned long long tr_first = 0;
             for (int t = pair; t < ntiles; t += npairs) {
                 const TileCoord tc = my_tile(t);
                 const bool valid = tc.m_blk < m_blocks;
@@ -148,7 +149,15 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
                     if (valid) {
                         const long long c0 = trace ? clock64() : 0;
                         Policy::kblock(p, tc, it, k0, ta, a_k0, a_m0);
-                        if (trace) tr_flag += clock64() - c0;
+                        if (trace) {
+                            const long long d = clock64() - c0;
+                            tr_flag += d;
+                            if (d > tr_max) tr_max = d;
+                            if (d > 2000) {
+                                if (tr_slow == 0) tr_first = ptx::globaltimer_ns();
+                                ++tr_slow;
+                            }
+                        }
                     } else {
                         // phantom m-block of an odd tail: its rows are out of range, TMA zero-fills
                         // them and there is nothing to wait for -- but the B half it loads feeds the
@@ -190,6 +199,9 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
             if (trace) {
                 trace[TR_PROD_FLAG] = (unsigned long long)tr_flag;
                 trace[TR_PROD_EMPTY] = (unsigned long long)tr_empty;
+                trace[TR_PROD_SLOW] = (unsigned long long)tr_slow;
+                trace[TR_PROD_MAX] = (unsigned long long)tr_max;
+                trace[TR_PROD_FIRST_NS] = tr_first;
             }
         }
         __syncwarp();
@@ -258,7 +270,7 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
                 while (Policy::template background<OutT>(p, st, cta, nctas, epi_tid, bcast + 2)) {}
         }
         uint32_t poll = 0;
-        long long tr_bg = 0, tr_wait = 0;
+        long long tr_bg = 0, tr_wait = 0, tr_slices = 0;
         const bool tr_on = trace != nullptr && epi_tid == 0;
         for (int t = pair; t < ntiles; t += npairs, ++local) {
             const TileCoord tc = my_tile(t);
@@ -285,6 +297,7 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
                     epi_bar_sync();
                     if (*w != 0) break;
                     if (!Policy::template background<OutT>(p, st, cta, nctas, epi_tid, bcast + 2)) break;
+                    ++tr_slices;
                 }
             }
             const long long c_w = tr_on ? clock64() : 0;
@@ -402,6 +415,7 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
             trace[TR_EPI_TAIL] = (unsigned long long)(clock64() - c_tail);
             trace[TR_T1_NS] = ptx::globaltimer_ns();
             trace[TR_TILES] = (unsigned long long)local;
+            trace[TR_EPI_SLICES] = (unsigned long long)tr_slices;
         }
     }
 

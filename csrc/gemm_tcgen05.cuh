@@ -93,6 +93,10 @@ enum TraceSlot : int {
     TR_EPI_TAIL = 7,     // epilogue: cycles in the policy's tail (left-over pushes / reductions / barriers)
     TR_T1_NS = 8,        // %globaltimer when the epilogue warps are done
     TR_TILES = 9,        // tiles this CTA computed
+    TR_PROD_SLOW = 10,   // TMA producer: kblock calls that took more than ~1 us
+    TR_PROD_MAX = 11,    // TMA producer: longest single kblock call
+    TR_PROD_FIRST_NS = 12, // TMA producer: ns from kernel entry until its first slow kblock call returned
+    TR_EPI_SLICES = 13,  // epilogue: background slices executed
     TRACE_WORDS = 16
 };
 
