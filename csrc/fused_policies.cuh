@@ -80,6 +80,27 @@ struct AgKPolicy : PlainPolicy {
         }
     }
 
+    __device__ static int num_kchunks(const RankParams& p) { return p.comm.size; }
+    __device__ static void kchunk(const RankParams& p, const TileCoord& tc, int ci, bool wait, int& k_base,
+                                  const CUtensorMap*& ta, int& a_k_base, int& a_m0) {
+        const ccmpi_dev_comm& c = p.comm;
+        int src = c.rank + ci;
+        if (src >= c.size) src -= c.size;
+        k_base = src * p.chunk;
+        a_m0 = tc.m_blk * BM;
+        if (src == c.rank) {
+            ta = &p.tmap_a2;
+            a_k_base = 0;
+        } else {
+            if (wait) {
+                ptx::wait_flag_ge_sys(user_flag(c, c.rank, ready_idx(p, src, tc.m_blk)), p.epoch * (unsigned)p.aux2, 500 + src);
+                ptx::fence_proxy_async_all();  // peer's stores -> our TMA reads
+            }
+            ta = &p.tmap_a;
+            a_k_base = k_base;
+        }
+    }
+
     // The gather itself. There are no dedicated communication CTAs: the four epilogue warps of
     // EVERY CTA are idle whenever no accumulator is ready (always so at kernel start), and in
     // those gaps -- never while a finished accumulator is waiting -- they push this rank's shard -- 16-byte vectors, 8 loads in flight per thread, ~19 k threads

@@ -62,6 +62,26 @@ struct AgMPolicy : PlainPolicy {
         }
     }
 
+    __device__ static void kchunk(const RankParams& p, const TileCoord& tc, int ci, bool wait, int& k_base,
+                                  const CUtensorMap*& ta, int& a_k_base, int& a_m0) {
+        const ccmpi_dev_comm& c = p.comm;
+        k_base = 0;
+        a_k_base = 0;
+        const int src = tc.m_blk / mbpr(p);
+        const int lm = tc.m_blk - src * mbpr(p);
+        if (src == c.rank) {
+            ta = &p.tmap_a2;
+            a_m0 = lm * BM;
+        } else {
+            if (wait) {
+                ptx::wait_flag_ge_sys(user_flag(c, c.rank, ready_idx(p, src, lm)), p.epoch * (unsigned)p.aux2, 520 + src);
+                ptx::fence_proxy_async_all();
+            }
+            ta = &p.tmap_a;
+            a_m0 = tc.m_blk * BM;
+        }
+    }
+
     struct State {
         long long base;
         int flagged, m_blocks;

@@ -82,6 +82,19 @@ struct PlainPolicy {
         a_k0 = k0;
         a_m0 = tc.m_blk * BM;
     }
+    // CTA-pair kernel: K is walked in `num_kchunks` equal chunks and kchunk() is called ONCE per (tile, chunk) --
+    // it may wait for the chunk to arrive (`wait`; false for the zero-filled phantom m-block of an odd tail) and
+    // says where the chunk's A rows come from; the per-K-block loop then only adds BK. (The producer thread has
+    // ~270 ns per K-block at full MMA rate: the divisions a per-K-block kblock() needs to find its chunk were
+    // measured at ~150 ns per call with the device trace, i.e. they starved the tensor cores.)
+    __device__ static int num_kchunks(const RankParams& p) { return 1; }
+    __device__ static void kchunk(const RankParams& p, const TileCoord& tc, int ci, bool wait, int& k_base,
+                                  const CUtensorMap*& ta, int& a_k_base, int& a_m0) {
+        k_base = 0;
+        ta = &p.tmap_a;
+        a_k_base = 0;
+        a_m0 = tc.m_blk * BM;
+    }
     // K coordinate of iteration `it` (what kblock would use for B), without any waiting
     __device__ static int kcoord(const RankParams& p, int it) { return it * BK; }
     template <typename OutT>

@@ -140,15 +140,20 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
             uint32_t phase = 0;
             long long tr_flag = 0, tr_empty = 0, tr_max = 0, tr_slow = 0;
             unsigned long long tr_first = 0;
+            const int nch = Policy::num_kchunks(p);
+            const int per = k_blocks / nch;                       // K-blocks per chunk
             for (int t = pair; t < ntiles; t += npairs) {
                 const TileCoord tc = my_tile(t);
                 const bool valid = tc.m_blk < m_blocks;
-                for (int it = 0; it < k_blocks; ++it) {
-                    int k0, a_k0, a_m0;
+                for (int ci = 0; ci < nch; ++ci) {
+                    int k_base, a_k_base, a_m0;
                     const CUtensorMap* ta;
-                    if (valid) {
+                    {
+                        // a phantom m-block of an odd tail has rows out of range: TMA zero-fills them and there is
+                        // nothing to wait for -- but the B half it loads feeds the partner's real rows, so K must
+                        // advance in the policy's order
                         const long long c0 = trace ? clock64() : 0;
-                        Policy::kblock(p, tc, it, k0, ta, a_k0, a_m0);
+                        Policy::kchunk(p, tc, ci, valid, k_base, ta, a_k_base, a_m0);
                         if (trace) {
                             const long long d = clock64() - c0;
                             tr_flag += d;
@@ -158,42 +163,34 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
                                 ++tr_slow;
                             }
                         }
-                    } else {
-                        // phantom m-block of an odd tail: its rows are out of range, TMA zero-fills
-                        // them and there is nothing to wait for -- but the B half it loads feeds the
-                        // partner's real rows, so K must advance in the policy's order
-                        k0 = Policy::kcoord(p, it);
-                        ta = &p.tmap_a;
-                        a_k0 = k0;
-                        a_m0 = tc.m_blk * BM;
                     }
-                    if constexpr (KSCALE != 1) {
-                        k0 *= KSCALE;
-                        a_k0 *= KSCALE;
-                    }
-                    {
-                        const long long c0 = trace ? clock64() : 0;
-                        ptx::mbar_wait(&empty[stage], phase ^ 1, 100 + stage);
-                        if (trace) tr_empty += clock64() - c0;
-                    }
-                    if (leader) ptx::mbar_arrive_expect_tx(&full[stage], 2 * C::STAGE_BYTES);
-                    else ptx::mbar_arrive_cluster(&full[stage], 0);
-                    if constexpr (!A_MN) {
-                        ptx::tma_load_2d_2sm(smem_a(stage), ta, &full[stage], a_k0, a_m0);
-                    } else {
+                    for (int w = 0; w < per; ++w) {
+                        const int k0 = (k_base + w * BK) * KSCALE;
+                        const int a_k0 = (a_k_base + w * BK) * KSCALE;
+                        {
+                            const long long c0 = trace ? clock64() : 0;
+                            ptx::mbar_wait(&empty[stage], phase ^ 1, 100 + stage);
+                            if (trace) tr_empty += clock64() - c0;
+                        }
+                        if (leader) ptx::mbar_arrive_expect_tx(&full[stage], 2 * C::STAGE_BYTES);
+                        else ptx::mbar_arrive_cluster(&full[stage], 0);
+                        if constexpr (!A_MN) {
+                            ptx::tma_load_2d_2sm(smem_a(stage), ta, &full[stage], a_k0, a_m0);
+                        } else {
 #pragma unroll
-                        for (int c = 0; c < BM / 64; ++c)
-                            ptx::tma_load_2d_2sm(smem_a(stage) + c * (BK * 128), ta, &full[stage], a_m0 + c * 64, a_k0);
-                    }
-                    const int n0 = tc.n_blk * BN + (int)cta_rank * C::B_ROWS;
-                    if constexpr (!B_MN) {
-                        ptx::tma_load_2d_2sm(smem_b(stage), &p.tmap_b, &full[stage], k0, n0);
-                    } else {
+                            for (int c = 0; c < BM / 64; ++c)
+                                ptx::tma_load_2d_2sm(smem_a(stage) + c * (BK * 128), ta, &full[stage], a_m0 + c * 64, a_k0);
+                        }
+                        const int n0 = tc.n_blk * BN + (int)cta_rank * C::B_ROWS;
+                        if constexpr (!B_MN) {
+                            ptx::tma_load_2d_2sm(smem_b(stage), &p.tmap_b, &full[stage], k0, n0);
+                        } else {
 #pragma unroll
-                        for (int c = 0; c < C::B_ROWS / 64; ++c)
-                            ptx::tma_load_2d_2sm(smem_b(stage) + c * (BK * 128), &p.tmap_b, &full[stage], n0 + c * 64, k0);
+                            for (int c = 0; c < C::B_ROWS / 64; ++c)
+                                ptx::tma_load_2d_2sm(smem_b(stage) + c * (BK * 128), &p.tmap_b, &full[stage], n0 + c * 64, k0);
+                        }
+                        if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
                     }
-                    if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
                 }
             }
             if (trace) {
