@@ -232,8 +232,15 @@ struct AgKPolicy : PlainPolicy {
         // peer costs an NVLink round trip under load (the device trace: ~13 us per slice, 90 us for a 33 MB
         // shard, whatever the copy size); the previous slice's copies have had a whole slice to complete,
         // so `wait_group 1` returns at once and the round trip overlaps the next load.
-        ptx::tma_store_wait<1>();          // every group but the newest has landed ...
-        const int publish = st.pending;    // ... which is what `pending` describes
+        // (The very first slice is published at once: until it is, no peer can start on its remote chunk anyway.)
+        int publish;
+        if (st.flagged == 0 && st.pending == 0) {
+            ptx::tma_store_wait<0>();
+            publish = done;
+        } else {
+            ptx::tma_store_wait<1>();      // every group but the newest has landed ...
+            publish = st.pending;          // ... which is what `pending` describes
+        }
         st.pending = done;
         if (publish <= st.flagged) return true;
         ptx::fence_proxy_async_all();      // landed copies are ordered before the flag traffic
