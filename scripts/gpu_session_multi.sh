@@ -18,7 +18,7 @@ torchrun_() { P=$((P + 1)); python -m torch.distributed.run --nnodes=1 --nproc-p
 launch_() { python -m collective_communication_mpi_b200.launch -n "$NG" --transport device "$@"; }
 export -f torchrun_ launch_; export NG P
 [ "$NG" -ge 8 ] && export CCMPI_TEST_LARGEST_ONLY=1     # budgeted box: multi-rank tests at the largest group size only
-run tests 1500 python -m pytest tests -x -q -m gpu
+run tests 1500 python -m pytest tests --maxfail=3 -q -m gpu
 run bench_ours 400 bash -c 'torchrun_ bench.py --gpus $NG --steps 20 --warmup 5'
 run bench_nccl 400 bash -c 'torchrun_ bench.py --impl nccl --gpus $NG --steps 20 --warmup 5'
 run sweep 900 bash -c 'launch_ python benchmarks/sweep.py --tight --min-kb 1 --max-mb ${SWEEP_MAX_MB:-256}'
@@ -32,7 +32,7 @@ if [ "$NG" -ge 8 ]; then
     run bench4_ours 400 bash -c 'P=$((P + 11)); CUDA_VISIBLE_DEVICES=0,1,2,3 python -m torch.distributed.run --nnodes=1 --nproc-per-node 4 --master-addr 127.0.0.1 --master-port $P bench.py --gpus 4 --steps 20 --warmup 5'
     run bench4_nccl 400 bash -c 'P=$((P + 12)); CUDA_VISIBLE_DEVICES=0,1,2,3 python -m torch.distributed.run --nnodes=1 --nproc-per-node 4 --master-addr 127.0.0.1 --master-port $P bench.py --impl nccl --gpus 4 --steps 20 --warmup 5'
     # one CPU step of the reference arm at N = 8 (how long the driver's run of that arm will take)
-    run ref8_probe 400 bash -c 'P=$((P + 13)); CCMPI_REF_BUDGET_S=${REF_PROBE_BUDGET_S:-60} python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port $P bench.py --impl reference --gpus 8 --steps 2 --warmup 3'
+    [ -n "$REF_PROBE" ] && run ref8_probe 400 bash -c 'P=$((P + 13)); CCMPI_REF_BUDGET_S=${REF_PROBE_BUDGET_S:-60} python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port $P bench.py --impl reference --gpus 8 --steps 2 --warmup 3'
 fi
 [ -n "$EXTRA" ] && run extra 900 bash -c "$EXTRA"
 cat "$OUT"
