@@ -35,18 +35,25 @@ def run_selfcheck(world_comm, mp_comm, dp_comm, *, tokens: int = 1024, hidden: i
     dy = (torch.randn(tokens, hidden // mp, device=dev, generator=g) * 0.5).bfloat16()
 
     # ---- through the layers (fused kernels) ----
+    # The weight gradients are checked through what the optimizer applied: (w_before - w_after) / lr. That covers
+    # every data-parallel path alike -- including the one whose reduction kernel IS the optimizer step and never
+    # materialises the averaged gradient. The step is large enough (>= 100 bf16 ulps of the weights) for the
+    # stochastic rounding of the new weights to stay below the tolerance.
+    LR = 0.01
+    w_before = [col.weight.detach().float().clone(), row.weight.detach().float().clone()]
+    sink.begin_step(LR, 0)
     h = col(x)
     y = row(h)
     y.backward(dy)
-    sink.finish()
+    sink.apply()
     torch.cuda.synchronize()
     got = {"y": y.detach().float(), "dx": x.grad.float(),
-           "dW_col": sink.view_for(col.weight).float().clone(), "dW_row": sink.view_for(row.weight).float().clone()}
+           "dW_col": (w_before[0] - col.weight.detach().float()) / LR, "dW_row": (w_before[1] - row.weight.detach().float()) / LR}
 
     # ---- oracle: unfused collectives + fp32 matmul ----
     with torch.no_grad():
         f32 = torch.float32
-        wc, wr = col.weight.detach().to(f32), row.weight.detach().to(f32)
+        wc, wr = w_before
         xf = mp_comm.gather_last_axis(x.detach()).to(f32) if mp > 1 else x.detach().to(f32)
         h_ref = (xf @ wc).bfloat16()                                   # the layer hands on a bf16 activation
         y_part = h_ref.to(f32) @ wr

@@ -196,6 +196,10 @@ def _declare_device(lib):
         "ccmpi_reduce_scatter_tight": (i, [P(DevComm), i, i, i, sz, sz, sz, sz, sz, sz, i, vp]),
         "ccmpi_allreduce_twoshot_tight": (i, [P(DevComm), i, i, i, sz, sz, sz, sz, f, i, vp]),
         "ccmpi_gemm_sgd_bf16": (i, [vp, vp, vp, i, i, i, i, i, i, i, i, f, i, vp]),
+        "ccmpi_gemm_mx": (i, [vp, vp, vp, vp, vp, i, i, i, i, i, i, i, i, vp]),
+        "ccmpi_fused_ag_gemm_mx": (i, [P(DevComm), i, sz, i, sz, sz, sz, PV, PV, PV, i, i, i, i, i, i, i, u, u, vp, i, vp]),
+        "ccmpi_fused_gemm_rs_mx": (i, [P(DevComm), i, PV, PV, PV, PV, sz, PV, i, i, i, i, i, i, i, i, u, PV, i64, vp, i, vp]),
+        "ccmpi_quantize_mxfp8": (i, [vp, C.c_longlong, vp, C.c_longlong, vp, i, i, vp]),
         "ccmpi_gemm_sgd_bf16_sr": (i, [vp, vp, vp, i, i, i, i, i, i, i, i, f, i, u, i, vp]),
         "ccmpi_sgd_sr_bf16": (i, [vp, vp, C.c_longlong, f, C.c_ulonglong, u, u, vp]),
         "ccmpi_allreduce_sgd_nvls": (i, [P(DevComm), i, sz, sz, sz, f, C.c_ulonglong, u, u, i, vp]),

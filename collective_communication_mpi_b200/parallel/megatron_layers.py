@@ -24,7 +24,7 @@ from __future__ import annotations
 import torch
 from torch import nn
 
-from .tp_layers import _backend, _init_weight, _weight_grad
+from .tp_layers import _backend, _dw_last, _init_weight, _weight_grad
 
 
 class _ColFn(torch.autograd.Function):
@@ -38,7 +38,7 @@ class _ColFn(torch.autograd.Function):
     def backward(ctx, dy):
         x, weight = ctx.saved_tensors
         layer, dy = ctx.layer, dy.contiguous()
-        fused_sgd = layer.sgd_lr is not None
+        fused_sgd = _dw_last(layer)       # dW's kernel (or the reduction it triggers) rewrites W: dx first
         dw = None if fused_sgd else _weight_grad(layer, x, dy)
         if layer.mp == 1:
             dx = layer._gemm(dy, weight, num_sms=layer.num_sms)

@@ -26,7 +26,7 @@ from torch import nn
 
 from ..ops import fused_seq as FS
 from ..ops import host_ops as H
-from .tp_layers import _backend, _init_weight, _weight_grad
+from .tp_layers import _backend, _dw_last, _init_weight, _weight_grad
 
 
 def _seq_ops():
@@ -46,7 +46,7 @@ class _SeqColumnFn(torch.autograd.Function):
     def backward(ctx, dy):
         (weight,) = ctx.saved_tensors
         layer, dy = ctx.layer, dy.contiguous()
-        fused_sgd = layer.sgd_lr is not None
+        fused_sgd = _dw_last(layer)       # dW's kernel (or the reduction it triggers) rewrites W: dx first
         dw = None if fused_sgd else _weight_grad(layer, ctx.x_full, dy)
         dx = layer.rs(dy, weight, b_kn=False, num_sms=layer.num_sms)
         if fused_sgd:

@@ -105,12 +105,13 @@ extern "C" int ccmpi_fused_ag_ctas(int kind, int M, int N, int nvr, int num_sms)
     CCMPI_REQUIRE(nvr >= 1 && M > 0 && N > 0, "bad arguments");
     const int sms = (num_sms > 0 ? num_sms : ccmpi::device_sm_count());
     int budget = sms / nvr;
-    const bool pairs = use_2cta() || kind == 1;
+    const bool pairs = use_2cta() || kind == 1 || kind == 2;
     if (pairs) budget &= ~1;
-    const int BN = pick_bn(M, N, budget);
+    const int BN = kind == 2 ? 128 : pick_bn(M, N, budget);     // kind 2: block-scaled K-gather (256 x 128 tiles)
     const int m_blocks = (M + BM - 1) / BM;
     const int nb = (N + BN - 1) / BN;
     const int tiles = kind == 1 ? 2 * ((m_blocks / 2) * nb) : (pairs ? 2 * (((m_blocks + 1) / 2) * nb) : m_blocks * nb);
+    CCMPI_REQUIRE(kind >= 0 && kind <= 2, "unknown kernel kind %d", kind);
     return budget < tiles ? budget : tiles;
 }
 

@@ -118,6 +118,8 @@ struct AgKPolicy : PlainPolicy {
         long long item;   // ... bulk path: first piece index of this CTA's next slice
         int pending;      // ... bulk path: m-blocks covered by the slices issued so far (published one slice later)
         bool local_started, local_done;   // ... bulk path: pass 1 (copy into this rank's own x_full)
+        long long sf_item;                // ... bulk path, block-scaled operands: next scale run of this CTA
+        bool sf_done;
         int flagged;      // m-blocks [0, flagged) already signalled by this CTA
         int m_blocks;
         uint32_t stg;     // this lane's staging row in shared memory (0: register path)
@@ -129,6 +131,8 @@ struct AgKPolicy : PlainPolicy {
         st.item = (long long)cta * 4;
         st.pending = 0;
         st.local_started = st.local_done = false;
+        st.sf_item = (long long)cta * 4;
+        st.sf_done = false;
         st.flagged = 0;
         st.m_blocks = p.comm.size == 1 ? 0 : (p.M + BM - 1) / BM;
         st.stg = stg;
@@ -166,7 +170,44 @@ struct AgKPolicy : PlainPolicy {
         // backward dW GEMM -- so it must not share the copy engine's time with what the peers' tensor
         // cores are starved for.
         if (st.m_blocks == 0 || st.local_done) return false;
+        const int lane_ = epi_tid & 31, w_ = epi_tid >> 5;
+        if (p.sf_run_bytes > 0 && !st.sf_done) {
+            // Block-scaled operands: this rank's scale chunks travel first -- one run of sf_run_bytes per m-block,
+            // into every peer's gathered scale array at this rank's position in the K order. They are issued (and,
+            // being earlier bulk groups, completed) before any payload piece of this CTA is published.
+            int segs = 1;
+            while (p.sf_run_bytes / segs > PUSH_PIECE) segs <<= 1;
+            const int seg_bytes = p.sf_run_bytes / segs;
+            const long long total = (long long)st.m_blocks * segs;
+            const long long i = st.sf_item + w_;
+            const bool ok = i < total;
+            const uint32_t wbuf = st.stg - (uint32_t)lane_ * STG_ROW_STRIDE;
+            if (lane_ == 0) ptx::tma_store_wait_read<0>();
+            ptx::mbar_arrive_expect_tx(st.wbar, (lane_ == 0 && ok) ? (uint32_t)seg_bytes : 0u);
+            const long long mb = ok ? i / segs : 0;
+            const int seg = ok ? (int)(i - mb * segs) : 0;
+            if (lane_ == 0 && ok) {
+                const uint8_t* src = c.heap[c.rank] + p.off_sf_local + (size_t)mb * p.sf_run_bytes + (size_t)seg * seg_bytes;
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(wbuf),
+                             "l"(src), "r"(seg_bytes), "r"(ptx::smem_u32(st.wbar))
+                             : "memory");
+            }
+            ptx::mbar_wait(st.wbar, st.phase, 801);
+            st.phase ^= 1;
+            if (lane_ == 0 && ok) {
+                const size_t d = p.off_sf_full + ((size_t)mb * c.size + c.rank) * p.sf_run_bytes + (size_t)seg * seg_bytes;
+                for (int s2 = 1; s2 < c.size; ++s2) ptx::bulk_s2g(c.heap[(c.rank + s2) % c.size] + d, wbuf, seg_bytes);
+            }
+            ptx::tma_store_commit();
+            st.sf_item += (long long)nctas * 4;
+            if (st.sf_item >= total) st.sf_done = true;
+            return true;
+        }
         const bool local_pass = st.flagged >= st.m_blocks;
+        if (local_pass && (p.aux1 & 8)) {     // the caller does not need the gathered operand afterwards
+            st.local_done = true;
+            return false;
+        }
         if (local_pass && !st.local_started) {
             st.local_started = true;
             st.item = (long long)cta * 4;
@@ -183,7 +224,9 @@ struct AgKPolicy : PlainPolicy {
         const long long total = ((long long)(p.M + rows_per - 1) / rows_per) * segs;
         const long long stride = (long long)nctas * 4;            // one piece per epilogue warp and slice
         const uint8_t* x = c.heap[c.rank] + p.off0;
-        const size_t src_ld = (size_t)p.aux0 * 2, dst_ld = (size_t)p.K * 2;
+        // (row strides in bytes; the gathered row is n shards wide -- not written as K * 2 because fp8 operands
+        // count K in elements while the policy's chunk / ldx are in 2-byte units)
+        const size_t src_ld = (size_t)p.aux0 * 2, dst_ld = (size_t)row_bytes * c.size;
         const size_t col0 = (size_t)c.rank * row_bytes;
         const long long i = st.item + w;
         const bool ok = i < total;

@@ -21,6 +21,7 @@
 //   tmem_empty[a]  lives in the leader; 8 arrivals (4 epilogue warps of each CTA)
 #pragma once
 #include "gemm_kernel.cuh"
+#include "mx_desc.cuh"
 
 namespace gemm {
 
@@ -30,15 +31,21 @@ namespace gemm {
 // which makes the lanes' 16-byte shared stores conflict-free.
 // (STG_CHUNK_BYTES / STG_ROW_STRIDE / STG_BYTES live in gemm_tcgen05.cuh: the policies use them too)
 
-template <int BN, bool STAGED = false>
+template <int BN, bool STAGED = false, bool MX = false>
 struct Cfg2 {
     static constexpr int A_BYTES = BM * BK * 2;          // this CTA's 128 rows of A
     static constexpr int B_ROWS = BN / 2;                // this CTA's half of the B tile
     static constexpr int B_BYTES = B_ROWS * BK * 2;
-    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    // block-scaled (MXFP8) operands: every stage also carries one 512-byte chunk of scales for this CTA's 128 rows
+    // of A and one for the tile's 128 columns of B (see gemm_mxfp8.cu / DESIGN.md section 6)
+    static constexpr int SF_BYTES = MX ? 512 : 0;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES + 2 * SF_BYTES;
+    static constexpr int SF_COL0 = 2 * BN;               // first scale column of tensor memory (MX)
+    static_assert(!MX || BN == 128, "block-scaled tiles are 256 x 128 per CTA pair");
+    static_assert(STAGE_BYTES % 1024 == 0, "operand tiles must stay 1024-byte aligned");
     static constexpr int RING_BUDGET = 200 * 1024 - (STAGED ? STG_BYTES : 0);
     static constexpr int STAGES = RING_BUDGET / STAGE_BYTES > 8 ? 8 : RING_BUDGET / STAGE_BYTES;
-    static constexpr int TMEM_COLS = (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
+    static constexpr int TMEM_COLS = MX ? 512 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256 + (STAGED ? STG_BYTES : 0);
     static_assert(BN % 128 == 0 && BN <= 256, "BN must be 128 or 256 for CTA pairs");
     static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget exceeded");
@@ -54,12 +61,31 @@ __device__ __forceinline__ bool own_tile(const RankParams& p, const TileCoord& t
     else return false;
 }
 
-template <int BN, bool A_MN, bool B_MN, typename OutT, typename Policy, int EB = 2>
+// MX = block-scaled e4m3 (OCP MXFP8, one UE8M0 scale per 1 x 32 block; tcgen05.mma kind::mxf8f6f4.block_scale):
+// EB = 1 plus two scale chunks per stage, copied shared -> tensor memory (tcgen05.cp) by the MMA thread right
+// before the four MMAs of a K-block. Everything a Policy does -- gathers, scatters, epilogues -- is unchanged.
+__device__ __forceinline__ void utccp_32x128b_2sm(uint32_t taddr, uint64_t sdesc) {
+    asm volatile("tcgen05.cp.cta_group::2.32x128b.warpx4 [%0], %1;" ::"r"(taddr), "l"(sdesc) : "memory");
+}
+__device__ __forceinline__ void umma_mx_ss_2sm(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                               uint32_t tmem_sfa, uint32_t tmem_sfb, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::mxf8f6f4.block_scale [%0], %1, %2, %3, [%5], [%6], p;\n\t"
+        "}\n" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(tmem_sfa), "r"(tmem_sfb)
+        : "memory");
+}
+
+template <int BN, bool A_MN, bool B_MN, typename OutT, typename Policy, int EB = 2, bool MX = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 gemm_kernel_2cta(const __grid_constant__ Launch lp) {
     static_assert(EB == 2 || (EB == 1 && !A_MN && !B_MN), "fp8 operands must be K-major");
+    static_assert(!MX || EB == 1, "block scaling is an fp8 mode");
     constexpr int KSCALE = 2 / EB;   // policies count K in bf16-sized elements (BK = 64 per block)
-    using C = Cfg2<BN, Policy::kNeedsStaging>;
+    using C = Cfg2<BN, Policy::kNeedsStaging, MX>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint64_t* bars = reinterpret_cast<uint64_t*>(base + C::STAGES * C::STAGE_BYTES);
@@ -71,6 +97,8 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
     uint8_t* stg_base = reinterpret_cast<uint8_t*>(bars) + 256;
     auto smem_a = [&](int s) { return base + s * C::STAGE_BYTES; };
     auto smem_b = [&](int s) { return base + s * C::STAGE_BYTES + C::A_BYTES; };
+    auto smem_sfa = [&](int s) { return base + s * C::STAGE_BYTES + C::A_BYTES + C::B_BYTES; };
+    auto smem_sfb = [&](int s) { return base + s * C::STAGE_BYTES + C::A_BYTES + C::B_BYTES + C::SF_BYTES; };
 
     // clusters are consecutive block pairs; emulated ranks interleave at pair granularity
     const int nvr = lp.nvr;
@@ -116,6 +144,11 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
         ptx::prefetch_tmap(&p.tmap_a);
         ptx::prefetch_tmap(&p.tmap_a2);
         ptx::prefetch_tmap(&p.tmap_b);
+        if constexpr (MX) {
+            ptx::prefetch_tmap(&p.tmap_sfa);
+            ptx::prefetch_tmap(&p.tmap_sfa2);
+            ptx::prefetch_tmap(&p.tmap_sfb);
+        }
 #pragma unroll
         for (int s = 0; s < C::STAGES; ++s) {
             ptx::mbar_init(&full[s], 2);
@@ -189,6 +222,16 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
                             for (int c = 0; c < C::B_ROWS / 64; ++c)
                                 ptx::tma_load_2d_2sm(smem_b(stage) + c * (BK * 128), &p.tmap_b, &full[stage], n0 + c * 64, k0);
                         }
+                        if constexpr (MX) {
+                            // scale chunks: row `chunk` of a [chunks][128 x uint32] matrix, K-fastest chunk order. A's
+                            // come from the array that belongs to the source of its rows (gathered staging or this
+                            // rank's own shard), B's from the weight's. A phantom m-block reads the row past the end
+                            // (TMA zero-fills it).
+                            const bool local = ta == &p.tmap_a2;
+                            const int sfa_row = (a_m0 / BM) * (local ? p.sf_a2_kblocks : k_blocks) + a_k_base / BK + w;
+                            ptx::tma_load_2d_2sm(smem_sfa(stage), local ? &p.tmap_sfa2 : &p.tmap_sfa, &full[stage], 0, sfa_row);
+                            ptx::tma_load_2d_2sm(smem_sfb(stage), &p.tmap_sfb, &full[stage], 0, tc.n_blk * k_blocks + k_base / BK + w);
+                        }
                         if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
                     }
                 }
@@ -208,7 +251,7 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
             constexpr uint32_t idesc = EB == 2 ? ptx::umma_idesc(1, 1, A_MN, B_MN, 2 * BM, BN)     // bf16 x bf16
                                                : ptx::umma_idesc(0, 0, false, false, 2 * BM, BN);  // e4m3 x e4m3
             int stage = 0;
-            uint32_t phase = 0;
+            uint32_t phase = 0, kb = 0;
             int local = 0;
             long long tr_full = 0, tr_acc = 0;
             for (int t = pair; t < ntiles; t += npairs, ++local) {
@@ -221,7 +264,7 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
                 }
                 ptx::tc_fence_after();
                 const uint32_t tmem_d = tmem_base + acc * BN;
-                for (int it = 0; it < k_blocks; ++it) {
+                for (int it = 0; it < k_blocks; ++it, ++kb) {
                     {
                         const long long c0 = trace ? clock64() : 0;
                         ptx::mbar_wait(&full[stage], phase, 300 + stage);
@@ -230,6 +273,21 @@ gemm_kernel_2cta(const __grid_constant__ Launch lp) {
                     ptx::tc_fence_after();
                     const uint32_t a_addr = ptx::smem_u32(smem_a(stage));
                     const uint32_t b_addr = ptx::smem_u32(smem_b(stage));
+                    if constexpr (MX) {
+                        // scale columns are double-buffered by K-block parity; tcgen05.cp and tcgen05.mma execute in
+                        // issue order, so the copies need no barrier of their own
+                        const uint32_t sf = tmem_base + C::SF_COL0 + (kb & 1) * 8;     // 4 columns SFA, then 4 columns SFB
+                        utccp_32x128b_2sm(sf, mx::smem_desc_noswizzle(ptx::smem_u32(smem_sfa(stage)), mx::SF_CHUNK_LBO, mx::SF_CHUNK_SBO));
+                        utccp_32x128b_2sm(sf + 4, mx::smem_desc_noswizzle(ptx::smem_u32(smem_sfb(stage)), mx::SF_CHUNK_LBO, mx::SF_CHUNK_SBO));
+#pragma unroll
+                        for (uint32_t ks = 0; ks < 4; ++ks)
+                            umma_mx_ss_2sm(tmem_d, operand_desc<false>(a_addr, ks), operand_desc<false>(b_addr, ks),
+                                           mx::idesc_mx(2 * BM, BN, ks), sf | (ks << 30), (sf + 4) | (ks << 30),
+                                           (it | (int)ks) != 0 ? 1u : 0u);
+                        ptx::umma_commit_2sm(&empty[stage], 0b11);
+                        if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                        continue;
+                    }
 #pragma unroll
                     for (int ks = 0; ks < BK / UMMA_K; ++ks) {
                         if constexpr (EB == 2)

@@ -67,6 +67,11 @@ struct alignas(64) RankParams {
     const void* epi_in;   // second epilogue operand  [M][epi_ld] bf16: u for EPI_MUL_DGELU, the residual for EPI_ADD
     void* epi_out2;       // second output            [M][epi_ld] bf16: gelu(C) for EPI_GELU_DUAL
     long long epi_ld;
+    // ---- block-scaled (MXFP8) operands: scale chunks of A (gathered staging / this rank's own shard) and of B ----
+    CUtensorMap tmap_sfa, tmap_sfa2, tmap_sfb;
+    int sf_a2_kblocks;    // K-blocks per 128-row chunk row of the tmap_sfa2 array
+    int sf_run_bytes;     // all-gather: bytes of this rank's scale run per m-block (0: no scales to push)
+    unsigned long long off_sf_local, off_sf_full;   // symmetric offsets of the local / gathered scale arrays
     // ---- per-CTA device trace (nullptr: off): TRACE_WORDS x uint64 per CTA, see TraceSlot ----
     unsigned long long* trace;
 };

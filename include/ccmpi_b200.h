@@ -320,6 +320,25 @@ int ccmpi_allreduce_sgd_nvls(const ccmpi_dev_comm* comms, int nvr, size_t grad_o
                              float lr_eff, unsigned long long base_index, unsigned step, unsigned seed, int max_blocks,
                              void* stream);
 
+/* Block-scaled fp8 (OCP MXFP8: e4m3 values, one UE8M0 scale per 1 x 32 block of K) on the generic CTA-pair
+ * kernel, plain and fused with the collectives (csrc/fused_gemm_mx.cu). Operands K-major: A [M][K], B [N][K];
+ * scale arrays in the chunked layout the tensor cores read (512-byte chunks of 128 rows x 4 scales, K-fastest;
+ * ccmpi_quantize_mxfp8 writes it). BASELINE config 3's fp8 forward products of func_impl.py:76-91 / :150-187.
+ *   ag_gemm_mx: xq_off / sfl_off = this rank's [M][K/n] shard and its scales, xfull_off / sffull_off = gathered
+ *               staging; the kernel pushes payload AND scales (half the bytes of the bf16 gather).
+ *   gemm_rs_mx: fp8 operands, partial tiles and result in out_dtype; optional bf16 residual as in gemm_rs_ex. */
+int ccmpi_gemm_mx(const void* A, const void* sfa, const void* B, const void* sfb, void* C, int M, int N, int K, int lda,
+                  int ldb, int ldc, int out_dtype, int num_sms, void* stream);
+int ccmpi_fused_ag_gemm_mx(const ccmpi_dev_comm* comms, int nvr, size_t xq_off, int ldx, size_t sfl_off, size_t xfull_off,
+                           size_t sffull_off, const void* const* B, const void* const* sfb, void* const* C, int M, int N,
+                           int K, int ldb, int ldc, int out_dtype, int flag_base, unsigned epoch, unsigned flag_target,
+                           void* trace, int num_sms, void* stream);
+int ccmpi_fused_gemm_rs_mx(const ccmpi_dev_comm* comms, int nvr, const void* const* A, const void* const* sfa,
+                           const void* const* B, const void* const* sfb, size_t slots_off, void* const* C, int M, int N,
+                           int K, int lda, int ldb, int ldc, int out_dtype, int flag_base, unsigned epoch,
+                           const void* const* residual, long long res_ld, void* trace, int num_sms, void* stream);
+int ccmpi_quantize_mxfp8(const void* x, long long ldx, void* q, long long ldq, void* sf, int R, int K, void* stream);
+
 /* EXPERIMENTAL (compiled, not yet run on hardware in round 1): fp8 e4m3 GEMM on the CTA-pair
  * kernel, C[M][N] = scale * A[M][K] * B[N][K]^T, both operands K-major (tcgen05.mma.kind::f8f6f4).
  * First step towards the block-scaled fp8 FC layers of BASELINE.md config 3; the reference has no
