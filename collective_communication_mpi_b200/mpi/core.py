@@ -537,7 +537,7 @@ class Comm:
         b = _Buf(buf, False)
         w = self._world
         if b.cuda and P2P.enabled() and w.device_available():
-            # opt-in NVLink route: the payload waits in the symmetric heap, a descriptor travels
+            # NVLink route: the payload waits in the symmetric heap, a descriptor travels
             host = P2P.stage_for_send(w, self._peer(dest), b.flat).view(np.uint8)
         else:
             host = _host_bytes(b)  # CUDA payloads are staged to the host for the mailbox path
@@ -560,6 +560,13 @@ class Comm:
         elif b.cuda:
             host = np.empty(b.nbytes, dtype=np.uint8)
             done = lambda: _from_host_bytes(b, host)  # noqa: E731
+        elif P2P.enabled() and w.device_available() and w.heap is not None:
+            # host buffer on the device plane: the sender may be a CUDA tensor on the NVLink route
+            dst_bytes = b.flat.view(np.uint8) if b.flat.dtype != np.uint8 else b.flat
+            host = np.empty(max(b.nbytes, P2P.DESC_BYTES), dtype=np.uint8)
+            host[:P2P.DESC_BYTES] = 0
+            src_world = self._peer(source)
+            done = lambda: P2P.complete_receive_host(w, src_world, host, dst_bytes)  # noqa: E731
         else:
             host, done = b.flat.view(np.uint8) if b.flat.dtype != np.uint8 else b.flat, None
         rid = w._hostlib.ccmpi_host_irecv(w.host, self._peer(source), self._cid, int(tag), host.ctypes.data, host.nbytes)

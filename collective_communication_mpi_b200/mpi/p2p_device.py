@@ -1,4 +1,5 @@
-"""Point-to-point transfers of CUDA tensors over NVLink (opt-in: ``CCMPI_P2P=device``).
+"""Point-to-point transfers of CUDA tensors over NVLink (the default on the device plane; ``CCMPI_P2P=host`` stages
+them through the host rings instead).
 
 The reference moves everything with ``Send`` / ``Recv`` / ``Isend`` / ``Irecv`` / ``Sendrecv`` on
 host arrays (mpi_wrapper/comm.py:86,99,104-105,140,147,192). The default path here keeps that
@@ -39,7 +40,7 @@ DESC_BYTES = DESC_WORDS * 8
 
 
 def enabled() -> bool:
-    return os.environ.get("CCMPI_P2P", "host") == "device"
+    return os.environ.get("CCMPI_P2P", "device") == "device"
 
 
 def make_descriptor(off: int, nbytes: int, seq: int) -> np.ndarray:
@@ -144,6 +145,25 @@ def complete_receive(world, src_world: int, raw: np.ndarray, flat_cuda) -> None:
     if n:
         heap = world.ensure_heap()
         flat_cuda.view(torch.uint8)[:n].copy_(heap.view(off, (n,), torch.uint8, rank=src_world), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+    rc = world._hostlib.ccmpi_host_ack_post(world.host, src_world)
+    if rc < 0:
+        raise RuntimeError("ccmpi_host_ack_post failed")
+
+
+def complete_receive_host(world, src_world: int, raw: np.ndarray, dst_bytes: np.ndarray) -> None:
+    """The same for a HOST receive buffer (``dst_bytes``: its uint8 view): MPI lets a CUDA sender meet a NumPy
+    receiver, so a host receive on the device plane must also understand a descriptor."""
+    nbytes = dst_bytes.nbytes
+    d = parse_descriptor(raw, nbytes)
+    if d is None:
+        np.copyto(dst_bytes, raw[:nbytes])
+        return
+    import torch
+    off, n, _ = d
+    if n:
+        heap = world.ensure_heap()
+        torch.from_numpy(dst_bytes)[:n].copy_(heap.view(off, (n,), torch.uint8, rank=src_world))
         torch.cuda.current_stream().synchronize()
     rc = world._hostlib.ccmpi_host_ack_post(world.host, src_world)
     if rc < 0:

@@ -6,7 +6,7 @@
 mkdir -p gpurun_out
 NG=$(nvidia-smi -L | wc -l)
 export CCMPI_DEVICE_TIMEOUT_S=${CCMPI_DEVICE_TIMEOUT_S:-20}
-export CCMPI_TEST_UNVERIFIED=1
+
 OUT=gpurun_out/session_${NG}gpu.txt
 : > "$OUT"
 P=29700

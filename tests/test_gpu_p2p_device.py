@@ -1,14 +1,10 @@
-"""NVLink route of Send/Recv for CUDA tensors (CCMPI_P2P=device). Needs >= 2 GPUs; written after
-round 1's GPU budget was spent, so opt-in with CCMPI_TEST_UNVERIFIED=1. The control path is tested
-without GPUs in tests/test_p2p_device_control.py."""
-import os
-
+"""NVLink route of Send/Recv for CUDA tensors (the default on the device plane). Needs >= 2 GPUs. The control
+path is tested without GPUs in tests/test_p2p_device_control.py."""
 import pytest
 
 from conftest import gpu_count, run_ranks
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("CCMPI_TEST_UNVERIFIED") != "1", reason="path not yet verified on hardware")]
+pytestmark = pytest.mark.gpu
 
 
 def test_cuda_tensors_travel_over_the_peer_mapping():

@@ -147,8 +147,8 @@ def check_device_put_signal():
 
 
 check_buffer_collectives(world, list(range(n)))
-if CUDA and n >= 2 and os.environ.get("CCMPI_TEST_UNVERIFIED") == "1":
-    check_device_put_signal()       # not yet run on a multi-GPU box: opt-in like the other unverified checks
+if CUDA and n >= 2:
+    check_device_put_signal()
 if n >= 4:
     # sub-communicators: interleaved groups (the dp_comm pattern: stride = number of groups)
     sub = world.Split(color=rank % 2, key=rank)

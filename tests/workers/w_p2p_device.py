@@ -11,7 +11,7 @@ from collective_communication_mpi_b200.mpi import p2p_device as P
 w = MPI.COMM_WORLD
 r, n = w.Get_rank(), w.Get_size()
 torch.cuda.set_device(r)
-assert P.enabled(), "run with CCMPI_P2P=device"
+assert P.enabled(), "the NVLink route is the default (CCMPI_P2P=host turns it off)"
 nxt, prv = (r + 1) % n, (r - 1) % n
 
 for it, count in enumerate([1, 3, 1000, 1 << 16, (1 << 24) + 5]):
@@ -47,5 +47,15 @@ elif r == 1:
     w.Recv(got, source=0, tag=77)
     assert torch.equal(got.cpu(), torch.arange(100, dtype=torch.float32))
 w.Barrier()
+# ... and a NumPy receiver accepts a CUDA sender's message (descriptor through the ring, payload pulled to the host)
+if r == 0 and n > 1:
+    w.Send(torch.arange(5000, device="cuda", dtype=torch.int64) * 3, dest=1, tag=78)
+elif r == 1:
+    host = np.empty(5000, dtype=np.int64)
+    w.Recv(host, source=0, tag=78)
+    assert np.array_equal(host, np.arange(5000, dtype=np.int64) * 3)
+w.Barrier()
+led.reclaim()
+assert led.outstanding == 0, led.outstanding
 if r == 0:
     print(f"P2P DEVICE OK ranks={n}")
