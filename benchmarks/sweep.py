@@ -108,7 +108,7 @@ def main():
             ms = timeit(lambda: CO.allgather(dev.comms, so, do, 1, per, 0, 0, use_mc=False, max_blocks=mb), iters, warm, comm)
             rec("allgather", "push_p2p", per * n, ms, f_x)
             if dev.has_mc:
-                ms = timeit(lambda: CO.allgather(dev.comms, so, do, 1, per, 0, 0, use_mc=True, max_blocks=mb), iters, warm, comm)
+                ms = timeit(lambda: CO.allgather(dev.comms, so, do, 1, per, 0, 0, use_mc=2, max_blocks=mb), iters, warm, comm)
                 rec("allgather", "push_mc", per * n, ms, f_x)
             ms = timeit(lambda: CO.reduce_scatter(dev.comms, cc, N.SUM, so, do, 1, per // es, 0, 0, use_mc=False, max_blocks=mb, tight=False), iters, warm, comm)
             rec("reduce_scatter", "pull_p2p", per * n, ms, f_x)
@@ -116,8 +116,12 @@ def main():
                 ms = timeit(lambda: CO.reduce_scatter(dev.comms, cc, N.SUM, so, do, 1, per // es, 0, 0, use_mc=False, max_blocks=mb, tight=True), iters, warm, comm)
                 rec("reduce_scatter", "pull_p2p_tight", per * n, ms, f_x)
             if dev.has_mc:
-                ms = timeit(lambda: CO.reduce_scatter(dev.comms, cc, N.SUM, so, do, 1, per // es, 0, 0, use_mc=True, max_blocks=mb), iters, warm, comm)
+                ms = timeit(lambda: CO.reduce_scatter(dev.comms, cc, N.SUM, so, do, 1, per // es, 0, 0, use_mc=3, max_blocks=mb), iters, warm, comm)
                 rec("reduce_scatter", "nvls", per * n, ms, f_x)
+            ms = timeit(lambda: CO.allgather(dev.comms, so, do, 1, per, 0, 0, use_mc=True, max_blocks=mb), iters, warm, comm)
+            rec("allgather", "auto", per * n, ms, f_x)
+            ms = timeit(lambda: CO.reduce_scatter(dev.comms, cc, N.SUM, so, do, 1, per // es, 0, 0, use_mc=True, max_blocks=mb), iters, warm, comm)
+            rec("reduce_scatter", "auto", per * n, ms, f_x)
             ms = timeit(lambda: CO.alltoall(dev.comms, so, do, per, max_blocks=mb), iters, warm, comm)
             rec("alltoall", "push", per * n, ms, f_x)
         if use_nccl:

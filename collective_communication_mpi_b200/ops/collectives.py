@@ -93,6 +93,7 @@ def allreduce_sgd(comms, grad_off: int, w_off: int, count: int, lr_eff: float, *
 def allgather(comms, src_off: int, dst_off: int, rows: int, row_bytes: int, src_row_stride: int,
               dst_row_stride: int, *, use_mc: bool = True, max_blocks: int = 0, stream=None):
     a, n = _arr(comms)
+    # use_mc: False = per-peer stores, True = library's choice (multicast below ~8 MB), 2 = multicast at any size
     N.check(N.device_lib().ccmpi_allgather(a, n, src_off, dst_off, rows, row_bytes, src_row_stride,
                                            dst_row_stride, int(use_mc), max_blocks, _sp(stream)), "ccmpi_allgather")
     N.count_launch()
@@ -109,7 +110,7 @@ def reduce_scatter(comms, dtype: int, op: int, src_off: int, dst_off: int, rows:
                 "ccmpi_reduce_scatter_tight")
         N.count_launch()
         return
-    mode = 2 if tight is False and not use_mc else int(use_mc)
+    mode = 2 if tight is False and not use_mc else int(use_mc)     # use_mc: False / True (library's choice) / 3 (NVLS at any size)
     N.check(N.device_lib().ccmpi_reduce_scatter(a, n, dtype, op, src_off, dst_off, rows, row_elems,
                                                 src_row_stride, dst_row_stride, mode, max_blocks,
                                                 _sp(stream)), "ccmpi_reduce_scatter")

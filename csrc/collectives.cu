@@ -640,7 +640,9 @@ extern "C" int ccmpi_allgather(const ccmpi_dev_comm* comms, int nvr, size_t src_
     cudaStream_t st = (cudaStream_t)stream;
     const int W = max_align(src_off | dst_off | row_bytes | (rows > 1 ? (src_row_stride | dst_row_stride) : 0));
     const int blocks = clamp_blocks(rows * (row_bytes / W), max_blocks);
-    const bool mc = use_mc && lp.c[0].mc_heap != nullptr && W == 16;
+    // multimem.st (one copy leaves the GPU, the switch replicates it) wins up to a few MB; above that the
+    // per-peer stores are faster (profiles/r2_sweep_4gpu.jsonl: 569 vs 466 GB/s at 64 MB)
+    const bool mc = use_mc && lp.c[0].mc_heap != nullptr && W == 16 && (use_mc == 2 || rows * row_bytes * lp.c[0].size < (8u << 20));
     switch (W) {
         case 16:
             if (mc) return launch(allgather_kernel<16, true>, nvr, blocks, st, lp, src_off, dst_off, rows, row_bytes, src_row_stride, dst_row_stride);
@@ -689,16 +691,22 @@ extern "C" int ccmpi_reduce_scatter(const ccmpi_dev_comm* comms, int nvr, int dt
     if (rc) return rc;
     if (rows == 0 || row_elems == 0) return CCMPI_OK;
     cudaStream_t st = (cudaStream_t)stream;
-    // use_mc: 0 = peer loads, 1 = NVLS when the group has a multicast mapping, 2 = peer loads with the kernel
+    // use_mc: 0 = peer loads, 1 = the library's choice (NVLS for small messages when the group has a multicast mapping),
+    // 3 = NVLS at any size, 2 = peer loads with the kernel
     // sized for any group (benchmarks). 0 -- and 1 without NVLS or between two GPUs, where peer loads measured
     // faster -- take the group-size-specialised kernel when dtype / alignment allow (same bits, 1.2-1.7x).
-    if (use_mc == 0 || (use_mc == 1 && (lp.c[0].mc_heap == nullptr || lp.c[0].size <= 2))) {
+    // NVLS (multimem.ld_reduce) wins while the message is latency-bound; from ~8 MB up the peer-load kernel is
+    // faster at every group size measured (profiles/r2_sweep_{2,4}gpu.jsonl: 537 vs 455 GB/s at 64 MB on 4 GPUs)
+    const size_t total_bytes = rows * row_elems * (dtype == CCMPI_F64 || dtype == CCMPI_I64 ? 8 : dtype == CCMPI_F32 || dtype == CCMPI_I32 ? 4 : 2) *
+                               (size_t)lp.c[0].size;
+    if (use_mc == 0 || (use_mc == 1 && (lp.c[0].mc_heap == nullptr || lp.c[0].size <= 2 || total_bytes >= (8u << 20)))) {
         rc = ccmpi_reduce_scatter_tight(comms, nvr, dtype, op, src_off, dst_off, rows, row_elems, src_row_stride,
                                         dst_row_stride, max_blocks, stream);
         if (rc != CCMPI_ERR_UNSUPPORTED) return rc;
         use_mc = 0;
     }
     if (use_mc == 2) use_mc = 0;
+    if (use_mc == 3) use_mc = 1;      // NVLS at any size (benchmarks)
     switch (dtype) {
         case CCMPI_F32: return rs_op<float>(lp, nvr, op, src_off, dst_off, rows, row_elems, src_row_stride, dst_row_stride, use_mc, max_blocks, st);
         case CCMPI_BF16: return rs_op<__nv_bfloat16>(lp, nvr, op, src_off, dst_off, rows, row_elems, src_row_stride, dst_row_stride, use_mc, max_blocks, st);
