@@ -23,7 +23,8 @@ model-parallel backward (mp > 1 and dp > 1): the reduction gets at most ``max_bl
 launched as 2-CTA clusters so that it takes whole SM pairs (the GEMM's CTA pairs need both SMs of a
 pair), and the layers' backward fused kernels are sized to the remaining SMs. Together they always
 fit, whatever order the hardware starts them in. The last bucket has nothing to hide behind: it is
-launched on the main stream, after the kernels before it, and may use every SM.
+launched on the main stream, after the kernels before it AND after the buckets still reducing on the side
+stream (collectives of one communicator share its barrier words and must not overlap), and may use every SM.
 
 Optimizer. With NVLS the reduction IS the optimizer step (``fused_update``): the weights live in a
 second flat symmetric buffer with the gradients' layout, and the kernel of a bucket sums its slice of
@@ -159,6 +160,12 @@ class GradSink:
             ev = torch.cuda.Event()
             ev.record(cur)
             st.wait_event(ev)
+        elif self.overlap:
+            # Two collectives on ONE communicator must never run at the same time: they share the communicator's
+            # per-block barrier words (block b of every rank pairs up through pad[b]), so a bucket still reducing on
+            # the side stream and this one would corrupt each other's epochs and hang (seen at dp = 4 after ~170
+            # barriers). The last bucket therefore also waits for the side stream.
+            cur.wait_stream(self.stream)
         blocks = 0 if not side else (self.max_blocks | N.BLOCKS_PAIRED if self.partitioned else self.max_blocks)
         if self.fused_update:
             CO.allreduce_sgd(self.dev.comms, off, self.wflat_off + b["lo"] * 2, count, self.lr / self.dp, base_index=b["lo"],
