@@ -29,6 +29,7 @@ import torch
 from .. import _native as N
 from ..utils import ktrace as KT
 from .collectives import _arr, _sp
+from .flags import FlagAllocator
 from .gemm import EPI_GELU_DUAL, epilogue_args
 
 _OUT = {torch.bfloat16: N.BF16, torch.float32: N.F32}
@@ -129,18 +130,97 @@ class FusedContext:
         self.heap = self.dev.heap
         self.n = comm.Get_size()
         self.rank = comm.Get_rank()
-        self._next_word = 0
+        self.flags = FlagAllocator(N.PAD_USER_WORDS)
 
     def new_slot(self, words: int) -> int:
-        """Reserve ``words`` flag words of this communicator's signal pad (never released: flag
-        regions of different fused ops must not overlap because each carries its own epochs)."""
-        base = self._next_word
-        words = (words + 15) // 16 * 16
-        if base + words > N.PAD_USER_WORDS:
-            raise RuntimeError(f"signal pad exhausted: {base} + {words} flag words > {N.PAD_USER_WORDS}; "
-                               "share fused-op contexts between layers of the same shape or use fewer tokens per call")
-        self._next_word += words
-        return base
+        """Reserve ``words`` flag words of this communicator's signal pad. Flag regions of different
+        live fused ops never overlap (each carries its own epochs); a region comes back through
+        ``release_slot`` when its op is closed."""
+        return self.flags.alloc(words)
+
+    def release_slot(self, base: int) -> None:
+        """Give a flag region back. COLLECTIVE over the communicator: every member closes the same
+        op at the same point of its program.
+
+        Flags are monotone ("wait until the word reaches this launch's target"), and what a region
+        holds after its last launch depends on the op and its shape, so a new owner cannot simply
+        carry on from there: the region is zeroed instead. Order: (1) this rank's launches that use
+        the region have finished; (2) so have everybody's, hence no peer store into our words is
+        still in flight; (3) zero our words; (4) nobody launches the next owner before every member
+        has zeroed (a peer's first store must not be wiped by our late memset)."""
+        words = self.flags.size_of(base)
+        torch.cuda.synchronize()
+        self.comm.Barrier()
+        pad_off = self.dev._cid * N.PAD_BYTES + (N.PAD_USER + base) * 4
+        self.heap.view(pad_off, (words,), torch.int32).zero_()
+        torch.cuda.synchronize()
+        self.comm.Barrier()
+        self.flags.free(base)
+
+
+class FusedOp:
+    """Life cycle shared by the fused-op objects: symmetric buffers and a flag region are taken
+    in ``__init__`` and given back by ``close()`` (collective; also a context manager). An op
+    that is never closed keeps them for the life of the communicator, as before."""
+
+    ctx: "FusedContext"
+    flag_base: Optional[int] = None
+    _closed = False
+
+    def _heap_offsets(self):
+        """Offsets this op took from the symmetric heap: attributes named ``*_off`` and the
+        ``[(offset, tensor), ...]`` lists ``heap.empty`` produced (double buffers)."""
+        offs = set()
+        for name, v in vars(self).items():
+            if name.endswith("_off") and isinstance(v, int):
+                offs.add(v)
+            elif isinstance(v, list) and v and all(isinstance(i, tuple) and len(i) == 2 and isinstance(i[0], int)
+                                                   and torch.is_tensor(i[1]) for i in v):
+                offs.update(i[0] for i in v)
+        return sorted(offs)
+
+    def close(self) -> None:
+        """Give the op's symmetric buffers and flag words back. COLLECTIVE: every member closes
+        the same ops in the same order (``FusedContext.release_slot``)."""
+        if self._closed:
+            return
+        self._closed = True
+        if self.flag_base is not None:
+            self.ctx.release_slot(self.flag_base)      # synchronises the device and the members
+        else:
+            torch.cuda.synchronize()
+            self.ctx.comm.Barrier()
+        for off in self._heap_offsets():
+            self.ctx.heap.free(off)
+        for name, v in list(vars(self).items()):       # drop the views: the memory may be handed out again
+            if torch.is_tensor(v) or (isinstance(v, list) and v and isinstance(v[0], tuple)):
+                setattr(self, name, None)
+
+    def _check_open(self):
+        if self._closed:
+            raise RuntimeError(f"{type(self).__name__} used after close()")
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+        return False
+
+
+def close_fused_ops(module) -> int:
+    """Close every fused op held by ``module`` and its submodules (COLLECTIVE; the order is the
+    module tree's, which is the same on every member). Returns how many were closed. For programs
+    that rebuild their layers with another token count: without this the old layers' flag words
+    and symmetric buffers stay reserved until the communicator goes away."""
+    done = 0
+    for m in module.modules():
+        for name in sorted(vars(m)):
+            v = getattr(m, name)
+            if isinstance(v, FusedOp) and not v._closed:
+                v.close()
+                done += 1
+    return done
 
 
 def _ctx(comm) -> FusedContext:
@@ -151,7 +231,7 @@ def _ctx(comm) -> FusedContext:
     return c
 
 
-class AllGatherGemm:
+class AllGatherGemm(FusedOp):
     """``y = gather_last_axis(x) @ w`` with the gather fused into the GEMM's K loop.
 
     ``x``: ``[M, K/n]`` bf16 per rank (copied into / taken from the symmetric heap), ``w``:
@@ -182,6 +262,7 @@ class AllGatherGemm:
                  out_dtype=torch.bfloat16, num_sms: int = 0, stream=None, gelu_out=None, dgelu_of=None, add=None):
         """``gelu_out`` / ``dgelu_of`` / ``add``: elementwise work fused into the epilogue, as in
         ``ops.gemm.gemm``; with ``gelu_out`` the call returns ``(y, gelu(y))``."""
+        self._check_open()
         if x.data_ptr() != self.x.data_ptr():
             self.x.copy_(x.reshape(self.M, self.chunk))
         Nn = w.shape[1] if b_kn else w.shape[0]
@@ -201,7 +282,7 @@ class AllGatherGemm:
         return (out, e_out2) if op == EPI_GELU_DUAL else out
 
 
-class GemmReduceScatter:
+class GemmReduceScatter(FusedOp):
     """``reduce_scatter_last_axis(a @ b)`` with the scatter + ordered reduction fused into the
     GEMM epilogue / tail. Result ``[M, N/n]``."""
 
@@ -218,6 +299,7 @@ class GemmReduceScatter:
                  add: Optional[torch.Tensor] = None) -> torch.Tensor:
         """``add``: a ``[M, N/n]`` bf16 tensor added to the reduced result by the reducer (residual
         connection / gradient accumulation) before the single rounding."""
+        self._check_open()
         K = a.shape[0] if a_km else a.shape[1]
         if out is None:
             out = torch.empty((self.M, self.chunk), dtype=self.dtype, device=a.device)
@@ -230,7 +312,7 @@ class GemmReduceScatter:
         return out
 
 
-class GemmAllReduce:
+class GemmAllReduce(FusedOp):
     """``all_reduce(a @ b)``: every rank ends with the full ``[M, N]`` sum in a symmetric buffer."""
 
     def __init__(self, comm, M: int, Nfull: int, *, dtype=torch.bfloat16, use_mc: bool = True):
@@ -245,6 +327,7 @@ class GemmAllReduce:
 
     def __call__(self, a: torch.Tensor, b: torch.Tensor, *, a_km: bool = False, b_kn: bool = False, num_sms: int = 0,
                  stream=None) -> torch.Tensor:
+        self._check_open()
         K = a.shape[0] if a_km else a.shape[1]
         self.epoch += 1
         off, out = self.outs[self.epoch & 1]
@@ -254,7 +337,7 @@ class GemmAllReduce:
         return out
 
 
-class GemmAllGather:
+class GemmAllGather(FusedOp):
     """``gather_last_axis(a @ b)``: each finished tile is stored into every rank's ``[M, N*n]``."""
 
     def __init__(self, comm, M: int, Nlocal: int, *, dtype=torch.bfloat16, use_mc: bool = True):
@@ -267,6 +350,7 @@ class GemmAllGather:
 
     def __call__(self, a: torch.Tensor, b: torch.Tensor, *, a_km: bool = False, b_kn: bool = True, num_sms: int = 0,
                  stream=None) -> torch.Tensor:
+        self._check_open()
         K = a.shape[0] if a_km else a.shape[1]
         self.epoch += 1
         off, out = self.outs[self.epoch & 1]

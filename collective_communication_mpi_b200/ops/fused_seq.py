@@ -21,7 +21,7 @@ import torch
 
 from .. import _native as N
 from .collectives import _arr, _sp
-from .fused import _OUT, _ctx, _ptrs, ag_ctas
+from .fused import _OUT, FusedOp, _ctx, _ptrs, ag_ctas
 
 
 def ag_gemm_m_raw(comms, x_off: int, ldx: int, xfull_off: int, B: List[torch.Tensor], Cout: List[torch.Tensor],
@@ -60,7 +60,7 @@ def _check_rows(M: int, n: int):
         raise ValueError(f"rows per rank M/n = {M}/{n} must be a multiple of 256")
 
 
-class AllGatherGemmM:
+class AllGatherGemmM(FusedOp):
     """``y = concat_rows(x_0, ..., x_{n-1}) @ w``; ``x``: this rank's ``[M/n, K]`` bf16 rows."""
 
     def __init__(self, comm, M: int, K: int):
@@ -82,6 +82,7 @@ class AllGatherGemmM:
 
     def __call__(self, x: torch.Tensor, w: torch.Tensor, *, b_kn: bool = True, out: Optional[torch.Tensor] = None,
                  out_dtype=torch.bfloat16, num_sms: int = 0, stream=None) -> torch.Tensor:
+        self._check_open()
         if x.data_ptr() != self.x.data_ptr():
             self.x.copy_(x.reshape(self.rows, self.K))
         Nn = w.shape[1] if b_kn else w.shape[0]
@@ -95,7 +96,7 @@ class AllGatherGemmM:
         return out
 
 
-class GemmReduceScatterM:
+class GemmReduceScatterM(FusedOp):
     """Rows ``[rank*M/n, (rank+1)*M/n)`` of ``sum over ranks of a @ b``; result ``[M/n, N]``."""
 
     def __init__(self, comm, M: int, Nfull: int, *, dtype=torch.bfloat16):
@@ -109,6 +110,7 @@ class GemmReduceScatterM:
 
     def __call__(self, a: torch.Tensor, b: torch.Tensor, *, a_km: bool = False, b_kn: bool = False,
                  out: Optional[torch.Tensor] = None, num_sms: int = 0, stream=None) -> torch.Tensor:
+        self._check_open()
         K = a.shape[0] if a_km else a.shape[1]
         if out is None:
             out = torch.empty((self.rows, self.N), dtype=self.dtype, device=a.device)
@@ -132,7 +134,7 @@ def ag_gemm_ag_raw(comms, x_off: int, ldx: int, xfull_off: int, B: List[torch.Te
     N.count_launch()
 
 
-class AllGatherGemmAllGather:
+class AllGatherGemmAllGather(FusedOp):
     """``gather_last_axis(gather_last_axis(x) @ w)``: ``naive_collect_forward_input``, the FC GEMM
     and ``naive_collect_forward_output`` (func_impl.py:76-109) as ONE kernel. ``x``: ``[M, K/n]``
     bf16 per rank; ``w``: this rank's ``[K, N]`` (``b_kn``) or ``[N, K]`` shard; result ``[M, N*n]``
@@ -154,6 +156,7 @@ class AllGatherGemmAllGather:
         return self.xfull[self.epoch & 1][1]
 
     def __call__(self, x: torch.Tensor, w: torch.Tensor, *, b_kn: bool = True, num_sms: int = 0, stream=None) -> torch.Tensor:
+        self._check_open()
         if x.data_ptr() != self.x.data_ptr():
             self.x.copy_(x.reshape(self.M, self.chunk))
         self.epoch += 1

@@ -1,8 +1,12 @@
-"""fp8 (e4m3) GEMM on the CTA-pair tcgen05 kernel (csrc/gemm_fp8.cu) with per-tensor scales.
+"""fp8 GEMMs on the CTA-pair tcgen05 kernel.
 
-EXPERIMENTAL (round 1): compiled and SASS-checked (``UTCQMMA.2CTA``) but not yet run on a GPU --
-the round's GPU budget was spent when it was written. Not used by any default path. First step
-towards the block-scaled fp8 configuration of BASELINE.md (config 3).
+* per-tensor-scaled e4m3 (``gemm_fp8``, csrc/gemm_fp8.cu, ``UTCQMMA.2CTA``);
+* block-scaled MXFP8 (``kind::mxf8f6f4.block_scale``: e4m3 payload, one e8m0 scale per 32 values;
+  csrc/fused_gemm_mx.cu): the plain GEMM, the CUDA quantiser, and the two fused
+  GEMM+collective ops of the tensor-parallel forward (``AllGatherGemmMX``, ``GemmReduceScatterMX``).
+
+Run on B200 in round 2 (tests/test_gpu_fp8.py, tests/test_gpu_mx_fused.py; numbers in
+profiles/R2_RESULTS.md). The block-scaled configuration is BASELINE.md's config 3.
 """
 from __future__ import annotations
 
@@ -11,6 +15,7 @@ import ctypes as C
 import torch
 
 from .. import _native as N
+from .fused import FusedOp
 
 E4M3_MAX = 448.0
 
@@ -224,7 +229,7 @@ class QuantizedWeight:
         self.N, self.K = wt.shape
 
 
-class AllGatherGemmMX:
+class AllGatherGemmMX(FusedOp):
     """``gather_last_axis(x) @ w`` with block-scaled fp8 operands: every rank quantises its ``[M, K/n]`` shard,
     and the fused kernel pushes e4m3 payload + scale chunks -- half the NVLink bytes of the bf16 gather -- while
     its tensor cores start on the local K range (func_impl.py:76-91 + the FC GEMM, in MXFP8)."""
@@ -247,6 +252,7 @@ class AllGatherGemmMX:
         self.epoch, self.flag_total = 0, 0
 
     def __call__(self, x: torch.Tensor, w: QuantizedWeight, *, out=None, out_dtype=torch.bfloat16, num_sms: int = 0, stream=None):
+        self._check_open()
         from ..utils import ktrace as KT
         from .fused import ag_ctas
         quantize_mxfp8_cuda(x.reshape(self.M, self.chunk), self.xq, self.sfl, stream=stream)
@@ -261,7 +267,7 @@ class AllGatherGemmMX:
         return out
 
 
-class GemmReduceScatterMX:
+class GemmReduceScatterMX(FusedOp):
     """``reduce_scatter_last_axis(a @ w)`` with block-scaled fp8 operands and bf16 partial tiles
     (the GEMM + func_impl.py:150-187 in MXFP8). ``a``: bf16 ``[M, K]`` (quantised here) ."""
 
@@ -277,6 +283,7 @@ class GemmReduceScatterMX:
         self.epoch = 0
 
     def __call__(self, a: torch.Tensor, w: QuantizedWeight, *, out=None, add=None, num_sms: int = 0, stream=None):
+        self._check_open()
         from ..utils import ktrace as KT
         aq, asf = quantize_mxfp8_cuda(a.reshape(self.M, -1), stream=stream)
         if out is None:
