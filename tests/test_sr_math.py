@@ -60,7 +60,8 @@ def test_non_finite_values_pass_through():
 
 def test_rounding_is_unbiased_where_nearest_rounding_loses_the_update():
     """w = 1.0 has a bf16 ulp of 2^-7; an update of 2^-11 is lost by round-to-nearest every step.
-    Stochastically it is applied with probability 1/16, so the MEAN moves by the true amount."""
+    Stochastically the step down (2^-8, the ulp below 1.0) is taken with probability 1/8, so the MEAN moves by
+    the true amount."""
     n = 1 << 16
     w = torch.ones(n)
     upd = 2.0 ** -11
