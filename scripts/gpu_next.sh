@@ -1,0 +1,28 @@
+#!/bin/bash
+# What has not run on hardware yet (written or fixed after round 2's GPU minutes were spent), each
+# under its own timeout. Needs >= 2 GPUs for the first item, 8 for the last.
+#   gpurun --gpus 2 --timeout 900  -- 'bash scripts/gpu_next.sh'
+#   gpurun --gpus 8 --timeout 1200 -- 'bash scripts/gpu_next.sh'
+# Results: gpurun_out/next_<N>gpu.txt and one log per item.
+mkdir -p gpurun_out
+NG=$(nvidia-smi -L | wc -l)
+OUT=gpurun_out/next_${NG}gpu.txt
+: > "$OUT"
+run() {   # run <label> <timeout> <command...>
+    local label=$1 limit=$2; shift 2
+    local log=gpurun_out/next_${label}_${NG}gpu.log
+    timeout "$limit" "$@" > "$log" 2>&1
+    local rc=$?
+    echo "[$label] rc=$rc  $(tail -1 "$log")" | tee -a "$OUT"
+}
+# 1. closing fused ops: flag words zeroed between barriers and reused by another kind of op
+run slot_reuse 300 python -m pytest tests/test_zzz_slot_reuse.py -q
+# 2. smoke() as the driver runs it (five steps, loss must fall)
+run smoke 300 python -c 'import __graft_entry__ as g; g.smoke(); print("SMOKE OK")'
+if [ "$NG" -ge 8 ]; then
+    # 3. the dp8 grid of the bench (gradient all-reduce + fused update only) after the last-bucket ordering
+    #    fix in parallel/dp.py; mp2 x dp4 was re-measured after the fix, dp8 was not
+    CCMPI_BENCH_MP=1 run bench_dp8 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 \
+        --master-addr 127.0.0.1 --master-port 29611 bench.py --gpus 8 --steps 20 --warmup 5
+fi
+cat "$OUT"
