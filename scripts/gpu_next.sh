@@ -20,9 +20,9 @@ run slot_reuse 300 python -m pytest tests/test_zzz_slot_reuse.py -q
 # 2. smoke() as the driver runs it (five steps, loss must fall)
 run smoke 300 python -c 'import __graft_entry__ as g; g.smoke(); print("SMOKE OK")'
 if [ "$NG" -ge 8 ]; then
-    # 3. the dp8 grid of the bench (gradient all-reduce + fused update only) after the last-bucket ordering
-    #    fix in parallel/dp.py; mp2 x dp4 was re-measured after the fix, dp8 was not
-    CCMPI_BENCH_MP=1 run bench_dp8 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 \
-        --master-addr 127.0.0.1 --master-port 29611 bench.py --gpus 8 --steps 20 --warmup 5
+    # 3. BASELINE config 4 (dp8: weights replicated, gradient all-reduce fused with the update) after the
+    #    last-bucket ordering fix in parallel/dp.py; mp2 x dp4 was re-measured after the fix, dp8 was not
+    run config_dp8 400 python -m collective_communication_mpi_b200.launch -n 8 --transport device \
+        python benchmarks/config_bench.py --config dp8
 fi
 cat "$OUT"
