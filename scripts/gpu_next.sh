@@ -17,6 +17,8 @@ run() {   # run <label> <timeout> <command...>
 }
 # 1. closing fused ops: flag words zeroed between barriers and reused by another kind of op
 run slot_reuse 300 python -m pytest tests/test_zzz_slot_reuse.py -q
+# 1b. one flag region, launches with changing CTA counts (absolute ready-flag targets)
+run flag_targets 300 python -m pytest tests/test_zzz_flag_targets.py -q
 # 2. smoke() as the driver runs it (five steps, loss must fall)
 run smoke 300 python -c 'import __graft_entry__ as g; g.smoke(); print("SMOKE OK")'
 if [ "$NG" -ge 8 ]; then
