@@ -21,10 +21,19 @@ from torch import nn
 
 from ..ops import elementwise as EW
 from ..parallel.dp import GradSink, sgd_step
-from ..parallel.tp_layers import ColumnParallelLinear, RowParallelLinear, attn_block, mlp_block
+from ..parallel.tp_layers import ColumnParallelLinear, RowParallelLinear, attn_block, mlp_block, set_tokens
 
 
-class TransformerFCBlock(nn.Module):
+class _Resizable:
+    """``set_tokens(tokens)``: rebuild every layer's fused ops for another token count (COLLECTIVE over
+    the model-parallel group; ``parallel.tp_layers.set_tokens``). The next ``forward`` takes inputs of the
+    new size; weights and optimizer state are kept."""
+
+    def set_tokens(self, tokens: int) -> None:
+        set_tokens(*([self.tp_layers()[0], tokens] + self.tp_layers()[1:]))
+
+
+class TransformerFCBlock(_Resizable, nn.Module):
     def __init__(self, mp_comm, tokens: int, hidden: int, ffn_mult: int = 4, *, seed: int = 0, num_comm_ctas: int = 0):
         super().__init__()
         self.hidden, self.mp = hidden, mp_comm.Get_size()
@@ -54,7 +63,7 @@ class TransformerFCBlock(nn.Module):
         return h + self.fc2(u)
 
 
-class TransformerFCBlockSP(nn.Module):
+class TransformerFCBlockSP(_Resizable, nn.Module):
     """The same block in the sequence-parallel layout (``parallel/sp_layers.py``): input and output are
     this rank's ``tokens/mp`` rows of the full width, so the residual adds touch 1/mp of the data; between
     the GEMM pairs the activation is feature-sharded as in ``TransformerFCBlock``."""
@@ -82,7 +91,7 @@ class TransformerFCBlockSP(nn.Module):
         return h + self.fc2(u)
 
 
-class TransformerFCBlockMegatron(nn.Module):
+class TransformerFCBlockMegatron(_Resizable, nn.Module):
     """The same block in the classic Megatron layout (``parallel/megatron_layers.py``): the residual stream
     ``[tokens, hidden]`` is replicated on every model-parallel rank; each column/row pair ends in a GEMM fused
     with an all-reduce. Note that with replicated outputs every rank computes the same loss on the same data."""
@@ -110,7 +119,7 @@ class TransformerFCBlockMegatron(nn.Module):
         return h + self.fc2(u)
 
 
-class MLPStack(nn.Module):
+class MLPStack(_Resizable, nn.Module):
     def __init__(self, mp_comm, tokens: int, width: int, depth: int, *, seed: int = 0):
         super().__init__()
         self.layers = nn.ModuleList(

@@ -75,7 +75,24 @@ def gemm_sgd_(w: torch.Tensor, a: torch.Tensor, b: torch.Tensor, lr: float, *, a
     return w
 
 
-class AllGatherGemm:
+class _HostOp:
+    """Life cycle of the CUDA ops (``ops.fused.FusedOp``): the CPU statements own no symmetric memory or
+    flag words, so ``close()`` only marks the object."""
+
+    _closed = False
+
+    def close(self) -> None:
+        self._closed = True
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+        return False
+
+
+class AllGatherGemm(_HostOp):
     """``gather_last_axis(x) @ w`` (func_impl.py:76-91 + the FC GEMM)."""
 
     def __init__(self, comm, M: int, K: int, *, num_comm_ctas: int = 0, use_mc: bool = True):
@@ -91,7 +108,7 @@ class AllGatherGemm:
         return gemm(self._gathered, w, b_kn=b_kn, out=out, out_dtype=out_dtype, gelu_out=gelu_out, dgelu_of=dgelu_of, add=add)
 
 
-class GemmReduceScatter:
+class GemmReduceScatter(_HostOp):
     """``reduce_scatter_last_axis(a @ b)`` (the dx GEMM + func_impl.py:150-187)."""
 
     def __init__(self, comm, M: int, Nfull: int, *, dtype=torch.bfloat16):
@@ -109,7 +126,7 @@ class GemmReduceScatter:
         return red
 
 
-class GemmAllReduce:
+class GemmAllReduce(_HostOp):
     """``all_reduce(a @ b)``."""
 
     def __init__(self, comm, M: int, Nfull: int, *, dtype=torch.bfloat16, use_mc: bool = True):
@@ -122,7 +139,7 @@ class GemmAllReduce:
         return out.to(self.dtype)
 
 
-class GemmAllGather:
+class GemmAllGather(_HostOp):
     """``gather_last_axis(a @ b)`` (the FC GEMM + func_impl.py:94-109)."""
 
     def __init__(self, comm, M: int, Nlocal: int, *, dtype=torch.bfloat16, use_mc: bool = True):
@@ -133,7 +150,7 @@ class GemmAllGather:
 
 
 # ---- token-axis (sequence-parallel) forms: ops/fused_seq.py -----------------------------------------
-class AllGatherGemmM:
+class AllGatherGemmM(_HostOp):
     """``concat_rows(x_0, ..., x_{n-1}) @ w``; ``x``: this rank's ``[M/n, K]`` rows."""
 
     def __init__(self, comm, M: int, K: int):
@@ -150,7 +167,7 @@ class AllGatherGemmM:
         return gemm(full, w, b_kn=b_kn, out=out, out_dtype=out_dtype)
 
 
-class GemmReduceScatterM:
+class GemmReduceScatterM(_HostOp):
     """Rows ``[rank*M/n, (rank+1)*M/n)`` of ``sum over ranks of a @ b``."""
 
     def __init__(self, comm, M: int, Nfull: int, *, dtype=torch.bfloat16):

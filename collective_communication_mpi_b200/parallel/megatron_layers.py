@@ -24,7 +24,7 @@ from __future__ import annotations
 import torch
 from torch import nn
 
-from .tp_layers import _backend, _dw_last, _init_weight, _weight_grad
+from .tp_layers import _backend, _dw_last, _init_weight, _weight_grad, set_tokens
 
 
 class _ColFn(torch.autograd.Function):
@@ -79,8 +79,16 @@ class MegatronColumnParallelLinear(nn.Module):
         dev, ops, self._gemm, self._matmul_tn, self._gemm_sgd = _backend()
         self.sgd_lr = None
         self.weight = _init_weight(in_features, self.N, in_features, dev, seed * 1000 + mp_comm.Get_rank())
-        self.ar = ops.GemmAllReduce(mp_comm, tokens, in_features) if self.mp > 1 else None      # backward dx
+        self._ops = ops
+        self._build_ops()
         self.num_sms = 0
+
+    def _build_ops(self):
+        self.ar = self._ops.GemmAllReduce(self.comm, self.M, self.K) if self.mp > 1 else None      # backward dx
+
+    def set_tokens(self, tokens: int) -> None:
+        """Rebuild the fused op for another token count (COLLECTIVE; ``tp_layers.set_tokens``)."""
+        set_tokens(self, tokens)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         return _ColFn.apply(x.reshape(self.M, -1), self.weight, self)
@@ -97,8 +105,16 @@ class MegatronRowParallelLinear(nn.Module):
         dev, ops, self._gemm, self._matmul_tn, self._gemm_sgd = _backend()
         self.sgd_lr = None
         self.weight = _init_weight(self.K, out_features, in_features, dev, seed * 1000 + mp_comm.Get_rank())
-        self.ar = ops.GemmAllReduce(mp_comm, tokens, out_features) if self.mp > 1 else None
+        self._ops = ops
+        self._build_ops()
         self.num_sms = 0
+
+    def _build_ops(self):
+        self.ar = self._ops.GemmAllReduce(self.comm, self.M, self.N) if self.mp > 1 else None
+
+    def set_tokens(self, tokens: int) -> None:
+        """Rebuild the fused op for another token count (COLLECTIVE; ``tp_layers.set_tokens``)."""
+        set_tokens(self, tokens)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         return _RowFn.apply(x.reshape(self.M, -1), self.weight, self)

@@ -26,7 +26,7 @@ from torch import nn
 
 from ..ops import fused_seq as FS
 from ..ops import host_ops as H
-from .tp_layers import _backend, _dw_last, _init_weight, _weight_grad
+from .tp_layers import _backend, _dw_last, _init_weight, _weight_grad, set_tokens
 
 
 def _seq_ops():
@@ -84,10 +84,17 @@ class SeqColumnParallelLinear(nn.Module):
         dev, _, self._gemm, self._matmul_tn, self._gemm_sgd = _backend()
         self.sgd_lr = None
         self.weight = _init_weight(in_features, self.N, in_features, dev, seed * 1000 + mp_comm.Get_rank())
-        ops = _seq_ops()
-        self.ag = ops.AllGatherGemmM(mp_comm, tokens, in_features)
-        self.rs = ops.GemmReduceScatterM(mp_comm, tokens, in_features)
+        self._build_ops()
         self.num_sms = 0
+
+    def _build_ops(self):
+        ops = _seq_ops()
+        self.ag = ops.AllGatherGemmM(self.comm, self.M, self.K)
+        self.rs = ops.GemmReduceScatterM(self.comm, self.M, self.K)
+
+    def set_tokens(self, tokens: int) -> None:
+        """Rebuild the fused ops for another token count (COLLECTIVE; ``tp_layers.set_tokens``)."""
+        set_tokens(self, tokens)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         return _SeqColumnFn.apply(x.reshape(self.M // self.mp, -1), self.weight, self)
@@ -106,10 +113,17 @@ class SeqRowParallelLinear(nn.Module):
         dev, _, self._gemm, self._matmul_tn, self._gemm_sgd = _backend()
         self.sgd_lr = None
         self.weight = _init_weight(self.K, out_features, in_features, dev, seed * 1000 + mp_comm.Get_rank())
-        ops = _seq_ops()
-        self.rs = ops.GemmReduceScatterM(mp_comm, tokens, out_features)
-        self.ag = ops.AllGatherGemmM(mp_comm, tokens, out_features)
+        self._build_ops()
         self.num_sms = 0
+
+    def _build_ops(self):
+        ops = _seq_ops()
+        self.rs = ops.GemmReduceScatterM(self.comm, self.M, self.N)
+        self.ag = ops.AllGatherGemmM(self.comm, self.M, self.N)
+
+    def set_tokens(self, tokens: int) -> None:
+        """Rebuild the fused ops for another token count (COLLECTIVE; ``tp_layers.set_tokens``)."""
+        set_tokens(self, tokens)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         return _SeqRowFn.apply(x.reshape(self.M, -1), self.weight, self)

@@ -109,6 +109,26 @@ def _dw_last(layer) -> bool:
     return sink is not None and sink.updates_in_backward
 
 
+def set_tokens(layer, tokens: int, *more_layers) -> None:
+    """Give a layer (or several: a whole block) another token count ``M``. The fused ops own staging
+    buffers and flag regions sized by ``M`` (``[M, K]`` gather buffers, one flag per 128-row block), so
+    the old ones are closed -- their symmetric memory and flag words go back to the allocators
+    (``ops.fused.FusedOp.close``) -- and new ones are built in the constructors' order. With several
+    layers everything is closed before anything is built, so growing does not need room for both
+    generations. COLLECTIVE: every member of the layers' group calls it at the same point with the
+    same ``tokens``. Weights, optimizer wiring and SM budgets are untouched."""
+    layers = [l for l in (layer, *more_layers) if l.M != tokens]
+    for l in layers:
+        for name in ("ag", "rs", "ar", "out_ag"):
+            op = getattr(l, name, None)
+            if op is not None:
+                op.close()
+                setattr(l, name, None)
+    for l in layers:
+        l.M = tokens
+        l._build_ops()
+
+
 def _init_weight(rows: int, cols: int, fan_in: int, device, seed: int) -> nn.Parameter:
     g = torch.Generator(device=device).manual_seed(seed)
     w = torch.randn(rows, cols, device=device, generator=g, dtype=torch.float32) * (1.0 / math.sqrt(fan_in))
@@ -129,18 +149,28 @@ class ColumnParallelLinear(nn.Module):
         self.sgd_lr = None      # set by TrainStep when the optimizer step is fused into the dW GEMM
         self.sgd_step, self.sgd_seed = None, seed
         self.weight = _init_weight(in_features, self.N, in_features, dev, seed * 1000 + mp_comm.Get_rank())
-        # a 1-member group needs no staging buffers or flags: plain GEMMs
-        self.ag = ops.AllGatherGemm(mp_comm, tokens, in_features, num_comm_ctas=num_comm_ctas) if self.mp > 1 else None
-        self.rs = ops.GemmReduceScatter(mp_comm, tokens, in_features) if self.mp > 1 else None
-        # gather_output: by default the fused all-gather->GEMM is followed by the strided all-gather
-        # kernel on its output; CCMPI_FUSED_GATHER_OUTPUT=1 selects the single gather->GEMM->gather
-        # kernel (ops/fused_seq.py), which has not run on hardware yet
-        self.out_ag = None
-        if gather_output and self.mp > 1 and dev.type == "cuda" and os.environ.get("CCMPI_FUSED_GATHER_OUTPUT") == "1":
-            from ..ops.fused_seq import AllGatherGemmAllGather
-            self.out_ag = AllGatherGemmAllGather(mp_comm, tokens, in_features, self.N)
+        self._ops, self._dev, self._num_comm_ctas = ops, dev, num_comm_ctas
+        self._build_ops()
         self.num_sms = 0
         self.bwd_num_sms = 0    # SM budget of the backward fused kernel (set by GradSink when a reduction runs next to it)
+
+    def _build_ops(self):
+        ops, comm, tokens, in_features = self._ops, self.comm, self.M, self.K
+        # a 1-member group needs no staging buffers or flags: plain GEMMs
+        self.ag = ops.AllGatherGemm(comm, tokens, in_features, num_comm_ctas=self._num_comm_ctas) if self.mp > 1 else None
+        self.rs = ops.GemmReduceScatter(comm, tokens, in_features) if self.mp > 1 else None
+        # gather_output: by default the fused all-gather->GEMM is followed by the strided all-gather
+        # kernel on its output; CCMPI_FUSED_GATHER_OUTPUT=1 selects the single gather->GEMM->gather
+        # kernel (ops/fused_seq.py)
+        self.out_ag = None
+        if self.gather_output and self.mp > 1 and self._dev.type == "cuda" and os.environ.get("CCMPI_FUSED_GATHER_OUTPUT") == "1":
+            from ..ops.fused_seq import AllGatherGemmAllGather
+            self.out_ag = AllGatherGemmAllGather(comm, tokens, in_features, self.N)
+
+    def set_tokens(self, tokens: int) -> None:
+        """Rebuild the layer's fused ops for another token count (COLLECTIVE over the model-parallel
+        group; see ``set_tokens`` below). The weight is untouched."""
+        set_tokens(self, tokens)
 
     def input_buffer(self) -> torch.Tensor:
         """Write the layer input here (symmetric memory) to skip one device copy."""
@@ -196,10 +226,19 @@ class RowParallelLinear(nn.Module):
         self.sgd_lr = None
         self.sgd_step, self.sgd_seed = None, seed
         self.weight = _init_weight(self.K, out_features, in_features, dev, seed * 1000 + mp_comm.Get_rank())
-        self.rs = ops.GemmReduceScatter(mp_comm, tokens, out_features) if self.mp > 1 else None
-        self.ag = ops.AllGatherGemm(mp_comm, tokens, out_features, num_comm_ctas=num_comm_ctas) if self.mp > 1 else None
+        self._ops, self._num_comm_ctas = ops, num_comm_ctas
+        self._build_ops()
         self.num_sms = 0
         self.bwd_num_sms = 0
+
+    def _build_ops(self):
+        ops, comm, tokens = self._ops, self.comm, self.M
+        self.rs = ops.GemmReduceScatter(comm, tokens, self.N) if self.mp > 1 else None
+        self.ag = ops.AllGatherGemm(comm, tokens, self.N, num_comm_ctas=self._num_comm_ctas) if self.mp > 1 else None
+
+    def set_tokens(self, tokens: int) -> None:
+        """Rebuild the layer's fused ops for another token count (COLLECTIVE over the model-parallel group)."""
+        set_tokens(self, tokens)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         return _RowFn.apply(x.reshape(self.M, -1), self.weight, self)

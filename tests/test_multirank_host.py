@@ -169,3 +169,10 @@ def test_megatron_layout_block_matches_dense_model_on_cpu(mp, dp):
 def test_sibling_groups_that_split_again_get_distinct_ids_and_do_not_disturb_each_other():
     """Two halves of the world split at the same time: ids come from one job-wide counter."""
     _ok(run_ranks(8, ["tests/workers/w_nested_split.py"], timeout=120), "NESTED SPLIT OK")
+
+
+@pytest.mark.parametrize("flags", [[], ["--sp"], ["--megatron"]], ids=["feature-sharded", "sequence-parallel", "megatron"])
+def test_blocks_can_be_given_another_token_count(flags):
+    """``set_tokens``: fused ops closed and rebuilt, weights kept, results still those of the dense model."""
+    sp, meg = int("--sp" in flags), int("--megatron" in flags)
+    _ok(run_ranks(2, ["tests/workers/w_set_tokens.py", "2"] + flags, timeout=240), f"SET TOKENS OK mp=2 sp={sp} megatron={meg}")

@@ -16,3 +16,15 @@ def test_flag_regions_are_reusable_after_close():
     proc = run_ranks(ranks, ["tests/workers/w_slot_reuse.py"], transport="device")
     assert proc.returncode == 0, f"rc={proc.returncode}\n--- stdout\n{proc.stdout[-4000:]}\n--- stderr\n{proc.stderr[-3000:]}"
     assert f"SLOT REUSE OK ranks={ranks}" in proc.stdout
+
+
+@pytest.mark.parametrize("flags", [[], ["--sp"], ["--megatron"]], ids=["feature-sharded", "sequence-parallel", "megatron"])
+def test_blocks_can_be_given_another_token_count_on_gpus(flags):
+    """``set_tokens`` on the fused kernels: the old ops' flag words and symmetric buffers come back
+    (the worker checks the allocators) and the rebuilt ops match the dense model."""
+    if gpu_count() < 2:
+        pytest.skip("needs at least 2 GPUs")
+    sp, meg = int("--sp" in flags), int("--megatron" in flags)
+    proc = run_ranks(2, ["tests/workers/w_set_tokens.py", "2"] + flags, transport="device")
+    assert proc.returncode == 0, f"rc={proc.returncode}\n--- stdout\n{proc.stdout[-4000:]}\n--- stderr\n{proc.stderr[-3000:]}"
+    assert f"SET TOKENS OK mp=2 sp={sp} megatron={meg}" in proc.stdout
