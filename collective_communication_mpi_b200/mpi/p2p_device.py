@@ -19,11 +19,11 @@ route ("put-with-signal mailbox ... CUDA / memcpy"):
   lazily, on its next point-to-point call (or when the heap runs short).
 
 Ordering, matching and error reporting are those of the host rings (strict FIFO per pair, tag and
-communicator checked). Both ends must use CUDA tensors in this mode; a descriptor landing in a
-NumPy receive buffer is not detected.
+communicator checked). A receiver may post a NumPy / CPU buffer against a CUDA sender: it recognises
+the descriptor and copies the payload out of the sender's staging block (``complete_receive_host``).
 
-EXPERIMENTAL in round 1: the control path (descriptors, ack counters, reclamation) runs in the CPU
-suite against a stand-in heap; the NVLink copy has not run on a multi-GPU box yet.
+The control path (descriptors, ack counters, reclamation) runs in the CPU suite against a stand-in
+heap (tests/test_p2p_device_control.py); the NVLink copy on 2 / 4 / 8 B200s (tests/test_gpu_p2p_device.py).
 """
 from __future__ import annotations
 

@@ -10,8 +10,9 @@ op                     computes                                               NC
 The reference shards the feature axis only (model/func_impl.py:90,108,182); this is the layout
 Megatron-style sequence parallelism adds on top. Kernels: csrc/fused_policies_m.cuh.
 
-EXPERIMENTAL in round 1: compiled for sm_100a but not yet run on hardware (the round's GPU budget
-was spent); tests are opt-in (``CCMPI_TEST_UNVERIFIED=1``). Nothing in the default paths uses it.
+Run on B200s in round 2: emulated ranks on one GPU and real ranks on 2 / 4 / 8 (tests/test_gpu_seq.py);
+numbers in profiles/r2_seq_bench_2gpu.jsonl. Used by ``parallel/sp_layers.py`` and, with
+``CCMPI_FUSED_GATHER_OUTPUT=1``, by ``ColumnParallelLinear(gather_output=True)``.
 """
 from __future__ import annotations
 

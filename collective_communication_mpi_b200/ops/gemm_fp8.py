@@ -112,7 +112,7 @@ def gemm_mxfp8(a_q: torch.Tensor, a_sf: torch.Tensor, b_q: torch.Tensor, b_sf: t
     """``out[M,N] = dequant(a) @ dequant(b).T`` on the block-scaled tensor-core path (csrc/gemm_mxfp8.cu).
     ``a_q [M,K]`` / ``b_q [N,K]``: ``float8_e4m3fn``; ``a_sf [M,K/32]`` / ``b_sf [N,K/32]``: row-major UE8M0
     scales as returned by ``quantize_mxfp8`` (re-laid out here), or 1-D tensors already in the hardware
-    layout (``swizzle_scales``; do that once for weights). Experimental: not yet run on hardware."""
+    layout (``swizzle_scales``; do that once for weights)."""
     if a_q.dtype != torch.float8_e4m3fn or b_q.dtype != torch.float8_e4m3fn:
         raise TypeError("gemm_mxfp8 takes float8_e4m3fn operands")
     M, K = a_q.shape

@@ -16,8 +16,8 @@ keeps the residual stream whole on every rank. The reference's ``get_info`` part
 this way (column-parallel fc_q/k/v, row-parallel fc_o, func_impl.py:65-70), so both layouts share shards.
 
 The all-reduce is fused into the producing GEMM (``ops.fused.GemmAllReduce``, ArPolicy in
-csrc/fused_policies.cuh -- verified on B200); the layers around it are checked on the CPU against a dense
-model and have not run on GPUs yet.
+csrc/fused_policies.cuh); the layers are checked against a dense model on CPU ranks and on 4 / 8 B200s
+(tests/test_gpu_seq.py::test_megatron_layout*).
 """
 from __future__ import annotations
 

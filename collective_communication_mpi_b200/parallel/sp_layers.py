@@ -16,7 +16,7 @@ full width -- so the elementwise work there (residuals, norms, dropout) shrinks 
 
 The reference never shards tokens inside a replica (its gathers and scatters are all on the feature
 axis, func_impl.py:90,108,182); SURVEY section 5.7 lists this layout as the optional extension of the
-same fused kernels. Kernels: ``ops/fused_seq.py`` (not yet run on hardware); without a GPU the layers
+same fused kernels. Kernels: ``ops/fused_seq.py``; without a GPU the layers
 run the CPU statement in ``ops/host_ops.py``, which is how their logic is tested.
 """
 from __future__ import annotations

@@ -12,7 +12,7 @@ all-reduces (mpi-test.py:40-98).
 
 Every rank must capture and replay the same sequence. Kernels go to ``torch.cuda.current_stream()``, which
 is the capture stream inside ``torch.cuda.graph``; nothing in the wrappers allocates or synchronises.
-EXPERIMENTAL: written after round 1's GPU budget was spent; its test is opt-in.
+Run on a B200 in round 2 (tests/test_gpu_graphs.py).
 """
 from __future__ import annotations
 

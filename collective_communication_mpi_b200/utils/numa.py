@@ -8,7 +8,7 @@ reference never needed it (README.md:52 runs CPU ranks). Here the rank pins itse
 process touches afterwards (pinned batches included) is then allocated on that node by first touch.
 
 Everything is best effort: no sysfs entry, node -1, or a cpuset that forbids the CPUs -> nothing changes.
-Not measured yet (written after round 1's GPU budget was spent), hence opt-in.
+Not measured yet (neither round had GPU minutes left for the A/B run), hence opt-in.
 """
 from __future__ import annotations
 
