@@ -212,12 +212,12 @@ class _DeviceSide:
         self.comms = [self.comm]
         self._members, self._me, self._cid = list(members), me, cid
         self._members_c = (C.c_int * len(members))(*members)
-        self._route_send = np.zeros(2, dtype=np.int64)
-        self._route_recv = np.zeros(2 * len(members), dtype=np.int64)
+        self._route_send = np.zeros(3, dtype=np.int64)
+        self._route_recv = np.zeros(3 * len(members), dtype=np.int64)
         self.alias = (False, False)
 
-    def agree(self, s: "_Buf", r: "_Buf"):
-        """Host-plane rendezvous in front of every front-end device collective. It does two jobs.
+    def agree(self, s: "_Buf", r: "_Buf", allow_host: bool = False) -> bool:
+        """Host-plane rendezvous in front of every front-end device collective. It does three jobs.
 
         (1) Zero-copy routing. A kernel applies ONE heap offset to every member
         (``heap[p] + off``), so an operand may be used in place only when every member passed a
@@ -229,24 +229,40 @@ class _DeviceSide:
 
         (2) Skew. MPI lets ranks reach a collective arbitrarily far apart; the device kernels'
         watchdog is for GPU-side faults. Meeting on the host first (the host plane waits
-        ``CCMPI_TIMEOUT`` seconds, like any MPI) leaves the device wait only GPU-side skew."""
+        ``CCMPI_TIMEOUT`` seconds, like any MPI) leaves the device wait only GPU-side skew.
+
+        (3) Small host payloads stay on the host. The reference's own workload is 800-byte NumPy
+        arrays (mpi-test.py:40-98): staging those into the heap, launching a kernel and
+        synchronising the stream costs ~140 us where the shared-memory plane needs ~17
+        (profiles/r2_config1_8gpu_box.jsonl). With ``allow_host`` each member also reports whether
+        its buffers are host memory of at most ``CCMPI_HOST_ROUTE_MAX`` bytes (default 64 KiB; 0
+        switches the route off); the return value is True when ALL members said so, and the caller
+        then uses the host plane. One member holding a CUDA tensor keeps everybody on the kernels."""
         n = len(self._members)
         if n == 1 or self.heap.emulated:
             self.alias = (False, False)
-            return
+            return False
 
         def base(b):
             if not b.cuda:
                 return -1
             off = self.heap.offset_of(b.flat)
             return off if off is not None and off % 16 == 0 else -1
-        self._route_send[0], self._route_send[1] = base(s), base(r)
+        host_ok = allow_host and not s.cuda and not r.cuda and max(s.nbytes, r.nbytes) <= host_route_max()
+        self._route_send[0], self._route_send[1], self._route_send[2] = base(s), base(r), int(host_ok)
         w = self.world
         N.check_host(w._hostlib.ccmpi_host_allgather(w.host, self._cid, self._members_c, n, self._me,
-                                                     self._route_send.ctypes.data, self._route_recv.ctypes.data, 16),
+                                                     self._route_send.ctypes.data, self._route_recv.ctypes.data, 24),
                      "device-collective rendezvous")
-        got = self._route_recv.reshape(n, 2)
+        got = self._route_recv.reshape(n, 3)
         self.alias = tuple(bool(got[0, k] >= 0 and (got[:, k] == got[0, k]).all()) for k in (0, 1))
+        return bool((got[:, 2] == 1).all())
+
+
+def host_route_max() -> int:
+    """Largest host buffer (bytes) that library collectives keep on the shared-memory plane when the
+    device plane is up (``_DeviceSide.agree``)."""
+    return int(os.environ.get("CCMPI_HOST_ROUTE_MAX", str(64 << 10)))
 
 
 class Comm:
@@ -421,8 +437,7 @@ class Comm:
         if len(self._members) == 1:
             _copy(r, s)
             return
-        if self._on_device(s, r):
-            _dev_allreduce(self._dev, s, r, op.code)
+        if self._on_device(s, r) and _dev_allreduce(self._dev, s, r, op.code, allow_host=True):
             return
         lib, h, cid, mem, n, me = self._hargs()
         N.check_host(lib.ccmpi_host_allreduce(h, cid, mem, n, me, s.ptr, r.ptr, s.count, s.cc, op.code), "Allreduce")
@@ -438,8 +453,7 @@ class Comm:
         if n == 1:
             _copy(r, s)
             return
-        if self._on_device(s, r):
-            _dev_allgather(self._dev, s, r, n)
+        if self._on_device(s, r) and _dev_allgather(self._dev, s, r, n, allow_host=True):
             return
         lib, h, cid, mem, n, me = self._hargs()
         N.check_host(lib.ccmpi_host_allgather(h, cid, mem, n, me, s.ptr, r.ptr, s.nbytes), "Allgather")
@@ -455,8 +469,7 @@ class Comm:
         if n == 1:
             _copy(r, s)
             return
-        if self._on_device(s, r):
-            _dev_reduce_scatter(self._dev, s, r, n, op.code)
+        if self._on_device(s, r) and _dev_reduce_scatter(self._dev, s, r, n, op.code, allow_host=True):
             return
         lib, h, cid, mem, n, me = self._hargs()
         N.check_host(lib.ccmpi_host_reduce_scatter(h, cid, mem, n, me, s.ptr, r.ptr, r.count, s.cc, op.code), "Reduce_scatter_block")
@@ -474,8 +487,7 @@ class Comm:
         if n == 1:
             _copy(r, s)
             return
-        if self._on_device(s, r):
-            _dev_alltoall(self._dev, s, r, n)
+        if self._on_device(s, r) and _dev_alltoall(self._dev, s, r, n, allow_host=True):
             return
         lib, h, cid, mem, n, me = self._hargs()
         N.check_host(lib.ccmpi_host_alltoall(h, cid, mem, n, me, s.ptr, r.ptr, s.nbytes // n), "Alltoall")
@@ -670,8 +682,7 @@ class Comm:
             src_t = np.ascontiguousarray(x)
             out = np.empty(tuple(x.shape[:-1]) + (pcols * n,), dtype=x.dtype)
         s, r = _Buf(src_t, False), _Buf(out, True)
-        if self._on_device(s, r):
-            _dev_allgather_rows(self._dev, s, r, n, rows, pcols * s.itemsize)
+        if self._on_device(s, r) and _dev_allgather_rows(self._dev, s, r, n, rows, pcols * s.itemsize, allow_host=True):
             return out
         if is_t:    # CPU tensor on the shared-memory plane
             flat = torch.empty((n, rows, pcols), dtype=x.dtype)
@@ -706,8 +717,7 @@ class Comm:
         s, r = _Buf(src_t, False), _Buf(out, True)
         if s.cc is None:
             raise TypeError(f"reduce-scatter: unsupported element type {x.dtype}")
-        if self._on_device(s, r):
-            _dev_reduce_scatter_rows(self._dev, s, r, n, rows, pcols, op.code)
+        if self._on_device(s, r) and _dev_reduce_scatter_rows(self._dev, s, r, n, rows, pcols, op.code, allow_host=True):
             return out
         if is_t:    # CPU tensor on the shared-memory plane
             blocks = src_t.reshape(rows, n, pcols).permute(1, 0, 2).contiguous()
@@ -860,8 +870,9 @@ def _finish(r: _Buf):
         torch.cuda.current_stream().synchronize()
 
 
-def _dev_allreduce(dev: _DeviceSide, s: _Buf, r: _Buf, op: int):
-    dev.agree(s, r)
+def _dev_allreduce(dev: _DeviceSide, s: _Buf, r: _Buf, op: int, allow_host: bool = False) -> bool:
+    if dev.agree(s, r, allow_host):
+        return False      # every member holds a small host buffer: the caller uses the host plane
     from ..ops import collectives as CO
     sin, sout, stmp, cap = _DeviceSide.STAGE
     es = s.itemsize
@@ -873,10 +884,12 @@ def _dev_allreduce(dev: _DeviceSide, s: _Buf, r: _Buf, op: int):
         CO.allreduce(dev.comms, s.cc, op, src, dst, nb // es, tmp_off=stmp)
         _stage_out(dev, r, dst, lo, nb)
     _finish(r)
+    return True
 
 
-def _dev_allgather(dev: _DeviceSide, s: _Buf, r: _Buf, n: int):
-    dev.agree(s, r)
+def _dev_allgather(dev: _DeviceSide, s: _Buf, r: _Buf, n: int, allow_host: bool = False) -> bool:
+    if dev.agree(s, r, allow_host):
+        return False      # every member holds a small host buffer: the caller uses the host plane
     from ..ops import collectives as CO
     sin, sout, _, cap = _DeviceSide.STAGE
     step = max(16, (cap // n) // 16 * 16)
@@ -892,10 +905,12 @@ def _dev_allgather(dev: _DeviceSide, s: _Buf, r: _Buf, n: int):
             for j in range(n):
                 _stage_out(dev, r, sout + j * nb, j * s.nbytes + lo, nb)
     _finish(r)
+    return True
 
 
-def _dev_reduce_scatter(dev: _DeviceSide, s: _Buf, r: _Buf, n: int, op: int):
-    dev.agree(s, r)
+def _dev_reduce_scatter(dev: _DeviceSide, s: _Buf, r: _Buf, n: int, op: int, allow_host: bool = False) -> bool:
+    if dev.agree(s, r, allow_host):
+        return False      # every member holds a small host buffer: the caller uses the host plane
     from ..ops import collectives as CO
     sin, sout, _, cap = _DeviceSide.STAGE
     es = s.itemsize
@@ -915,11 +930,13 @@ def _dev_reduce_scatter(dev: _DeviceSide, s: _Buf, r: _Buf, n: int, op: int):
             CO.reduce_scatter(dev.comms, s.cc, op, sin, sout, 1, nb // es, 0, 0, use_mc=dev.has_mc)
             _stage_out(dev, r, sout, lo, nb)
     _finish(r)
+    return True
 
 
-def _dev_allgather_rows(dev: _DeviceSide, s: _Buf, r: _Buf, n: int, rows: int, row_bytes: int):
+def _dev_allgather_rows(dev: _DeviceSide, s: _Buf, r: _Buf, n: int, rows: int, row_bytes: int, allow_host: bool = False) -> bool:
     """Strided (last-axis) all-gather; row-chunked when it exceeds the staging arena."""
-    dev.agree(s, r)
+    if dev.agree(s, r, allow_host):
+        return False
     from ..ops import collectives as CO
     sin, sout, _, cap = _DeviceSide.STAGE
     if row_bytes * n > cap:
@@ -933,10 +950,12 @@ def _dev_allgather_rows(dev: _DeviceSide, s: _Buf, r: _Buf, n: int, rows: int, r
         CO.allgather(dev.comms, src, dst, nr, row_bytes, row_bytes, row_bytes * n, use_mc=dev.has_mc)
         _stage_out(dev, r, dst, r0 * row_bytes * n, nr * row_bytes * n)
     _finish(r)
+    return True
 
 
-def _dev_reduce_scatter_rows(dev: _DeviceSide, s: _Buf, r: _Buf, n: int, rows: int, pcols: int, op: int):
-    dev.agree(s, r)
+def _dev_reduce_scatter_rows(dev: _DeviceSide, s: _Buf, r: _Buf, n: int, rows: int, pcols: int, op: int, allow_host: bool = False) -> bool:
+    if dev.agree(s, r, allow_host):
+        return False
     from ..ops import collectives as CO
     sin, sout, _, cap = _DeviceSide.STAGE
     es = s.itemsize
@@ -952,6 +971,7 @@ def _dev_reduce_scatter_rows(dev: _DeviceSide, s: _Buf, r: _Buf, n: int, rows: i
         CO.reduce_scatter(dev.comms, s.cc, op, src, dst, nr, pcols, in_row, pcols * es, use_mc=dev.has_mc)
         _stage_out(dev, r, dst, r0 * pcols * es, nr * pcols * es)
     _finish(r)
+    return True
 
 
 def _stage_in_at(dev: _DeviceSide, b: _Buf, off: int, byte_lo: int, nbytes: int):
@@ -961,8 +981,9 @@ def _stage_in_at(dev: _DeviceSide, b: _Buf, off: int, byte_lo: int, nbytes: int)
     dev.heap.view(off, (nbytes,), torch.uint8).copy_(src)
 
 
-def _dev_alltoall(dev: _DeviceSide, s: _Buf, r: _Buf, n: int, staggered: bool = False):
-    dev.agree(s, r)
+def _dev_alltoall(dev: _DeviceSide, s: _Buf, r: _Buf, n: int, staggered: bool = False, allow_host: bool = False) -> bool:
+    if dev.agree(s, r, allow_host):
+        return False      # every member holds a small host buffer: the caller uses the host plane
     from ..ops import collectives as CO
     sin, sout, _, cap = _DeviceSide.STAGE
     seg = s.nbytes // n
@@ -981,6 +1002,7 @@ def _dev_alltoall(dev: _DeviceSide, s: _Buf, r: _Buf, n: int, staggered: bool = 
             for j in range(n):
                 _stage_out(dev, r, sout + j * nb, j * seg + lo, nb)
     _finish(r)
+    return True
 
 
 # ---------------------------------------------------------------------------------------------

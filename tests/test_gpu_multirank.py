@@ -8,6 +8,10 @@ from conftest import gpu_count, run_ranks
 
 pytestmark = pytest.mark.gpu
 
+# NumPy payloads below CCMPI_HOST_ROUTE_MAX would stay on the shared-memory plane (mpi/core.py:
+# _DeviceSide.agree); these tests are about the kernels, so the route is off unless a test says otherwise
+KERNELS = {"CCMPI_HOST_ROUTE_MAX": "0"}
+
 
 def _ok(proc, token):
     assert proc.returncode == 0, f"rc={proc.returncode}\n--- stdout\n{proc.stdout[-4000:]}\n--- stderr\n{proc.stderr[-3000:]}"
@@ -27,15 +31,22 @@ def _ranks_for_box(wanted):
 @pytest.mark.parametrize("cuda", [False, True])
 def test_collectives_on_device_plane(cuda):
     for n in _ranks_for_box([2, 4, 8]):
-        _ok(run_ranks(n, ["tests/workers/w_collectives.py"] + (["--cuda"] if cuda else []), transport="device"),
+        _ok(run_ranks(n, ["tests/workers/w_collectives.py"] + (["--cuda"] if cuda else []), transport="device", env=KERNELS),
             f"COLLECTIVES OK ranks={n} cuda={cuda}")
 
 
 @pytest.mark.parametrize("cuda", [False, True])
 def test_tp_steps_on_device_plane(cuda):
     for n in _ranks_for_box([4, 8]):
-        _ok(run_ranks(n, ["tests/workers/w_tp_steps.py"] + (["--cuda"] if cuda else []), transport="device"),
+        _ok(run_ranks(n, ["tests/workers/w_tp_steps.py"] + (["--cuda"] if cuda else []), transport="device", env=KERNELS),
             f"TP STEPS OK ranks={n} cuda={cuda}")
+
+
+def test_small_host_payloads_take_the_host_plane_by_default():
+    """Default routing on a device-plane job: same checks, tiny NumPy payloads over shared memory,
+    large ones and CUDA tensors through the kernels."""
+    for n in _ranks_for_box([2, 4, 8]):
+        _ok(run_ranks(n, ["tests/workers/w_collectives.py"], transport="device"), f"COLLECTIVES OK ranks={n} cuda=False")
 
 
 def test_single_rank_device_world():

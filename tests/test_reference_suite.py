@@ -21,9 +21,9 @@ PYTEST = ["-m", "pytest", "-l", "-q", "-p", "collective_communication_mpi_b200.p
           "--rootdir", "/tmp"]
 
 
-def _run(nranks, fname, transport, expect):
+def _run(nranks, fname, transport, expect, env=None):
     p = run_ranks(nranks, PYTEST + (["--with-mpi"] if nranks > 1 else []) + [os.path.join(REF_TESTS, fname)],
-                  transport=transport, env={"CCMPI_FORCE_SHIM": "1"})
+                  transport=transport, env={"CCMPI_FORCE_SHIM": "1", **(env or {})})
     assert p.returncode == 0, f"{fname} on {nranks} ranks ({transport})\n{p.stdout[-4000:]}\n{p.stderr[-2000:]}"
     assert expect in p.stdout, p.stdout[-2000:]
 
@@ -50,7 +50,10 @@ def test_reference_backward_file_on_4_ranks():
 
 # ---- the same files on the DEVICE plane: every collective they make is a CUDA kernel over NVLink ----
 # (int64 SUM all-reduce over mp_comm / dp_comm, fp64 last-axis gather and reduce-scatter through the
-# strided all-gather / reduce-scatter kernels; NumPy arrays are staged through the symmetric heap)
+# strided all-gather / reduce-scatter kernels; NumPy arrays are staged through the symmetric heap).
+# The tests' arrays are tiny; by default such host payloads would stay on the shared-memory plane
+# (mpi/core.py: _DeviceSide.agree), so the route is switched off here to keep the kernels under test.
+KERNELS = {"CCMPI_HOST_ROUTE_MAX": "0"}
 def _need_gpus(n):
     from conftest import gpu_count
     if gpu_count() < n:
@@ -60,22 +63,30 @@ def _need_gpus(n):
 @pytest.mark.gpu
 def test_reference_get_info_file_on_8_gpus_device_plane():
     _need_gpus(8)
-    _run(8, "test_get_info.py", "device", "2 passed")
+    _run(8, "test_get_info.py", "device", "2 passed", KERNELS)
 
 
 @pytest.mark.gpu
 def test_reference_forward_file_on_4_gpus_device_plane():
     _need_gpus(4)
-    _run(4, "test_transformer_forward.py", "device", "2 passed")
+    _run(4, "test_transformer_forward.py", "device", "2 passed", KERNELS)
 
 
 @pytest.mark.gpu
 def test_reference_backward_file_on_4_gpus_device_plane():
     _need_gpus(4)
-    _run(4, "test_transformer_backward.py", "device", "2 passed")
+    _run(4, "test_transformer_backward.py", "device", "2 passed", KERNELS)
 
 
 @pytest.mark.gpu
 def test_reference_forward_file_on_8_gpus_device_plane_with_empty_shards():
     _need_gpus(8)
-    _run(8, "test_transformer_forward.py", "device", "2 passed")
+    _run(8, "test_transformer_forward.py", "device", "2 passed", KERNELS)
+
+
+@pytest.mark.gpu
+def test_reference_files_on_the_device_plane_with_default_routing():
+    """As a user runs them: device transport up, tiny NumPy payloads routed to the host plane."""
+    _need_gpus(4)
+    _run(4, "test_transformer_forward.py", "device", "2 passed")
+    _run(4, "test_transformer_backward.py", "device", "2 passed")
