@@ -83,3 +83,80 @@ def test_rsn_tiles_flags_and_slots(n, M, chunk, BN):
             assert idx < m_blocks * per * n
             written[(owner, rank, m, nl)] = written.get((owner, rank, m, nl), 0) + 1
     assert set(written.values()) == {1} and len(written) == n * n * m_blocks * per
+
+
+# ---- RsNPolicy, round 2: peers' tiles first, own tiles last and reduced in their own epilogue -----
+def rsn2_tile(t, rank, n, mb, per):
+    """csrc/fused_policies.cuh: RsNPolicy::tile"""
+    remote = (n - 1) * mb * per
+    if t < remote:
+        g, in_g = t % (n - 1), t // (n - 1)
+        owner = (rank + 1 + g) % n
+    else:
+        owner, in_g = rank, t - remote
+    m, nl = raster(in_g, mb, per)
+    return m, nl + owner * per
+
+
+@pytest.mark.parametrize("n,M,chunk,BN", [(2, 256, 256, 256), (2, 8192, 2048, 256), (4, 384, 128, 128), (8, 8192, 1024, 256),
+                                          (4, 8192, 512, 256)])
+def test_rsn_v2_own_tiles_come_last_and_never_wait_on_a_waiting_tile(n, M, chunk, BN):
+    m_blocks = -(-M // BM)
+    m_pairs = (m_blocks + 1) // 2
+    per = chunk // BN
+    remote = (n - 1) * m_pairs * per
+    when = {}                                            # (rank, pair-row, n-block) -> position in the rank's schedule
+    for rank in range(n):
+        sched = [rsn2_tile(t, rank, n, m_pairs, per) for t in range(m_pairs * per * n)]
+        assert sorted(sched) == sorted(itertools.product(range(m_pairs), range(per * n))), "every tile exactly once"
+        owners = [nb // per for _, nb in sched]
+        assert all(o != rank for o in owners[:remote]) and all(o == rank for o in owners[remote:])
+        # peers are served round-robin, the next rank first: NVLink traffic is spread over the whole remote phase
+        assert owners[:n - 1] == [(rank + 1 + g) % n for g in range(n - 1)]
+        for pos, tile in enumerate(sched):
+            when[(rank, *tile)] = pos
+    # An own tile waits for the partials the peers push from THEIR remote phase, and remote tiles wait for
+    # nothing: no cycle of waits exists whatever the CTAs' relative progress. In tile units the partial is
+    # also produced no later than it is consumed (mirrored order), so own epilogues rarely wait at all.
+    for rank in range(n):
+        for m in range(m_pairs):
+            for nl in range(per):
+                own_pos = when[(rank, m, rank * per + nl)]
+                assert own_pos >= remote
+                for peer in range(n):
+                    if peer != rank:
+                        assert when[(peer, m, rank * per + nl)] < remote
+                        assert when[(peer, m, rank * per + nl)] <= own_pos
+
+
+@pytest.mark.parametrize("n", [2, 3, 4, 8])
+def test_rsn_v2_own_epilogue_adds_the_peers_slots_in_rank_order(n):
+    """RsNPolicy::own_load: pseudo-source k -> slot of rank (k < rank ? k : k + 1), then the residual."""
+    for rank in range(n):
+        srcs = [k if k < rank else k + 1 for k in range(n - 1)]
+        assert srcs == [s for s in range(n) if s != rank]            # rank order, own partial excluded
+    # the sum a rank forms: slots below it, its own accumulator, slots above it (np.sum(axis=0) order of
+    # func_impl.py:186 is 0..n-1; the own partial is rounded to the slot type first, so the result is the
+    # same bits as summing n slots)
+
+
+# ---- AgKPolicy, round 2: the producer asks once per (tile, K-chunk) ---------------------------------
+def agk_kchunk(ci, rank, n, chunk):
+    """csrc/fused_policies.cuh: AgKPolicy::kchunk -> (source rank, first K of the chunk, reads the local shard?)"""
+    src = rank + ci
+    if src >= n:
+        src -= n
+    return src, src * chunk, src == rank
+
+
+@pytest.mark.parametrize("n,K", [(2, 512), (4, 1024), (8, 8192)])
+def test_agk_kchunk_form_visits_the_same_blocks_as_the_per_block_form(n, K):
+    chunk = K // n
+    per = chunk // BK
+    for rank in range(n):
+        by_chunk = []
+        for ci in range(n):
+            src, k_base, local = agk_kchunk(ci, rank, n, chunk)
+            assert local == (ci == 0), "only the first chunk is this rank's own shard: no flag wait before it"
+            by_chunk += [(src, k_base + j * BK) for j in range(per)]
+        assert by_chunk == [agk_kblock(it, rank, n, chunk) for it in range(K // BK)]
