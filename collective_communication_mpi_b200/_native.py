@@ -232,6 +232,7 @@ def _declare_host(lib):
         "ccmpi_host_test": (i, [i64, i64]),
         "ccmpi_host_waitall": (i, [i64, P(C.c_int64), i]),
         "ccmpi_host_probe": (i64, [i64, i]),
+        "ccmpi_host_iprobe": (i, [i64, i, P(C.c_int), P(C.c_int), P(C.c_int64)]),
         "ccmpi_host_reserve_comm_ids": (i, [i64, i]),
         "ccmpi_host_ack_post": (i, [i64, i]),
         "ccmpi_host_ack_count": (i64, [i64, i]),

@@ -21,6 +21,7 @@ from __future__ import annotations
 import ctypes as C
 import os
 import pickle
+import time
 from typing import List, Optional, Sequence
 
 import numpy as np
@@ -141,12 +142,45 @@ class _Buf:
         return self.flat.data_ptr() if self.cuda else self.flat.ctypes.data
 
 
+class Status:
+    """``MPI.Status``: who sent the message a receive or probe matched, with which tag, how large."""
+
+    def __init__(self):
+        self.source, self.tag, self.nbytes, self.error = ANY_SOURCE, ANY_TAG, 0, 0
+
+    def Get_source(self) -> int:
+        return self.source
+
+    def Get_tag(self) -> int:
+        return self.tag
+
+    def Get_error(self) -> int:
+        return self.error
+
+    def Get_count(self, datatype: "Datatype" = None) -> int:
+        size = datatype.Get_size() if datatype is not None else 1
+        return self.nbytes // size if size else 0
+
+    def Get_elements(self, datatype: "Datatype" = None) -> int:
+        return self.Get_count(datatype)
+
+    count = property(lambda self: self.nbytes)
+
+    def _set(self, source: int, tag: int, nbytes: int):
+        self.source, self.tag, self.nbytes = source, tag, int(nbytes)
+
+
 class Request:
     """Handle of a non-blocking operation (``Isend`` / ``Irecv``)."""
 
-    def __init__(self, world: Optional[World] = None, rid: int = -1, keep=None, on_done=None):
+    def __init__(self, world: Optional[World] = None, rid: int = -1, keep=None, on_done=None, info=None):
         self._world, self._rid, self._keep, self._on_done = world, rid, keep, on_done
         self._done = rid < 0
+        self._info = info      # (group rank of the source, tag, bytes) of a receive, for MPI.Status
+
+    def _fill(self, status):
+        if status is not None and self._info is not None:
+            status._set(*self._info)
 
     def _finish(self):
         if not self._done:
@@ -160,6 +194,7 @@ class Request:
             arr = (C.c_int64 * 1)(self._rid)
             N.check_host(self._world._hostlib.ccmpi_host_waitall(self._world.host, arr, 1), "Wait")
             self._finish()
+        self._fill(status)
         return True
 
     wait = Wait
@@ -170,6 +205,8 @@ class Request:
         rc = N.check_host(self._world._hostlib.ccmpi_host_test(self._world.host, self._rid), "Test")
         if rc == 1:
             self._finish()
+        if self._done:
+            self._fill(status)
         return self._done
 
     test = Test
@@ -184,6 +221,10 @@ class Request:
             N.check_host(w._hostlib.ccmpi_host_waitall(w.host, arr, len(pend)), "Waitall")
             for r in pend:
                 r._finish()
+        if statuses is not None:
+            for r, st in zip(requests, statuses):
+                if r is not None:
+                    r._fill(st)
         return True
 
     waitall = Waitall
@@ -558,9 +599,14 @@ class Comm:
         return Request(w, rid, keep=(host, b))
 
     def Irecv(self, buf, source: int = ANY_SOURCE, tag: int = ANY_TAG) -> Request:
-        if source == ANY_SOURCE:
-            raise NotImplementedError("Irecv from ANY_SOURCE")
+        """``MPI_Irecv``. With ``ANY_SOURCE`` the call first waits until some member has a message for this
+        communicator (and tag) at the head of its ring, then posts the receive from that member: matching is
+        decided when the receive is POSTED, not when it completes, and messages of one pair stay FIFO."""
         b = _Buf(buf, True)
+        if source == ANY_SOURCE:
+            source, mtag, _ = self._match(ANY_SOURCE, tag, block=True)
+            if tag == ANY_TAG:
+                tag = mtag
         w = self._world
         if b.cuda and P2P.enabled() and w.device_available():
             # room for a whole payload (a NumPy sender uses the host path), but only the descriptor-sized
@@ -583,19 +629,84 @@ class Comm:
             host, done = b.flat.view(np.uint8) if b.flat.dtype != np.uint8 else b.flat, None
         rid = w._hostlib.ccmpi_host_irecv(w.host, self._peer(source), self._cid, int(tag), host.ctypes.data, host.nbytes)
         N.check_host(rid, "Irecv")
-        return Request(w, rid, keep=(host, b), on_done=done)
+        return Request(w, rid, keep=(host, b), on_done=done, info=(source, int(tag), b.nbytes))
 
     def Send(self, buf, dest: int, tag: int = 0):
         self.Isend(buf, dest, tag).Wait()
 
     def Recv(self, buf, source: int = ANY_SOURCE, tag: int = ANY_TAG, status=None):
+        if status is not None:
+            # the header tells the actual source, tag and size (a message may be shorter than the buffer, as
+            # in MPI). On the NVLink route the ring carries a fixed-size descriptor, not the payload: there
+            # the count reported is the receive buffer's.
+            source, mtag, nbytes = self._match(source, tag, block=True)
+            req = self.Irecv(buf, source, mtag)
+            if nbytes == P2P.DESC_BYTES and req._info[2] != nbytes and P2P.enabled() and self._world.device_available():
+                nbytes = req._info[2]
+            req._info = (source, mtag, nbytes)
+            req.Wait(status)
+            return
         self.Irecv(buf, source, tag).Wait()
 
     def Sendrecv(self, sendbuf, dest: int, sendtag: int = 0, recvbuf=None, source: int = ANY_SOURCE,
                  recvtag: int = ANY_TAG, status=None):
-        rr = self.Irecv(recvbuf, source, recvtag)
-        rs = self.Isend(sendbuf, dest, sendtag)
+        if source == ANY_SOURCE:
+            # the send goes first: matching ANY_SOURCE waits for an incoming header, and the peer may be
+            # waiting for ours in the same way
+            rs = self.Isend(sendbuf, dest, sendtag)
+            rr = self.Irecv(recvbuf, source, recvtag)
+        else:
+            rr = self.Irecv(recvbuf, source, recvtag)
+            rs = self.Isend(sendbuf, dest, sendtag)
         Request.Waitall([rr, rs])
+        rr._fill(status)
+
+    # ---- probing ---------------------------------------------------------------------------
+    def _match(self, source: int, tag: int, block: bool):
+        """``(group rank, tag, bytes)`` of the next message for this communicator from ``source`` (or from
+        whichever member has one first), or ``None`` when ``block`` is false and nothing is there. Only the
+        HEAD of each pair's ring is looked at (strict FIFO per pair): a head message of another
+        communicator or tag is not skipped, exactly like a posted receive would not skip it."""
+        w = self._world
+        lib, h = w._hostlib, w.host
+        cid, mtag, nbytes = C.c_int(), C.c_int(), C.c_int64()
+        if source == ANY_SOURCE:
+            peers = [r for r in range(len(self._members)) if r != self._me]
+        else:
+            peers = [source]
+            self._peer(source)
+        if not peers:
+            raise ValueError("no other member to receive from")
+        t0, spins = time.monotonic(), 0
+        while True:
+            for r in peers:
+                rc = N.check_host(lib.ccmpi_host_iprobe(h, self._members[r], C.byref(cid), C.byref(mtag), C.byref(nbytes)),
+                                  "probe")
+                if rc == 1 and cid.value == self._cid and (tag == ANY_TAG or mtag.value == tag):
+                    return r, mtag.value, nbytes.value
+            if not block:
+                return None
+            spins += 1
+            if spins > 50:
+                time.sleep(0)          # let the senders run when ranks outnumber cores
+                if spins % 1000 == 0 and time.monotonic() - t0 > w.timeout_s:
+                    raise TimeoutError(f"no matching message within {w.timeout_s:.0f} s (source {source}, tag {tag})")
+
+    def Probe(self, source: int = ANY_SOURCE, tag: int = ANY_TAG, status=None) -> bool:
+        """``MPI_Probe``: wait until a matching message can be received; describes it in ``status``."""
+        m = self._match(source, tag, block=True)
+        if status is not None:
+            status._set(*m)
+        return True
+
+    def Iprobe(self, source: int = ANY_SOURCE, tag: int = ANY_TAG, status=None) -> bool:
+        """``MPI_Iprobe``: is a matching message ready to be received right now?"""
+        m = self._match(source, tag, block=False)
+        if m is not None and status is not None:
+            status._set(*m)
+        return m is not None
+
+    probe, iprobe = Probe, Iprobe
 
     # ---- object (pickle) API -------------------------------------------------------------
     def allgather(self, sendobj):
@@ -762,10 +873,11 @@ class Comm:
         self.Send(blob, dest, tag)
 
     def recv(self, buf=None, source: int = ANY_SOURCE, tag: int = ANY_TAG, status=None):
-        w = self._world
-        nbytes = N.check_host(w._hostlib.ccmpi_host_probe(w.host, self._peer(source)), "recv(probe)")
+        source, mtag, nbytes = self._match(source, tag, block=True)
         blob = np.empty(int(nbytes), dtype=np.uint8)
-        self.Recv(blob, source, tag)
+        self.Irecv(blob, source, mtag).Wait()
+        if status is not None:
+            status._set(source, mtag, nbytes)
         return pickle.loads(blob.tobytes())
 
 

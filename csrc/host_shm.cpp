@@ -683,6 +683,29 @@ extern "C" int64_t ccmpi_host_ack_count(int64_t h, int dst) {
     return (int64_t)H->ring(H->rank, dst).acked.load(std::memory_order_acquire);
 }
 
+// Non-blocking look at the next message queued from `src`: 1 and its header fields when a whole header
+// is at the head of the ring and no posted receive is ahead of it, 0 otherwise. What MPI_Iprobe and
+// receives from MPI_ANY_SOURCE are built from (mpi/core.py); ordering per pair stays strict FIFO.
+extern "C" int ccmpi_host_iprobe(int64_t h, int src, int* comm_id, int* tag, int64_t* bytes) {
+    Handle* H = get(h);
+    if (!H) { set_error("bad host transport handle"); return -2; }
+    if (src < 0 || src >= H->nranks || src == H->rank) { set_error("iprobe: bad source %d", src); return -2; }
+    if (H->hdr->failed.load(std::memory_order_relaxed)) { set_error("a peer rank failed"); return -4; }
+    progress_all(H);
+    if (!H->recvq[src].empty()) return 0;
+    RingCtl& rc = H->ring(src, H->rank);
+    const uint64_t tail = rc.tail.load(std::memory_order_relaxed);
+    const uint64_t head = rc.head.load(std::memory_order_acquire);
+    if (head - tail < sizeof(MsgHdr)) return 0;
+    MsgHdr m;
+    ring_get(H->rdata(src, H->rank), H->ring_bytes, tail, (char*)&m, sizeof(m));
+    if (m.check != (MAGIC ^ m.bytes)) { set_error("iprobe: corrupt message header from rank %d", src); return -2; }
+    if (comm_id) *comm_id = m.comm_id;
+    if (tag) *tag = m.tag;
+    if (bytes) *bytes = (int64_t)m.bytes;
+    return 1;
+}
+
 extern "C" int64_t ccmpi_host_probe(int64_t h, int src) {
     Handle* H = get(h);
     if (!H) { set_error("bad host transport handle"); return -2; }

@@ -53,6 +53,9 @@ int ccmpi_host_test(int64_t h, int64_t req);              /* 1 done, 0 pending, 
 int ccmpi_host_waitall(int64_t h, const int64_t* reqs, int n);
 /* size of the next message queued from `src` (blocks until a header is there) */
 int64_t ccmpi_host_probe(int64_t h, int src);
+/* non-blocking: 1 and the header fields of the next message queued from `src`, 0 when none is there
+ * (or a posted receive is ahead of it), <0 on error */
+int ccmpi_host_iprobe(int64_t h, int src, int* comm_id, int* tag, int64_t* bytes);
 
 /* Reserve `count` consecutive communicator ids from the job-wide counter in the segment; returns the
  * first one (>= 1; 0 is the world) or <0. One member of the parent calls this and tells the others. */

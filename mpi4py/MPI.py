@@ -7,7 +7,7 @@ is created on first access so that merely importing this module starts nothing.
 from collective_communication_mpi_b200.mpi.core import (  # noqa: F401
     ANY_SOURCE, ANY_TAG, BYTE, CHAR, DOUBLE, FLOAT, IN_PLACE, INT, INT32_T, INT64_T, LAND, LONG, LOR, MAX, MIN,
     PROC_NULL, PROD, SUM, UNDEFINED, Comm, Datatype, Finalize, Get_processor_name, Is_finalized, Is_initialized,
-    Op, Request, Wtime, comm_world,
+    Op, Request, Status, Wtime, comm_world,
 )
 
 Intracomm = Comm

@@ -176,3 +176,9 @@ def test_blocks_can_be_given_another_token_count(flags):
     """``set_tokens``: fused ops closed and rebuilt, weights kept, results still those of the dense model."""
     sp, meg = int("--sp" in flags), int("--megatron" in flags)
     _ok(run_ranks(2, ["tests/workers/w_set_tokens.py", "2"] + flags, timeout=240), f"SET TOKENS OK mp=2 sp={sp} megatron={meg}")
+
+
+@pytest.mark.parametrize("n", [3, 8])
+def test_status_probe_and_any_source(n):
+    """mpi4py's ``Status`` / ``Probe`` / ``Iprobe`` / ``ANY_SOURCE`` on the host plane (master/worker pattern)."""
+    _ok(run_ranks(n, ["tests/workers/w_probe_status.py"], timeout=120), f"PROBE STATUS OK ranks={n}")
