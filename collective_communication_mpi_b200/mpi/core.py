@@ -517,8 +517,108 @@ class Comm:
 
     def Reduce_scatter(self, sendbuf, recvbuf, recvcounts=None, op: Op = SUM):
         if recvcounts is not None and len(set(recvcounts)) > 1:
-            raise NotImplementedError("Reduce_scatter with unequal recvcounts")
+            # unequal blocks: reduce the whole vector, keep this rank's segment
+            self._check_op(op)
+            s = _Buf(sendbuf, False)
+            counts = [int(c) for c in recvcounts]
+            if len(counts) != len(self._members) or sum(counts) != s.count:
+                raise ValueError(f"Reduce_scatter: recvcounts {counts} do not add up to the send count {s.count}")
+            whole = _scratch(s, s.count)
+            self.Allreduce(sendbuf, whole, op)
+            lo = sum(counts[:self._me])
+            _copy(_Buf(recvbuf, True), _Buf(whole[lo:lo + counts[self._me]], False))
+            return
         return self.Reduce_scatter_block(sendbuf, recvbuf, op)
+
+    # ---- "v" collectives: blocks of different sizes ----------------------------------------------
+    # Built on the equal-block collectives by padding every block to the largest one: what the
+    # reference's own Alltoall asserts away (comm.py:44-49, "must be divisible") and what ragged shards
+    # need. One collective of n * max(counts) elements instead of n point-to-point rounds.
+    def Allgatherv(self, sendbuf, recvbuf):
+        """``recvbuf``: ``[buf, counts]``, ``[buf, counts, displs]`` (+ optional datatype), counts / displs in
+        elements. Rank j contributes ``counts[j]`` elements, stored at ``displs[j]`` (default: back to back)."""
+        n = len(self._members)
+        s = _Buf(_vbuf(sendbuf), False)
+        rb, counts, displs = _vspec(recvbuf, n)
+        r = _Buf(rb, True)
+        if counts is None:
+            counts = [s.count] * n
+            displs = [j * s.count for j in range(n)]
+        if s.count != counts[self._me]:
+            raise ValueError(f"Allgatherv: this rank sends {s.count} elements, recvcounts says {counts[self._me]}")
+        if max(d + c for d, c in zip(displs, counts)) > r.count:
+            raise ValueError("Allgatherv: receive buffer too small for counts / displacements")
+        m = max(counts)
+        if m == 0:
+            return
+        pad = _scratch(r, m)
+        pad[:s.count] = _convert(s.flat, r)
+        tmp = _scratch(r, n * m)
+        self.Allgather(pad, tmp)
+        for j in range(n):
+            r.flat[displs[j]:displs[j] + counts[j]] = tmp[j * m:j * m + counts[j]]
+
+    def Gatherv(self, sendbuf, recvbuf, root: int = 0):
+        """Like ``Allgatherv``; only the root's ``recvbuf`` is written (the others pass ``None``). Every rank
+        needs the counts, so the root's are broadcast first."""
+        n = len(self._members)
+        s = _Buf(_vbuf(sendbuf), False)
+        spec = None
+        if self._me == root:
+            rb, counts, displs = _vspec(recvbuf, n)
+            if counts is None:
+                raise ValueError("Gatherv: the root passes [recvbuf, counts] (or [recvbuf, counts, displs])")
+            spec = (counts, displs)
+        counts, displs = self.bcast(spec, root)
+        if self._me == root:
+            self.Allgatherv(sendbuf, [rb, counts, displs])
+        else:
+            packed = [sum(counts[:j]) for j in range(n)]
+            self.Allgatherv(sendbuf, [_scratch(s, sum(counts)), counts, packed])
+
+    def Scatterv(self, sendbuf, recvbuf, root: int = 0):
+        """``sendbuf`` on the root: ``[buf, counts]`` / ``[buf, counts, displs]``; block j goes to rank j."""
+        n = len(self._members)
+        r = _Buf(recvbuf, True)
+        spec = None
+        if self._me == root:
+            sb, counts, displs = _vspec(sendbuf, n)
+            if counts is None:
+                raise ValueError("Scatterv: the root passes [sendbuf, counts] (or [sendbuf, counts, displs])")
+            spec = (counts, displs)
+        counts, displs = self.bcast(spec, root)
+        if r.count < counts[self._me]:
+            raise ValueError(f"Scatterv: receive buffer holds {r.count} elements, this rank is sent {counts[self._me]}")
+        m = max(counts)
+        if m == 0:
+            return
+        packed = _scratch(r, n * m)
+        if self._me == root:
+            s = _Buf(sb, False)
+            for j in range(n):
+                packed[j * m:j * m + counts[j]] = _convert(s.flat[displs[j]:displs[j] + counts[j]], r)
+        mine = _scratch(r, m)
+        self.Scatter(packed, mine, root)
+        r.flat[:counts[self._me]] = mine[:counts[self._me]]
+
+    def Alltoallv(self, sendbuf, recvbuf):
+        """``[buf, counts, displs]`` on both sides: block j of ``sendbuf`` goes to rank j, block i of
+        ``recvbuf`` comes from rank i."""
+        n = len(self._members)
+        sb, scounts, sdispls = _vspec(sendbuf, n)
+        rb, rcounts, rdispls = _vspec(recvbuf, n)
+        if scounts is None or rcounts is None:
+            raise ValueError("Alltoallv: pass [buf, counts] (or [buf, counts, displs]) for both buffers")
+        s, r = _Buf(sb, False), _Buf(rb, True)
+        m = int(self.allreduce(max(max(scounts), max(rcounts)), MAX))
+        if m == 0:
+            return
+        out, inn = _scratch(r, n * m), _scratch(r, n * m)
+        for j in range(n):
+            out[j * m:j * m + scounts[j]] = _convert(s.flat[sdispls[j]:sdispls[j] + scounts[j]], r)
+        self.Alltoall(out, inn)
+        for j in range(n):
+            r.flat[rdispls[j]:rdispls[j] + rcounts[j]] = inn[j * m:j * m + rcounts[j]]
 
     def Alltoall(self, sendbuf, recvbuf):
         s, r = _Buf(sendbuf, False), _Buf(recvbuf, True)
@@ -906,6 +1006,55 @@ def _empty_like_flat(b: _Buf, count: int):
     """Scratch with ``count`` elements of ``b``'s element type on ``b``'s device (torch buffers)."""
     import torch
     return torch.empty(count, dtype=b.flat.dtype, device=b.flat.device)
+
+
+def _scratch(b: _Buf, count: int):
+    """``count`` elements of ``b``'s element type where ``b`` lives (NumPy array or CUDA tensor)."""
+    if b.cuda:
+        return _empty_like_flat(b, count)
+    return np.empty(count, dtype=b.flat.dtype)
+
+
+def _convert(flat, like: _Buf):
+    """``flat`` (a NumPy array or a CUDA tensor) as something assignable into a slice of ``like``'s kind."""
+    if like.cuda and isinstance(flat, np.ndarray):
+        import torch
+        return torch.from_numpy(np.ascontiguousarray(flat)).to(like.flat.device)
+    if not like.cuda and not isinstance(flat, np.ndarray):
+        return flat.cpu().numpy()
+    return flat
+
+
+def _vbuf(spec):
+    """The buffer of a send spec that may be written ``[buf, count, datatype]``."""
+    if isinstance(spec, (list, tuple)) and spec and not np.isscalar(spec[0]) and not isinstance(spec[0], (list, tuple)) \
+            and any(isinstance(x, (int, Datatype)) or x is None for x in spec[1:]) and len(spec) <= 3:
+        return spec[0]
+    return spec
+
+
+def _vspec(spec, n: int):
+    """``(buffer, counts, displs)`` of a "v" buffer spec: ``buf``, ``[buf, counts]``, ``[buf, counts, displs]``,
+    ``[buf, (counts, displs)]``, each optionally followed by a datatype. Counts and displacements are in
+    elements; missing displacements pack the blocks back to back."""
+    if not isinstance(spec, (list, tuple)) or not spec or np.isscalar(spec[0]):
+        return spec, None, None
+    items = [x for x in spec[1:] if not isinstance(x, Datatype)]
+    buf = spec[0]
+    if not items or items[0] is None:
+        return buf, None, None
+    counts, displs = items[0], (items[1] if len(items) > 1 else None)
+    if isinstance(counts, (list, tuple)) and len(counts) == 2 and isinstance(counts[0], (list, tuple, np.ndarray)):
+        counts, displs = counts
+    counts = [int(c) for c in counts]
+    if len(counts) != n:
+        raise ValueError(f"{len(counts)} counts for a communicator of size {n}")
+    if displs is None:
+        displs = [sum(counts[:j]) for j in range(n)]
+    displs = [int(d) for d in displs]
+    if len(displs) != n or min(counts) < 0 or min(displs) < 0:
+        raise ValueError("counts and displacements must be non-negative, one per rank")
+    return buf, counts, displs
 
 
 def _np_dtype_of(b: _Buf):

@@ -182,3 +182,9 @@ def test_blocks_can_be_given_another_token_count(flags):
 def test_status_probe_and_any_source(n):
     """mpi4py's ``Status`` / ``Probe`` / ``Iprobe`` / ``ANY_SOURCE`` on the host plane (master/worker pattern)."""
     _ok(run_ranks(n, ["tests/workers/w_probe_status.py"], timeout=120), f"PROBE STATUS OK ranks={n}")
+
+
+@pytest.mark.parametrize("n,flags", [(4, []), (8, []), (3, ["--torch"])])
+def test_v_collectives_with_ragged_blocks(n, flags):
+    """``Allgatherv`` / ``Gatherv`` / ``Scatterv`` / ``Alltoallv`` / ``Reduce_scatter(recvcounts=...)``."""
+    _ok(run_ranks(n, ["tests/workers/w_vcollectives.py"] + flags, timeout=120), f"V COLLECTIVES OK ranks={n} torch={int(bool(flags))}")
