@@ -487,7 +487,11 @@ class Comm:
         r = _Buf(recvbuf, True)
         n = len(self._members)
         if sendbuf is IN_PLACE:
-            raise NotImplementedError("Allgather with IN_PLACE")
+            # this rank's contribution already sits in its block of recvbuf; it travels from a copy, because the
+            # collective writes recvbuf while peers may still be reading the block
+            per = r.count // n
+            mine = r.flat[self._me * per:(self._me + 1) * per]
+            sendbuf = mine.clone() if r.cuda else np.array(mine, copy=True)
         s = _Buf(sendbuf, False)
         if r.nbytes != s.nbytes * n:
             raise ValueError(f"Allgather: recv buffer holds {r.nbytes} B, expected {n} x {s.nbytes} B")

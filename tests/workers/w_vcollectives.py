@@ -74,6 +74,16 @@ world.Reduce_scatter(mk(vec), seg, recvcounts=counts)
 lo = sum(counts[:rank])
 assert np.array_equal(host(seg), np.arange(total)[lo:lo + counts[rank]] * (n * (n + 1) // 2))
 
+# MPI.IN_PLACE: the contribution already sits in the receive buffer
+buf = np.full(3 * n, -1, dtype=np.int64)
+buf[3 * rank:3 * rank + 3] = rank
+bufm = mk(buf)
+world.Allgather(MPI.IN_PLACE, bufm)
+assert np.array_equal(host(bufm), np.repeat(np.arange(n), 3))
+acc = mk(np.arange(5, dtype=np.float64) + rank)
+world.Allreduce(MPI.IN_PLACE, acc)
+assert np.allclose(host(acc), n * np.arange(5) + n * (n - 1) / 2)
+
 # errors are raised on every rank before any traffic
 try:
     world.Allgatherv(mk(block(rank)), [mk(np.empty(total)), counts[:-1]])
