@@ -95,7 +95,8 @@ def host_lib():
         if _host is not None:
             return _host
         _ensure_built()
-        path = _build.HOST_LIB
+        # CCMPI_HOST_LIB: another build of the same sources, e.g. the AddressSanitizer one of scripts/sanitize_host.sh
+        path = os.environ.get("CCMPI_HOST_LIB") or _build.HOST_LIB
         if not Path(path).exists():
             raise NativeError(f"{path} is missing; run `python -m collective_communication_mpi_b200.build`")
         lib = C.CDLL(str(path))
