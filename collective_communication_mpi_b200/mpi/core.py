@@ -230,6 +230,36 @@ class Request:
     waitall = Waitall
 
 
+class _ObjRecv:
+    """Request of ``Comm.irecv``: a pickled object whose size the receiver learns from the message header."""
+
+    def __init__(self, comm, source: int, tag: int):
+        self._comm, self._source, self._tag, self._obj, self._done = comm, source, tag, None, False
+
+    def _take(self, m, status):
+        src, mtag, nbytes = m
+        blob = np.empty(int(nbytes), dtype=np.uint8)
+        self._comm.Irecv(blob, src, mtag).Wait()
+        self._obj, self._done = pickle.loads(blob.tobytes()), True
+        if status is not None:
+            status._set(src, mtag, nbytes)
+
+    def wait(self, status=None):
+        if not self._done:
+            self._take(self._comm._match(self._source, self._tag, block=True), status)
+        return self._obj
+
+    def test(self, status=None):
+        if not self._done:
+            m = self._comm._match(self._source, self._tag, block=False)
+            if m is None:
+                return False, None
+            self._take(m, status)
+        return True, self._obj
+
+    Wait, Test = wait, test
+
+
 class _DeviceSide:
     """Per-communicator device state: the ``ccmpi_dev_comm`` plus the world's staging arena."""
 
@@ -955,12 +985,84 @@ class Comm:
         rows = self.bcast(sendobj, root)
         return rows[self._me]
 
-    def allreduce(self, sendobj, op: Op = SUM):
-        vals = self.allgather(sendobj)
+    @staticmethod
+    def _fold(vals, op: Op):
+        """Rank-ordered fold of Python objects (the order of the reference's root loop, comm.py:85-93)."""
         acc = vals[0]
         for v in vals[1:]:
-            acc = acc + v if op == SUM else (min(acc, v) if op == MIN else (max(acc, v) if op == MAX else acc * v))
+            if op == SUM:
+                acc = acc + v
+            elif op == MIN:
+                acc = min(acc, v)
+            elif op == MAX:
+                acc = max(acc, v)
+            elif op == PROD:
+                acc = acc * v
+            elif op == LAND:
+                acc = bool(acc) and bool(v)
+            elif op == LOR:
+                acc = bool(acc) or bool(v)
+            else:
+                raise NotImplementedError(f"object reduction with {op}")
         return acc
+
+    def allreduce(self, sendobj, op: Op = SUM):
+        return self._fold(self.allgather(sendobj), op)
+
+    def reduce(self, sendobj, op: Op = SUM, root: int = 0):
+        out = self._fold(self.allgather(sendobj), op)
+        return out if self._me == root else None
+
+    def scan(self, sendobj, op: Op = SUM):
+        """Inclusive prefix reduction over the ranks 0..me."""
+        return self._fold(self.allgather(sendobj)[:self._me + 1], op)
+
+    def exscan(self, sendobj, op: Op = SUM):
+        """Exclusive prefix reduction over the ranks 0..me-1 (``None`` on rank 0, as in mpi4py)."""
+        vals = self.allgather(sendobj)          # collective: rank 0 takes part although it keeps nothing
+        return self._fold(vals[:self._me], op) if self._me else None
+
+    def Scan(self, sendbuf, recvbuf, op: Op = SUM):
+        """``MPI_Scan`` on buffers: an all-gather of the inputs, then each rank folds its prefix locally --
+        one collective, and the same rank order of additions on every rank."""
+        self._prefix(sendbuf, recvbuf, op, inclusive=True)
+
+    def Exscan(self, sendbuf, recvbuf, op: Op = SUM):
+        """``MPI_Exscan``: rank 0's ``recvbuf`` is left untouched."""
+        self._prefix(sendbuf, recvbuf, op, inclusive=False)
+
+    def _prefix(self, sendbuf, recvbuf, op: Op, inclusive: bool):
+        self._check_op(op)
+        r = _Buf(recvbuf, True)
+        s = r if sendbuf is IN_PLACE else _Buf(sendbuf, False)
+        if s.count != r.count:
+            raise ValueError(f"Scan: send count {s.count} != recv count {r.count}")
+        n = len(self._members)
+        mine = s.flat.clone() if s.cuda else np.array(s.flat, copy=True)
+        allv = _scratch(s, n * s.count)
+        self.Allgather(mine, allv)
+        hi = self._me + 1 if inclusive else self._me
+        if hi == 0:
+            return
+        rows = allv.reshape(n, s.count)[:hi]
+        if s.cuda:
+            acc = rows.sum(0) if op == SUM else (rows.amin(0) if op == MIN else rows.amax(0))
+            r.flat.copy_(acc.to(r.flat.dtype))
+        else:
+            fold = np.add if op == SUM else (np.minimum if op == MIN else np.maximum)
+            acc = rows[0].copy()
+            for row in rows[1:]:
+                fold(acc, row, out=acc)
+            r.flat[:] = acc
+
+    def isend(self, obj, dest: int, tag: int = 0) -> Request:
+        blob = np.frombuffer(pickle.dumps(_to_wire(obj), protocol=pickle.HIGHEST_PROTOCOL), dtype=np.uint8)
+        return self.Isend(blob, dest, tag)
+
+    def irecv(self, buf=None, source: int = ANY_SOURCE, tag: int = ANY_TAG) -> "_ObjRecv":
+        """Object ``irecv``: ``req.wait()`` returns the object. The message is matched when ``wait`` /
+        ``test`` first finds it (its size is only known then)."""
+        return _ObjRecv(self, source, tag)
 
     def sendrecv(self, sendobj, dest: int, sendtag: int = 0, recvbuf=None, source: int = ANY_SOURCE,
                  recvtag: int = ANY_TAG, status=None):

@@ -95,5 +95,26 @@ if rank == 0:
 else:
     world.Send(np.full(2, rank * 10, dtype=np.int64), dest=0, tag=9)
 world.Barrier()
+
+# 6. prefix reductions and the remaining lowercase forms
+assert world.scan(rank + 1) == (rank + 1) * (rank + 2) // 2
+assert world.exscan(rank + 1) == (None if rank == 0 else rank * (rank + 1) // 2)
+assert world.reduce([rank], root=1) == (list(range(n)) if rank == 1 else None)         # SUM of lists: concatenation, rank order
+assert world.allreduce(rank % 2 == 0, MPI.LAND) is False and world.allreduce(rank == 1, MPI.LOR) is True
+x = np.arange(6, dtype=np.int64) + rank
+inc, exc = np.empty_like(x), np.full_like(x, -7)
+world.Scan(x, inc)
+world.Exscan(x, exc, op=MPI.MAX)
+assert np.array_equal(inc, (rank + 1) * np.arange(6) + rank * (rank + 1) // 2)
+assert np.array_equal(exc, np.full(6, -7) if rank == 0 else np.arange(6) + rank - 1)
+# object isend / irecv: the receiver learns the size from the header
+if rank == 0:
+    reqs = [world.irecv(source=j, tag=40 + j) for j in range(1, n)]
+    for j, rq in enumerate(reqs, 1):
+        st = MPI.Status()
+        assert rq.wait(st) == {"rank": j, "payload": "x" * (10 * j)} and st.Get_source() == j
+else:
+    world.isend({"rank": rank, "payload": "x" * (10 * rank)}, dest=0, tag=40 + rank).Wait()
+world.Barrier()
 if rank == 0:
     print(f"PROBE STATUS OK ranks={n}")
