@@ -90,3 +90,12 @@ def test_reference_files_on_the_device_plane_with_default_routing():
     _need_gpus(4)
     _run(4, "test_transformer_forward.py", "device", "2 passed")
     _run(4, "test_transformer_backward.py", "device", "2 passed")
+
+
+@pytest.mark.parametrize("n", [4, 8])
+def test_differential_against_the_unmodified_reference_modules(n):
+    """Reference ``Communicator`` / ``func_impl`` / ``split_data`` loaded from baseline/_ref and run side by side
+    with ours on the same communicators: equal results bit for bit, equal byte accounting (w_differential.py)."""
+    p = run_ranks(n, ["tests/workers/w_differential.py"], transport="host", timeout=240, env={"CCMPI_FORCE_SHIM": "1"})
+    assert p.returncode == 0, f"{p.stdout[-3000:]}\n{p.stderr[-3000:]}"
+    assert f"DIFFERENTIAL OK ranks={n}" in p.stdout
