@@ -99,3 +99,30 @@ def test_differential_against_the_unmodified_reference_modules(n):
     p = run_ranks(n, ["tests/workers/w_differential.py"], transport="host", timeout=240, env={"CCMPI_FORCE_SHIM": "1"})
     assert p.returncode == 0, f"{p.stdout[-3000:]}\n{p.stderr[-3000:]}"
     assert f"DIFFERENTIAL OK ranks={n}" in p.stdout
+
+
+CASES = [None, "allreduce", "myallreduce", "allgather", "reduce_scatter", "split", "alltoall", "myalltoall"]
+
+
+@pytest.mark.parametrize("case", CASES, ids=[c or "default" for c in CASES])
+def test_cli_prints_what_the_reference_cli_prints(case):
+    """``mpi-test.py`` of the reference and ours, 8 ranks each: the same lines once numbers are blanked (payloads are
+    random, times differ) and rank-prefixed lines are sorted (ranks print concurrently)."""
+    import re
+    ref_cli = os.path.join(os.path.dirname(REF_TESTS), "mpi-test.py")
+    if not os.path.isfile(ref_cli):
+        pytest.skip("reference mpi-test.py not present")
+    args = ["--test_case", case] if case else []
+
+    def shape(script):
+        p = run_ranks(8, [script] + args, transport="host", timeout=240, env={"CCMPI_FORCE_SHIM": "1"})
+        assert p.returncode == 0, f"{script}\n{p.stdout[-3000:]}\n{p.stderr[-3000:]}"
+        lines = [re.sub(r"-?\d+(\.\d+)?(e[-+]?\d+)?", "#", ln).strip() for ln in p.stdout.splitlines() if ln.strip()]
+        lines = [re.sub(r"\[\s+", "[", re.sub(r"\s+", " ", ln)) for ln in lines]      # numpy pads short numbers
+        return sorted(lines)
+
+    ours, theirs = shape("mpi-test.py"), shape(ref_cli)
+    # ours may add lines (e.g. the summary of --runs); every line the reference prints must be there, as often
+    from collections import Counter
+    missing = Counter(theirs) - Counter(ours)
+    assert not missing, f"lines of the reference's output that ours lacks: {dict(missing)}\nours: {ours}"
