@@ -152,3 +152,60 @@ def test_real_ops_share_the_life_cycle():
     for cls in (F.AllGatherGemm, F.GemmReduceScatter, F.GemmAllReduce, F.GemmAllGather, FS.AllGatherGemmM,
                 FS.GemmReduceScatterM, FS.AllGatherGemmAllGather, F8.AllGatherGemmMX, F8.GemmReduceScatterMX):
         assert issubclass(cls, F.FusedOp), cls
+
+
+# ---- the symmetric heap's allocator (runtime/symm.py): the same first-fit + coalescing policy, in bytes.
+# The object is built without its CUDA half (the allocator is pure bookkeeping; offsets must come out the
+# same on every rank, which is why it is deterministic and has no address-dependent behaviour).
+def _bare_heap(nbytes):
+    from collective_communication_mpi_b200.runtime.symm import PAD_REGION, SymmetricHeap
+    h = object.__new__(SymmetricHeap)
+    h.bytes = PAD_REGION + nbytes
+    h._free, h._live = [(PAD_REGION, nbytes)], {}
+    return h, PAD_REGION
+
+
+def test_symmetric_heap_offsets_are_deterministic_aligned_and_reused_after_free():
+    from collective_communication_mpi_b200.runtime.symm import ALIGN
+    (a, base), (b, _) = _bare_heap(1 << 20), _bare_heap(1 << 20)
+    sizes = [1, 255, 256, 257, 4096, 100_000, 7]
+    offs_a = [a.alloc(s) for s in sizes]
+    offs_b = [b.alloc(s) for s in sizes]
+    assert offs_a == offs_b, "every rank must compute the same offsets from the same call sequence"
+    assert offs_a[0] == base and all(o % ALIGN == 0 for o in offs_a)
+    assert all(o2 - o1 >= s for o1, o2, s in zip(offs_a, offs_a[1:], sizes)), "no overlap"
+    a.free(offs_a[1])
+    a.free(offs_a[2])                                    # neighbours coalesce: 512 B hole
+    assert a.alloc(512) == offs_a[1]
+    a.free(offs_a[4])
+    assert a.alloc(4096) == offs_a[4]                    # exact fit is taken, nothing is split off
+    with pytest.raises(KeyError):
+        a.free(12345)                                    # not an allocation
+    with pytest.raises(MemoryError, match="symmetric heap exhausted: need .* largest free block"):
+        a.alloc(2 << 20)
+
+
+def test_symmetric_heap_random_alloc_free_never_overlaps_and_merges_back():
+    from collective_communication_mpi_b200.runtime.symm import ALIGN
+    rng = random.Random(3)
+    h, base = _bare_heap(4 << 20)
+    live = {}
+    for _ in range(4000):
+        if live and rng.random() < 0.5:
+            off = rng.choice(list(live))
+            h.free(off)
+            del live[off]
+        else:
+            want = rng.randint(1, 200_000)
+            try:
+                off = h.alloc(want)
+            except MemoryError:
+                continue
+            size = max(ALIGN, (want + ALIGN - 1) // ALIGN * ALIGN)
+            assert base <= off and off + size <= h.bytes and off % ALIGN == 0
+            for o, s in live.items():
+                assert off + size <= o or o + s <= off, "overlapping symmetric allocations"
+            live[off] = size
+    for off in list(live):
+        h.free(off)
+    assert h._free == [(base, 4 << 20)] and not h._live
