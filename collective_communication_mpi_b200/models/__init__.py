@@ -1,2 +1,2 @@
 from .fc_stack import (MLPStack, TrainStep, TransformerFCBlock, TransformerFCBlockMegatron,  # noqa: F401
-                       TransformerFCBlockSP)
+                       TransformerFCBlockSP, TransformerFCStack)

@@ -34,14 +34,16 @@ class _Resizable:
 
 
 class TransformerFCBlock(_Resizable, nn.Module):
-    def __init__(self, mp_comm, tokens: int, hidden: int, ffn_mult: int = 4, *, seed: int = 0, num_comm_ctas: int = 0):
+    def __init__(self, mp_comm, tokens: int, hidden: int, ffn_mult: int = 4, *, seed: int = 0, num_comm_ctas: int = 0,
+                 share_scatter: bool = False):
         super().__init__()
         self.hidden, self.mp = hidden, mp_comm.Get_size()
+        kw = dict(num_comm_ctas=num_comm_ctas, share_scatter=share_scatter)
         # fc_q, fc_k, fc_v share their input: one gather, one GEMM with the three shards side by side
-        self.fc_qkv = ColumnParallelLinear(mp_comm, tokens, hidden, 3 * hidden, seed=seed + 1, num_comm_ctas=num_comm_ctas)
-        self.fc_o = RowParallelLinear(mp_comm, tokens, hidden, hidden, seed=seed + 2, num_comm_ctas=num_comm_ctas)
-        self.fc1 = ColumnParallelLinear(mp_comm, tokens, hidden, ffn_mult * hidden, seed=seed + 3, num_comm_ctas=num_comm_ctas)
-        self.fc2 = RowParallelLinear(mp_comm, tokens, ffn_mult * hidden, hidden, seed=seed + 4, num_comm_ctas=num_comm_ctas)
+        self.fc_qkv = ColumnParallelLinear(mp_comm, tokens, hidden, 3 * hidden, seed=seed + 1, **kw)
+        self.fc_o = RowParallelLinear(mp_comm, tokens, hidden, hidden, seed=seed + 2, **kw)
+        self.fc1 = ColumnParallelLinear(mp_comm, tokens, hidden, ffn_mult * hidden, seed=seed + 3, **kw)
+        self.fc2 = RowParallelLinear(mp_comm, tokens, ffn_mult * hidden, hidden, seed=seed + 4, **kw)
         # one-pass gate / GELU kernels with hand-written backward (CCMPI_FUSED_ELEMENTWISE=0: eager op chains)
         self.fused_elementwise = EW.enabled()
         # ... and GELU / GELU' / the residual adds inside the GEMM epilogues (CCMPI_FUSED_EPILOGUE=0: separate kernels)
@@ -61,6 +63,29 @@ class TransformerFCBlock(_Resizable, nn.Module):
         h = x + self.fc_o(a)
         u = torch.nn.functional.gelu(self.fc1(h), approximate="tanh")
         return h + self.fc2(u)
+
+
+class TransformerFCStack(_Resizable, nn.Module):
+    """``depth`` transformer FC blocks in sequence (the reference's layer set fc_q/k/v/o + fc1/fc2,
+    func_impl.py:65-70, repeated). All four reduce-scatters of a block produce ``[tokens, hidden]``, so with
+    ``share_scatter_ops`` (default) the whole stack uses ONE GEMM->reduce-scatter op and its flag region
+    (``parallel.tp_layers._scatter_op``): at 8192 tokens x 4096 over two ranks a block then takes 512 flag words
+    instead of 4608 and 26 blocks fit a communicator's signal pad instead of 3."""
+
+    def __init__(self, mp_comm, tokens: int, hidden: int, depth: int, ffn_mult: int = 4, *, seed: int = 0,
+                 share_scatter_ops: bool = True):
+        super().__init__()
+        self.hidden, self.mp, self.depth = hidden, mp_comm.Get_size(), depth
+        self.blocks = nn.ModuleList([TransformerFCBlock(mp_comm, tokens, hidden, ffn_mult, seed=seed + 10 * i,
+                                                        share_scatter=share_scatter_ops) for i in range(depth)])
+
+    def tp_layers(self) -> List[nn.Module]:
+        return [l for b in self.blocks for l in b.tp_layers()]
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        for b in self.blocks:
+            x = b(x)
+        return x
 
 
 class TransformerFCBlockSP(_Resizable, nn.Module):

@@ -166,6 +166,14 @@ class FusedOp:
     ctx: "FusedContext"
     flag_base: Optional[int] = None
     _closed = False
+    _refs = 1
+
+    def retain(self) -> "FusedOp":
+        """Another holder of this op (layers of one shape may share an op whose buffers carry nothing from
+        one call to the next, e.g. a GEMM->reduce-scatter: ``parallel.tp_layers`` with ``share_scatter``).
+        Each holder calls ``close()`` once; the last one really closes."""
+        self._refs += 1
+        return self
 
     def _heap_offsets(self):
         """Offsets this op took from the symmetric heap: attributes named ``*_off`` and the
@@ -183,6 +191,9 @@ class FusedOp:
         """Give the op's symmetric buffers and flag words back. COLLECTIVE: every member closes
         the same ops in the same order (``FusedContext.release_slot``)."""
         if self._closed:
+            return
+        if self._refs > 1:
+            self._refs -= 1
             return
         self._closed = True
         if self.flag_base is not None:
@@ -217,7 +228,8 @@ def close_fused_ops(module) -> int:
     for m in module.modules():
         for name in sorted(vars(m)):
             v = getattr(m, name)
-            if isinstance(v, FusedOp) and not v._closed:
+            # the kernels' ops or their CPU statements (ops/host_ops.py): same life cycle
+            if hasattr(v, "retain") and callable(getattr(v, "close", None)) and not getattr(v, "_closed", True):
                 v.close()
                 done += 1
     return done

@@ -80,8 +80,16 @@ class _HostOp:
     flag words, so ``close()`` only marks the object."""
 
     _closed = False
+    _refs = 1
+
+    def retain(self):
+        self._refs += 1
+        return self
 
     def close(self) -> None:
+        if self._refs > 1:
+            self._refs -= 1
+            return
         self._closed = True
 
     def __enter__(self):

@@ -129,6 +129,27 @@ def set_tokens(layer, tokens: int, *more_layers) -> None:
         l._build_ops()
 
 
+def _scatter_op(layer, width: int):
+    """The layer's GEMM->reduce-scatter op for ``[M, width]`` results. With ``layer.share_scatter`` every
+    layer of the communicator with that shape uses ONE op object: a reduce-scatter keeps nothing from one
+    call to the next (slots are double-buffered by launch parity and a rank can never be two launches ahead
+    of a peer whose partials it still reads, whichever layer launched), and its flag region -- one word per
+    tile and source, 1024 words at 8192 x 4096 over two ranks -- is what runs out first in a deep stack
+    (``N.PAD_USER_WORDS`` = 14336). The gather ops are NOT shared: their gathered operand is kept for the
+    backward dW GEMM."""
+    ops, comm = layer._ops, layer.comm
+    if not getattr(layer, "share_scatter", False):
+        return ops.GemmReduceScatter(comm, layer.M, width)
+    cache = vars(comm).setdefault("_shared_scatter_ops", {})
+    key = (ops.__name__, layer.M, width)
+    op = cache.get(key)
+    if op is None or op._closed:
+        op = cache[key] = ops.GemmReduceScatter(comm, layer.M, width)
+    else:
+        op.retain()
+    return op
+
+
 def _init_weight(rows: int, cols: int, fan_in: int, device, seed: int) -> nn.Parameter:
     g = torch.Generator(device=device).manual_seed(seed)
     w = torch.randn(rows, cols, device=device, generator=g, dtype=torch.float32) * (1.0 / math.sqrt(fan_in))
@@ -139,11 +160,11 @@ class ColumnParallelLinear(nn.Module):
     """``[M, in/mp] -> [M, out/mp]`` (or ``[M, out]`` with ``gather_output``)."""
 
     def __init__(self, mp_comm, tokens: int, in_features: int, out_features: int, *, gather_output: bool = False,
-                 grad_dtype=torch.bfloat16, seed: int = 0, num_comm_ctas: int = 0):
+                 grad_dtype=torch.bfloat16, seed: int = 0, num_comm_ctas: int = 0, share_scatter: bool = False):
         super().__init__()
         self.comm, self.mp = mp_comm, mp_comm.Get_size()
         self.M, self.K, self.N = tokens, in_features, out_features // self.mp
-        self.gather_output = gather_output
+        self.gather_output, self.share_scatter = gather_output, share_scatter
         self.grad_dtype = grad_dtype
         dev, ops, self._gemm, self._matmul_tn, self._gemm_sgd = _backend()
         self.sgd_lr = None      # set by TrainStep when the optimizer step is fused into the dW GEMM
@@ -158,7 +179,7 @@ class ColumnParallelLinear(nn.Module):
         ops, comm, tokens, in_features = self._ops, self.comm, self.M, self.K
         # a 1-member group needs no staging buffers or flags: plain GEMMs
         self.ag = ops.AllGatherGemm(comm, tokens, in_features, num_comm_ctas=self._num_comm_ctas) if self.mp > 1 else None
-        self.rs = ops.GemmReduceScatter(comm, tokens, in_features) if self.mp > 1 else None
+        self.rs = _scatter_op(self, in_features) if self.mp > 1 else None
         # gather_output: by default the fused all-gather->GEMM is followed by the strided all-gather
         # kernel on its output; CCMPI_FUSED_GATHER_OUTPUT=1 selects the single gather->GEMM->gather
         # kernel (ops/fused_seq.py)
@@ -217,9 +238,10 @@ class RowParallelLinear(nn.Module):
     """``[M, in/mp] -> [M, out/mp]``: partial products are reduce-scattered on the feature axis."""
 
     def __init__(self, mp_comm, tokens: int, in_features: int, out_features: int, *, grad_dtype=torch.bfloat16,
-                 seed: int = 0, num_comm_ctas: int = 0):
+                 seed: int = 0, num_comm_ctas: int = 0, share_scatter: bool = False):
         super().__init__()
         self.comm, self.mp = mp_comm, mp_comm.Get_size()
+        self.share_scatter = share_scatter
         self.M, self.K, self.N = tokens, in_features // self.mp, out_features
         self.grad_dtype = grad_dtype
         dev, ops, self._gemm, self._matmul_tn, self._gemm_sgd = _backend()
@@ -233,7 +255,7 @@ class RowParallelLinear(nn.Module):
 
     def _build_ops(self):
         ops, comm, tokens = self._ops, self.comm, self.M
-        self.rs = ops.GemmReduceScatter(comm, tokens, self.N) if self.mp > 1 else None
+        self.rs = _scatter_op(self, self.N) if self.mp > 1 else None
         self.ag = ops.AllGatherGemm(comm, tokens, self.N, num_comm_ctas=self._num_comm_ctas) if self.mp > 1 else None
 
     def set_tokens(self, tokens: int) -> None:

@@ -16,7 +16,7 @@ run() {   # run <label> <timeout> <command...>
     echo "[$label] rc=$rc  $(tail -1 "$log")" | tee -a "$OUT"
 }
 # 1. closing fused ops: flag words zeroed between barriers and reused by another kind of op
-run slot_reuse 300 python -m pytest tests/test_zzz_slot_reuse.py -q
+run slot_reuse 600 python -m pytest tests/test_zzz_slot_reuse.py -q     # close() / set_tokens() / shared scatter op of a block stack
 # 1b. one flag region, launches with changing CTA counts (absolute ready-flag targets)
 run flag_targets 300 python -m pytest tests/test_zzz_flag_targets.py -q
 # 2. smoke() as the driver runs it (five steps, loss must fall)

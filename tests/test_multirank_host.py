@@ -188,3 +188,9 @@ def test_status_probe_and_any_source(n):
 def test_v_collectives_with_ragged_blocks(n, flags):
     """``Allgatherv`` / ``Gatherv`` / ``Scatterv`` / ``Alltoallv`` / ``Reduce_scatter(recvcounts=...)``."""
     _ok(run_ranks(n, ["tests/workers/w_vcollectives.py"] + flags, timeout=120), f"V COLLECTIVES OK ranks={n} torch={int(bool(flags))}")
+
+
+@pytest.mark.parametrize("mp,dp,depth", [(2, 1, 3), (2, 2, 2), (4, 1, 2)])
+def test_block_stack_with_one_shared_scatter_op_matches_dense_model(mp, dp, depth):
+    """``TransformerFCStack``: several blocks, every reduce-scatter of the stack through ONE op object."""
+    _ok(run_ranks(mp * dp, ["tests/workers/w_stack.py", str(mp), str(dp), str(depth)], timeout=300), f"STACK OK mp={mp} dp={dp} depth={depth}")

@@ -28,3 +28,15 @@ def test_blocks_can_be_given_another_token_count_on_gpus(flags):
     proc = run_ranks(2, ["tests/workers/w_set_tokens.py", "2"] + flags, transport="device")
     assert proc.returncode == 0, f"rc={proc.returncode}\n--- stdout\n{proc.stdout[-4000:]}\n--- stderr\n{proc.stderr[-3000:]}"
     assert f"SET TOKENS OK mp=2 sp={sp} megatron={meg}" in proc.stdout
+
+
+@pytest.mark.parametrize("mp,dp,depth", [(2, 1, 3), (2, 2, 2)])
+def test_block_stack_shares_one_scatter_op_on_gpus(mp, dp, depth):
+    """``TransformerFCStack`` on the fused kernels: 4 x depth layers launch their reduce-scatters through one op
+    (one flag region, one pair of slot buffers); results match the dense model, a few steps train, close() of
+    every holder releases the op once."""
+    if gpu_count() < mp * dp:
+        pytest.skip(f"needs {mp * dp} GPUs")
+    proc = run_ranks(mp * dp, ["tests/workers/w_stack.py", str(mp), str(dp), str(depth)], transport="device")
+    assert proc.returncode == 0, f"rc={proc.returncode}\n--- stdout\n{proc.stdout[-4000:]}\n--- stderr\n{proc.stderr[-3000:]}"
+    assert f"STACK OK mp={mp} dp={dp} depth={depth}" in proc.stdout
