@@ -38,6 +38,7 @@ setup(
     package_data={"collective_communication_mpi_b200": ["lib/*.so"]},
     install_requires=["numpy", "torch"],
     cmdclass={"build_py": BuildWithNative},
-    entry_points={"console_scripts": ["ccmpi-launch=collective_communication_mpi_b200.launch:main"],
+    entry_points={"console_scripts": ["ccmpi-launch=collective_communication_mpi_b200.launch:main",
+                                      "ccmpi-info=collective_communication_mpi_b200.info:main"],
                   "pytest11": ["ccmpi_mpi=collective_communication_mpi_b200.pytest_plugin"]},
 )

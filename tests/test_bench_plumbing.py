@@ -51,3 +51,17 @@ def test_launcher_exports_torchrun_style_environment():
     p = run_ranks(3, ["-c", code])
     assert p.returncode == 0 and sorted(l for l in p.stdout.splitlines() if l.startswith("ENV")) == \
         ["ENV 0 3", "ENV 1 3", "ENV 2 3"]
+
+
+def test_info_command_describes_the_installation():
+    import json
+    import subprocess
+    import sys
+    p = subprocess.run([sys.executable, "-m", "collective_communication_mpi_b200.info", "--json"], cwd=REPO, capture_output=True,
+                       text=True, timeout=120, env=dict(os.environ, PYTHONPATH=REPO, CCMPI_HEAP_MB="512"))
+    assert p.returncode == 0, p.stderr[-2000:]
+    info = json.loads(p.stdout)
+    assert info["libraries"]["host"]["loads"] and info["libraries"]["device"]["loads"]
+    assert info["limits"]["flag_words_for_fused_ops"] == info["limits"]["signal_pad_words"] - 2048
+    assert info["environment"].get("CCMPI_HEAP_MB") == "512"
+    assert isinstance(info["gpus"], list) and "device_plane" in info
