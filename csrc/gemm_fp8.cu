@@ -2,11 +2,11 @@
 // operands K-major, fp32 accumulation in TMEM, bf16 or fp32 output. `scale` is the product of the
 // two per-tensor dequantisation scales and is applied in the epilogue.
 //
-// EXPERIMENTAL in round 1: written after the round's GPU budget was spent, so it has compiled
-// (UTCQMMA.2CTA in the SASS) but has not run on hardware yet; nothing in the default paths calls
-// it and its test is opt-in (CCMPI_TEST_UNVERIFIED=1). It is the first step towards BASELINE.md
-// config 3 (block-scaled fp8, tcgen05.mma.kind::mxf8f6f4.block_scale), which additionally needs the
-// scale-factor tiles in tensor memory.
+// Run on a B200 in round 2 (tests/test_gpu_fp8.py; UTCQMMA.2CTA in the SASS). Nothing in the
+// default paths calls it: it is the per-tensor-scaled step towards BASELINE.md config 3, whose
+// block-scaled form (tcgen05.mma.kind::mxf8f6f4.block_scale, scale-factor tiles in tensor memory)
+// is csrc/gemm_mxfp8.cu (stand-alone) and the MX mode of the generic CTA-pair kernel
+// (csrc/fused_gemm_mx.cu: plain, all-gather->GEMM, GEMM->reduce-scatter).
 #include "gemm_host.h"
 
 namespace gemm {

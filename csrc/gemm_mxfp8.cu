@@ -12,12 +12,12 @@
 //     execute in issue order, and the scale columns are double-buffered by K-block parity.
 // Tile: 256 x 128 per pair (two 128-column accumulators + 16 scale columns of tensor memory).
 //
-// EXPERIMENTAL DRAFT (round 1): compiles for sm_100a; NOT yet run on hardware. What could be checked without
-// a GPU was: the instruction descriptor, the shared-memory descriptor of a scale chunk (LBO 16 B, SBO 128 B,
-// no swizzle) and the scale layouts in shared and tensor memory (32 lanes x 4 columns per chunk, scale id =
-// byte of the column, replicated to the four lane quadrants) are bit-for-bit what the CUTLASS 4.5 headers on
-// the image compute for this tile (evaluated in a host program). Nothing uses the kernel; its test is opt-in
-// (CCMPI_TEST_UNVERIFIED=1).
+// Run on a B200 in round 2 (tests/test_gpu_fp8.py); the MX mode of the generic CTA-pair kernel agrees with it
+// bit for bit (tests/test_gpu_mx_fused.py). Checked without a GPU as well: the instruction descriptor, the
+// shared-memory descriptor of a scale chunk (LBO 16 B, SBO 128 B, no swizzle) and the scale layouts in shared
+// and tensor memory (32 lanes x 4 columns per chunk, scale id = byte of the column, replicated to the four lane
+// quadrants) are bit-for-bit what the CUTLASS 4.5 headers on the image compute for this tile (evaluated in a
+// host program, scripts/cutlass_crosscheck.sh).
 #include "gemm_host.h"
 #include "mx_desc.cuh"
 
