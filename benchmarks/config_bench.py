@@ -25,7 +25,7 @@ CONFIGS = {
     "tp8": dict(model="block", hidden=8192, ffn=4, tokens=8192, mp="all"),
     "tp24": dict(model="block", hidden=4096, ffn=4, tokens=8192, mp=2),
     "dp8": dict(model="mlp", hidden=8192, depth=16, tokens=4096, mp=1),
-    # the same block in the other two activation layouts (ours only; kernels / layers not yet run on hardware)
+    # the same block in the other two activation layouts (ours only)
     "tp8sp": dict(model="block_sp", hidden=8192, ffn=4, tokens=8192, mp="all"),
     "tp8meg": dict(model="block_megatron", hidden=8192, ffn=4, tokens=8192, mp="all"),
     "tp24sp": dict(model="block_sp", hidden=4096, ffn=4, tokens=8192, mp=2),

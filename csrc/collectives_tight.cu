@@ -8,9 +8,9 @@
 //     MAXR = 2: U = 8      MAXR = 4: U = 4      MAXR = 8: U = 2
 // Same protocol, same rank-ordered reduction (bit-identical results), same barriers.
 //
-// EXPERIMENTAL in round 1: written after the GPU budget was spent; compiled, not yet run or measured. The
-// regular kernels stay the default until this has been timed against them (the 2-GPU reduce-scatter, 336 vs
-// NCCL's 385 GB/s at 256 MB, is the case it is meant to fix).
+// Run and measured in round 2 (tests/test_gpu_tight.py; sweeps profiles/r2_sweep_{2,4,8}gpu.jsonl: +3..44 %
+// over the generic kernels) and now the default for two-shot all-reduce and pull reduce-scatter; the 2-GPU
+// reduce-scatter went from 336 to 602 GB/s at 256 MB (NCCL 390).
 #include "collectives_common.cuh"
 
 namespace coll {

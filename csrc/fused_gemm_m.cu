@@ -1,5 +1,5 @@
 // Host entry points of the token-axis (sequence-parallel) fused kernels; device side:
-// fused_policies_m.cuh. EXPERIMENTAL in round 1 (compiled, not yet run on hardware).
+// fused_policies_m.cuh. Run on B200s in round 2 (tests/test_gpu_seq.py).
 //
 // Same calling conventions as fused_gemm.cu: `nvr` device communicators (1 in production, one per
 // member to emulate the ranks in one cooperative launch on one GPU), per-rank pointer lists, and

@@ -8,8 +8,8 @@
 // machinery (background push on the bulk-copy engine, staged bulk epilogue, per-tile flags,
 // opportunistic rank-ordered reduction); only the index arithmetic differs.
 //
-// EXPERIMENTAL in round 1: written after the round's GPU budget was spent; compiled, not yet run on
-// hardware, opt-in tests only (CCMPI_TEST_UNVERIFIED=1). CTA-pair kernel only.
+// Run on B200s in round 2: emulated ranks on one GPU and real ranks on 2 / 4 / 8 GPUs
+// (tests/test_gpu_seq.py, profiles/r2_seq_bench_2gpu.jsonl). CTA-pair kernel only.
 #pragma once
 #include "fused_policies.cuh"
 
@@ -304,7 +304,7 @@ namespace gemm {
 //   off2 : symmetric offset of y_full [M][N * size] (OutT)
 // The staging row of an epilogue lane serves both its pushes and its output rows; each use starts
 // by waiting until the previous bulk copy has finished reading the row.
-// EXPERIMENTAL in round 1 (compiled, not yet run on hardware). CTA-pair kernel only.
+// Run on B200s in round 2 (tests/test_gpu_seq.py::test_gather_gemm_gather*). CTA-pair kernel only.
 // ================================================================================================
 struct AgKAgOutPolicy : AgKPolicy {
     static constexpr bool kEpiOps = false;   // own store: no fused elementwise epilogue

@@ -246,7 +246,7 @@ int ccmpi_fused_gemm_ag(const ccmpi_dev_comm* comms, int nvr, const void* const*
                         size_t yfull_off, int M, int N, int K, int lda, int ldb, int a_km, int b_kn,
                         int out_dtype, int num_sms, int use_mc, void* stream);
 
-/* EXPERIMENTAL (compiled, not yet run on hardware in round 1): the token-axis ("sequence
+/* Run on B200s in round 2 (tests/test_gpu_seq.py): the token-axis ("sequence
  * parallel") forms of the two kernels above (csrc/fused_gemm_m.cu, csrc/fused_policies_m.cuh).
  * The reference shards only the feature axis; these cover layouts that shard the activation rows.
  * M/n must be a multiple of 256. CTA-pair kernels only.
@@ -263,7 +263,7 @@ int ccmpi_fused_gemm_rs_m(const ccmpi_dev_comm* comms, int nvr, const void* cons
                           int a_km, int b_kn, int out_dtype, int flag_base, unsigned epoch, int num_sms,
                           void* stream);
 
-/* EXPERIMENTAL (compiled, not yet run on hardware in round 1): the reference's whole forward step
+/* Run on B200s in round 2 (tests/test_gpu_seq.py): the reference's whole forward step
  * -- gather the input, multiply, gather the output (func_impl.py:76-109) -- in one kernel:
  * ccmpi_fused_ag_gemm's K-gather plus ccmpi_fused_gemm_ag's epilogue. yfull_off: symmetric
  * [M][N*n]; x_off / xfull_off as in ccmpi_fused_ag_gemm. */
@@ -272,7 +272,7 @@ int ccmpi_fused_ag_gemm_ag(const ccmpi_dev_comm* comms, int nvr, size_t x_off, i
                            int out_dtype, int flag_base, unsigned epoch, unsigned flag_target, int num_sms,
                            void* stream);
 
-/* EXPERIMENTAL (compiled, not yet run on hardware in round 1): fused elementwise kernels of the
+/* Run on B200s in round 2 (tests/test_gpu_elementwise.py; default in the models): fused elementwise kernels of the
  * transformer-FC block (csrc/elementwise.cu), bf16 in / bf16 out, fp32 math, one pass over HBM each.
  * The reference has no compute; these sit between the GEMMs of models/fc_stack.py.
  *   gate:  a[T][H] = v * sigmoid(q * k) with qkv[T][3H] = q | k | v; backward writes dq | dk | dv.
@@ -288,7 +288,7 @@ size_t ccmpi_mse_workspace_bytes(void);
 int ccmpi_mse_fwd_bwd(const void* y, const void* t, void* dy, long long n, void* workspace, void* loss,
                       void* stream);
 
-/* EXPERIMENTAL (compiled, not yet run or measured in round 1): the pull-style reduce-scatter and the two-shot
+/* Run and measured in round 2 (tests/test_gpu_tight.py; the default): the pull-style reduce-scatter and the two-shot
  * all-reduce with their in-flight buffers sized by the communicator (2 / 4 / 8 members) instead of for 8
  * (csrc/collectives_tight.cu). fp32 / bf16, SUM / MIN / MAX, 16-byte aligned operands; anything else returns
  * CCMPI_ERR_UNSUPPORTED. Results are bit-identical to ccmpi_reduce_scatter / ccmpi_allreduce(CCMPI_AR_TWOSHOT). */
@@ -339,14 +339,14 @@ int ccmpi_fused_gemm_rs_mx(const ccmpi_dev_comm* comms, int nvr, const void* con
                            const void* const* residual, long long res_ld, void* trace, int num_sms, void* stream);
 int ccmpi_quantize_mxfp8(const void* x, long long ldx, void* q, long long ldq, void* sf, int R, int K, void* stream);
 
-/* EXPERIMENTAL (compiled, not yet run on hardware in round 1): fp8 e4m3 GEMM on the CTA-pair
+/* Run on a B200 in round 2 (tests/test_gpu_fp8.py): fp8 e4m3 GEMM on the CTA-pair
  * kernel, C[M][N] = scale * A[M][K] * B[N][K]^T, both operands K-major (tcgen05.mma.kind::f8f6f4).
  * First step towards the block-scaled fp8 FC layers of BASELINE.md config 3; the reference has no
  * GEMM at all. */
 int ccmpi_gemm_fp8_e4m3(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb,
                         int ldc, float scale, int out_dtype, int num_sms, void* stream);
 
-/* EXPERIMENTAL DRAFT (compiled, not yet run on hardware in round 1): block-scaled fp8 GEMM (OCP MXFP8:
+/* Run on a B200 in round 2 (tests/test_gpu_fp8.py, tests/test_gpu_mx_fused.py): block-scaled fp8 GEMM (OCP MXFP8:
  * e4m3 values, one UE8M0 scale per 1 x 32 block), C[M][N] = (A * 2^sfa) (B * 2^sfb)^T with both operands
  * K-major, on tcgen05.mma.kind::mxf8f6f4.block_scale (csrc/gemm_mxfp8.cu). sfa / sfb are in the tensor
  * cores' chunked layout: 512-byte chunks of 128 rows x 4 scales, K-fastest, padded to whole chunks

@@ -147,7 +147,7 @@ def test_sequence_parallel_block_matches_dense_model(mp, dp):
 
 @pytest.mark.parametrize("mp,dp", [(2, 1), (2, 2), (8, 1)])
 def test_megatron_layout_block_matches_dense_model(mp, dp):
-    """Layers built from hardware-verified ops (plain GEMM, GEMM -> all-reduce) but not yet run themselves."""
+    """Classic Megatron layout (replicated activations, GEMM -> all-reduce) against the dense model."""
     from conftest import gpu_count, run_ranks
     if gpu_count() < mp * dp:
         pytest.skip(f"needs {mp * dp} GPUs")
