@@ -19,7 +19,7 @@ from mpi4py import MPI  # noqa: E402
 from data.data_parallel_preprocess import split_data  # noqa: E402
 from model.func_impl import get_info  # noqa: E402
 from collective_communication_mpi_b200.models import (TrainStep, TransformerFCBlock, TransformerFCBlockMegatron,  # noqa: E402
-                                                      TransformerFCBlockSP)
+                                                      TransformerFCBlockSP, TransformerFCStack)
 
 
 def main():
@@ -28,10 +28,15 @@ def main():
     ap.add_argument("--hidden", type=int, default=512)
     ap.add_argument("--tokens", type=int, default=256, help="tokens per replica and step")
     ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--depth", type=int, default=1, help="number of blocks in sequence (reference layout; the stack shares one "
+                                                         "reduce-scatter op between all its layers)")
     ap.add_argument("--sp", action="store_true", help="sequence-parallel layout: each rank holds tokens/mp rows of the full width")
     ap.add_argument("--megatron", action="store_true", help="classic Megatron layout: activations replicated across the mp group")
-    ap.add_argument("--lr", type=float, default=10.0, help="plain SGD on a mean-squared error: gradients are tiny")
+    ap.add_argument("--lr", type=float, default=None, help="plain SGD on a mean-squared error: gradients are tiny "
+                                                           "(default 10 for one block, 0.3 for a stack)")
     args = ap.parse_args()
+    if args.lr is None:
+        args.lr = 10.0 if args.depth == 1 else 0.3
 
     comm = MPI.COMM_WORLD
     rank, world = comm.Get_rank(), comm.Get_size()
@@ -46,7 +51,12 @@ def main():
     mp_idx, dp_idx, mp_comm, dp_comm, _, _ = get_info(comm=comm, rank=rank, mp_size=args.mp, dp_size=dp, fc_layer="fc_q",
                                                       in_dim=args.hidden, out_dim=args.hidden)
     block = TransformerFCBlockSP if args.sp else TransformerFCBlockMegatron if args.megatron else TransformerFCBlock
-    model = block(mp_comm, args.tokens, args.hidden, ffn_mult=4, seed=1)
+    if args.depth > 1:
+        if args.sp or args.megatron:
+            raise SystemExit("--depth > 1 builds the reference-layout stack; drop --sp / --megatron")
+        model = TransformerFCStack(mp_comm, args.tokens, args.hidden, args.depth, ffn_mult=4, seed=1)
+    else:
+        model = block(mp_comm, args.tokens, args.hidden, ffn_mult=4, seed=1)
     step = TrainStep(model, dp_comm, lr=args.lr)
 
     # one fixed synthetic regression task; every replica gets its slice of the batch, every model-parallel

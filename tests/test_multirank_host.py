@@ -194,3 +194,18 @@ def test_v_collectives_with_ragged_blocks(n, flags):
 def test_block_stack_with_one_shared_scatter_op_matches_dense_model(mp, dp, depth):
     """``TransformerFCStack``: several blocks, every reduce-scatter of the stack through ONE op object."""
     _ok(run_ranks(mp * dp, ["tests/workers/w_stack.py", str(mp), str(dp), str(depth)], timeout=300), f"STACK OK mp={mp} dp={dp} depth={depth}")
+
+
+def test_examples_stack_and_task_farm():
+    import os
+    import subprocess
+    import sys
+    from conftest import REPO
+    env = dict(os.environ, PYTHONPATH=REPO)
+    base = [sys.executable, "-m", "collective_communication_mpi_b200.launch", "--transport", "host"]
+    p = subprocess.run(base + ["-n", "4", sys.executable, "examples/train_block.py", "--mp", "2", "--steps", "5", "--depth", "2"],
+                       cwd=REPO, capture_output=True, text=True, timeout=300, env=env)
+    assert p.returncode == 0 and "TRAIN OK" in p.stdout, p.stdout[-2000:] + p.stderr[-2000:]
+    p = subprocess.run(base + ["-n", "5", sys.executable, "examples/master_worker.py", "--items", "30"],
+                       cwd=REPO, capture_output=True, text=True, timeout=120, env=env)
+    assert p.returncode == 0 and "FARM OK" in p.stdout, p.stdout[-2000:] + p.stderr[-2000:]
