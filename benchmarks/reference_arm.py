@@ -33,6 +33,23 @@ import time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
+def usable_cpus() -> int:
+    """CPUs this process may really use: the affinity mask, capped by a cgroup CPU quota when there is one
+    (a container with 16 of a host's 128 CPUs must not start 128 BLAS threads)."""
+    try:
+        n = len(os.sched_getaffinity(0))
+    except (AttributeError, OSError):
+        n = os.cpu_count() or 1
+    try:
+        with open("/sys/fs/cgroup/cpu.max") as f:
+            quota, period = f.read().split()[:2]
+        if quota != "max":
+            n = min(n, max(1, -(-int(quota) // int(period))))
+    except (OSError, ValueError):
+        pass
+    return max(1, n)
+
+
 def run_reference(args, emit, grid_for, cfg):
     t_start = time.perf_counter()
     rank = int(os.environ.get("RANK", "0"))
@@ -56,7 +73,7 @@ def run_reference(args, emit, grid_for, cfg):
         if rank == 0:
             emit({"impl": "reference", "unavailable": f"--gpus {args.gpus} but WORLD_SIZE={world}"})
         return
-    ncpu = os.cpu_count() or 1
+    ncpu = usable_cpus()
     threads = max(1, ncpu // world)
     for k in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
         os.environ[k] = str(threads)
