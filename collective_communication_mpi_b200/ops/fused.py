@@ -203,6 +203,7 @@ class FusedOp:
             self.ctx.comm.Barrier()
         for off in self._heap_offsets():
             self.ctx.heap.free(off)
+        KT.forget(self)
         for name, v in list(vars(self).items()):       # drop the views: the memory may be handed out again
             if torch.is_tensor(v) or (isinstance(v, list) and v and isinstance(v[0], tuple)):
                 setattr(self, name, None)

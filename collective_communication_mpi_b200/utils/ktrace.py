@@ -45,6 +45,12 @@ def buffer_for(owner, name: str) -> Optional[torch.Tensor]:
     return buf
 
 
+def forget(owner) -> None:
+    """Drop the trace buffer of an op that is being closed (``id()`` values are reused by later objects)."""
+    _buffers.pop(id(owner), None)
+    _names.pop(id(owner), None)
+
+
 def last(owner) -> Optional[torch.Tensor]:
     """The buffer the last traced launch of ``owner`` wrote (no reset)."""
     return _buffers.get(id(owner))
@@ -52,7 +58,8 @@ def last(owner) -> Optional[torch.Tensor]:
 
 def summary(buf: torch.Tensor, sm_mhz: float = 1965.0) -> dict:
     """Decode the last launch recorded in ``buf``: per-role blocked time, mean / max over CTAs, in us."""
-    torch.cuda.synchronize()
+    if buf.is_cuda:
+        torch.cuda.synchronize()
     t = buf.view(-1, WORDS).cpu()
     live = t[:, 0] != 0
     t = t[live]
