@@ -8,7 +8,8 @@ reference never needed it (README.md:52 runs CPU ranks). Here the rank pins itse
 process touches afterwards (pinned batches included) is then allocated on that node by first touch.
 
 Everything is best effort: no sysfs entry, node -1, or a cpuset that forbids the CPUs -> nothing changes.
-Not measured yet (neither round had GPU minutes left for the A/B run), hence opt-in.
+Not measured: the pool's 8-GPU boxes are virtual machines that expose ONE NUMA node (CPU affinity 0-31 and NUMA
+node 0 for all eight GPUs, profiles/r1_topo_8gpu.txt), so binding is a no-op there. Hence opt-in.
 """
 from __future__ import annotations
 
