@@ -32,6 +32,9 @@ def test_reference_arm_emits_one_json_line(nproc):
     assert d["impl"] == "reference" and d["n_gpus"] == nproc
     assert d["metric"] == "tp_fc_fwd_bwd_tokens_per_s" and d["value"] > 0 and d["higher_is_better"] is True
     assert "shared-memory stand-in" in d["mpi_runtime"]
+    # none of this repository's kernels or engine on the reference arm: only the host transport is mapped
+    assert d["native_libs_mapped"] == (["libccmpi_host.so"] if nproc > 1 else []), d["native_libs_mapped"]
+    assert d["gpu_launches"] == 0 and d["e2e"]["ms_per_step"] == d["ms_per_step"]
 
 
 def test_reference_arm_shortens_the_run_to_its_wall_budget_and_says_so():
