@@ -45,3 +45,15 @@ def test_transports_and_tp_layers_against_the_oracle(nranks):
     p = run_ranks(nranks, ["tests/workers/w_oracle.py"])
     assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-3000:]
     assert f"ORACLE OK ranks={nranks}" in p.stdout
+
+
+def test_committed_result_tables_are_what_the_raw_measurement_files_say():
+    """profiles/R2_RESULTS.md is generated from the raw r2_* files (scripts/make_profiles_readme.py); a table that
+    was edited by hand, or raw files changed without regenerating, fails here."""
+    import os
+    import subprocess
+    import sys
+    from conftest import REPO
+    p = subprocess.run([sys.executable, os.path.join("scripts", "make_profiles_readme.py"), "--check"], cwd=REPO,
+                       capture_output=True, text=True, timeout=120)
+    assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-2000:]
