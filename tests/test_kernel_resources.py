@@ -66,3 +66,50 @@ def test_the_generic_reductions_are_the_ones_with_stack_arrays(families):
     buffers for 8 members and the compiler keeps part of them on the stack."""
     assert max(k["stack"] for k in families["coll::allreduce_twoshot_kernel"]) > 100
     assert max(k["stack"] for k in families["coll::reduce_scatter_kernel"]) > 100
+
+
+# ---- SASS of the built library: the Blackwell instructions the kernels of record are made of ------------------
+def _sass(mangled=None):
+    import subprocess
+    from collective_communication_mpi_b200 import build as B
+    cmd = ["cuobjdump", "-sass"] + (["-fun", mangled] if mangled else []) + [str(B.DEVICE_LIB)]
+    return subprocess.run(cmd, capture_output=True, text=True, timeout=600).stdout
+
+
+KERNELS = {
+    "gemm": "_ZN4gemm16gemm_kernel_2ctaILi256ELb0ELb1E13__nv_bfloat16NS_11PlainPolicyELi2ELb0EEEvNS_6LaunchE",
+    "ag_gemm": "_ZN4gemm16gemm_kernel_2ctaILi256ELb0ELb1E13__nv_bfloat16NS_9AgKPolicyELi2ELb0EEEvNS_6LaunchE",
+    "gemm_rs": "_ZN4gemm16gemm_kernel_2ctaILi256ELb0ELb1E13__nv_bfloat16NS_9RsNPolicyELi2ELb0EEEvNS_6LaunchE",
+    "ag_gemm_mx": "_ZN4gemm16gemm_kernel_2ctaILi128ELb0ELb0E13__nv_bfloat16NS_9AgKPolicyELi1ELb1EEEvNS_6LaunchE",
+    "allreduce_nvls": "_ZN4coll21allreduce_nvls_kernelI13__nv_bfloat16S1_EEvNS_6LaunchEmmmf",
+    "allreduce_sgd_nvls": "_ZN4coll25allreduce_sgd_nvls_kernelENS_6LaunchEmmmfyjj",
+}
+
+
+def test_kernels_of_record_are_made_of_tcgen05_tma_and_multimem_instructions():
+    import re
+    found = {k: set(re.findall(r"\b(UTC[A-Z]+(?:\.[A-Z0-9_]+)*|UTMALDG(?:\.[A-Z0-9_]+)*|UBLKCP(?:\.[A-Z0-9_]+)*|LDTM(?:\.[a-zA-Z0-9_]+)*"
+                               r"|LDGMC(?:\.[A-Z0-9_]+)*|[A-Z]+(?:\.[A-Z0-9_]+)*\.SYS\b)", _sass(m)))
+             for k, m in KERNELS.items()}
+    has = lambda k, prefix: any(x.startswith(prefix) for x in found[k])        # noqa: E731
+    for k in ("gemm", "ag_gemm", "gemm_rs"):
+        assert has(k, "UTCHMMA.2CTA"), (k, "tcgen05.mma cta_group::2 (bf16)")
+        assert has(k, "UTMALDG.2D"), (k, "TMA tensor loads")
+        assert has(k, "LDTM"), (k, "tcgen05.ld from tensor memory")
+    assert has("ag_gemm", "UBLKCP") and has("gemm_rs", "UBLKCP"), "bulk copies carry the peer traffic"
+    assert any(x.endswith(".SYS") for x in found["ag_gemm"]) and any(x.endswith(".SYS") for x in found["gemm_rs"]), "system-scope flags"
+    assert has("ag_gemm_mx", "UTCQMMA.2CTA") and has("ag_gemm_mx", "UTCCP"), "block-scaled MMA + scale copies into tensor memory"
+    assert has("allreduce_nvls", "LDGMC") and has("allreduce_sgd_nvls", "LDGMC"), "multimem.ld_reduce (reduction in the switch)"
+
+
+def test_no_tma_load_in_the_library_is_a_multicast_load():
+    """TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's
+    memory hung the GPU -- in fact the library issues no multicast TMA load at all: the only cluster-multicast
+    instruction is the MMA-completion signal (tcgen05.commit -> UTCBAR), which touches shared-memory barriers."""
+    import collections
+    import re
+    ops = collections.Counter(re.findall(r"\b((?:UTMALDG|UBLKCP|UTMASTG|UTMAREDG|UTMAPF|UTCBAR)(?:\.[A-Z0-9_]+)*)", _sass()))
+    assert ops, "no SASS found"
+    loads = {k: v for k, v in ops.items() if k.startswith(("UTMALDG", "UBLKCP"))}
+    assert loads and not any("MULTICAST" in k or ".MC" in k for k in loads), loads
+    assert any(k.startswith("UTCBAR") and "MULTICAST" in k for k in ops)
