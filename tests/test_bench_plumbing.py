@@ -33,7 +33,8 @@ def test_reference_arm_emits_one_json_line(nproc):
     assert d["metric"] == "tp_fc_fwd_bwd_tokens_per_s" and d["value"] > 0 and d["higher_is_better"] is True
     assert "shared-memory stand-in" in d["mpi_runtime"]
     # none of this repository's kernels or engine on the reference arm: only the host transport is mapped
-    assert d["native_libs_mapped"] == (["libccmpi_host.so"] if nproc > 1 else []), d["native_libs_mapped"]
+    libs = d["native_libs_mapped"]      # (a sanitizer build of the host transport has another file name)
+    assert len(libs) == (1 if nproc > 1 else 0) and all(l.startswith("libccmpi_host") for l in libs), libs
     assert d["gpu_launches"] == 0 and d["e2e"]["ms_per_step"] == d["ms_per_step"]
 
 
